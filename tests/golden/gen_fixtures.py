@@ -1,0 +1,188 @@
+#!/usr/bin/env python3
+"""Generate the AV1 bitstream fixtures + golden per-frame MD5s committed under tests/golden/.
+
+Run in the BUILD container only (needs Pillow's AVIF plugin = libaom encoder, and
+oracle/_ref/libdav1d_ref.so = the reference's own dav1d C build, see oracle/Makefile):
+
+    python tests/golden/gen_fixtures.py
+
+Method: no media is vendored in the reference and no
+stand-alone encoder exists offline, so clips are synthesised with numpy, encoded
+through Pillow's animated-AVIF writer (aom), the av01 samples are demuxed from the
+ISOBMFF container and written as IVF.  The golden answer of every clip is the
+per-frame MD5 of the visible Y,U,V planes as decoded by the reference C decoder
+(method of ext/dav1d/tools/output/md5.c:194-250, reset per frame).
+"""
+import hashlib
+import io
+import json
+import os
+import struct
+import sys
+
+import numpy as np
+from PIL import Image
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.join(HERE, "..", ".."))
+
+
+def synth_frames(w, h, n, seed, noise=3.0, pan=(3, 2)):
+    """Low-pass noise field panning + two moving shapes + per-frame noise (C1/C2 recipe)."""
+    rng = np.random.default_rng(seed)
+    big_w, big_h = w + abs(pan[0]) * n + 16, h + abs(pan[1]) * n + 16
+    lo = rng.integers(0, 256, size=((big_h + 7) // 8 + 2, (big_w + 7) // 8 + 2, 3), dtype=np.uint8)
+    field = np.asarray(Image.fromarray(lo).resize((big_w, big_h), Image.BICUBIC), dtype=np.float32)
+    frames = []
+    for i in range(n):
+        ox, oy = pan[0] * i, pan[1] * i
+        f = field[oy:oy + h, ox:ox + w].copy()
+        # moving shapes
+        cx = int((0.2 + 0.6 * i / max(n - 1, 1)) * w)
+        cy = int(0.3 * h)
+        r = max(h // 10, 4)
+        f[max(cy - r, 0):cy + r, max(cx - r, 0):cx + r] = (220, 40, 40)
+        cy2 = int((0.8 - 0.5 * i / max(n - 1, 1)) * h)
+        cx2 = int(0.7 * w)
+        yy, xx = np.ogrid[:h, :w]
+        f[(yy - cy2) ** 2 + (xx - cx2) ** 2 < r * r] = (30, 200, 90)
+        f += rng.normal(0.0, noise, size=f.shape).astype(np.float32)
+        frames.append(Image.fromarray(np.clip(f, 0, 255).astype(np.uint8)))
+    return frames
+
+
+def boxes(buf, start, end):
+    pos = start
+    while pos + 8 <= end:
+        size, typ = struct.unpack(">I4s", buf[pos:pos + 8])
+        hdr = 8
+        if size == 1:
+            size = struct.unpack(">Q", buf[pos + 8:pos + 16])[0]
+            hdr = 16
+        elif size == 0:
+            size = end - pos
+        yield typ.decode("latin1"), pos + hdr, pos + size
+        pos += size
+
+
+def find(buf, start, end, path):
+    for typ, s, e in boxes(buf, start, end):
+        if typ == path[0]:
+            if len(path) == 1:
+                return s, e
+            r = find(buf, s, e, path[1:])
+            if r:
+                return r
+    return None
+
+
+def avif_samples(buf):
+    """Return the list of av01 samples (bytes) of the first video track."""
+    stbl = find(buf, 0, len(buf), ["moov", "trak", "mdia", "minf", "stbl"])
+    assert stbl, "no moov/trak (not an image sequence?)"
+    s, e = stbl
+    sizes, chunk_offs, stsc = [], [], []
+    for typ, bs, be in boxes(buf, s, e):
+        if typ == "stsz":
+            _, fixed, cnt = struct.unpack(">III", buf[bs:bs + 12])
+            sizes = [fixed] * cnt if fixed else list(struct.unpack(">%dI" % cnt, buf[bs + 12:bs + 12 + 4 * cnt]))
+        elif typ == "stco":
+            _, cnt = struct.unpack(">II", buf[bs:bs + 8])
+            chunk_offs = list(struct.unpack(">%dI" % cnt, buf[bs + 8:bs + 8 + 4 * cnt]))
+        elif typ == "co64":
+            _, cnt = struct.unpack(">II", buf[bs:bs + 8])
+            chunk_offs = list(struct.unpack(">%dQ" % cnt, buf[bs + 8:bs + 8 + 8 * cnt]))
+        elif typ == "stsc":
+            _, cnt = struct.unpack(">II", buf[bs:bs + 8])
+            stsc = [struct.unpack(">III", buf[bs + 8 + 12 * i:bs + 20 + 12 * i]) for i in range(cnt)]
+    samples, si = [], 0
+    for ci, off in enumerate(chunk_offs):
+        per = 1
+        for first, n, _ in stsc:
+            if ci + 1 >= first:
+                per = n
+        pos = off
+        for _ in range(per):
+            if si >= len(sizes):
+                break
+            samples.append(bytes(buf[pos:pos + sizes[si]]))
+            pos += sizes[si]
+            si += 1
+    assert si == len(sizes), (si, len(sizes))
+    return samples
+
+
+def write_ivf(path, samples, w, h, fps=30):
+    with open(path, "wb") as f:
+        f.write(b"DKIF" + struct.pack("<HH4sHHIIII", 0, 32, b"AV01", w, h, fps, 1, len(samples), 0))
+        for i, s in enumerate(samples):
+            f.write(struct.pack("<IQ", len(s), i))
+            f.write(s)
+
+
+def read_ivf(path):
+    buf = open(path, "rb").read()
+    assert buf[:4] == b"DKIF"
+    hdr = struct.unpack("<H", buf[6:8])[0]
+    pos, out = hdr, []
+    while pos + 12 <= len(buf):
+        sz = struct.unpack("<I", buf[pos:pos + 4])[0]
+        out.append(buf[pos + 12:pos + 12 + sz])
+        pos += 12 + sz
+    return out
+
+
+def encode(frames, advanced, quality=55, speed=6):
+    bio = io.BytesIO()
+    frames[0].save(bio, format="AVIF", save_all=True, append_images=frames[1:], codec="aom",
+                   quality=quality, speed=speed, subsampling="4:2:0", duration=33,
+                   advanced=advanced)
+    return bio.getvalue()
+
+
+def golden_md5(obu):
+    from tests.refdec import decode_all_big as _dec
+    decode_all = lambda o: _dec(o, 3840 * 2160 * 4)
+    out = []
+    for info, planes in decode_all(obu):
+        out.append({"md5": hashlib.md5(planes).hexdigest(), "w": info.w, "h": info.h,
+                    "bpc": info.bpc, "layout": info.layout, "frame_type": info.frame_type})
+    return out
+
+
+CLIPS = {
+    # name: (w, h, n_frames, seed, advanced-options, quality, speed)
+    # intra-only, no post filters: recon parity in isolation
+    "intra_64x64_nofilt": (64, 64, 2, 11, {"enable-cdef": "0", "enable-restoration": "0", "enable-palette": "0",
+                                            "enable-intrabc": "0"}, 60, 6),
+    "cif_intra": (352, 288, 2, 12, {"enable-cdef": "1", "enable-restoration": "1"}, 55, 6),
+    "cif_inter": (352, 288, 8, 13, {"enable-cdef": "1", "enable-restoration": "1"}, 55, 6),
+    "c1_360p": (640, 360, 12, 1, {"enable-cdef": "1", "enable-restoration": "1"}, 55, 6),
+    "c2_1080p": (1920, 1080, 6, 7, {"enable-cdef": "1", "enable-restoration": "1"}, 55, 6),
+}
+
+
+def main():
+    only = sys.argv[1:]
+    manifest_path = os.path.join(HERE, "manifest.json")
+    manifest = json.load(open(manifest_path)) if os.path.exists(manifest_path) else {}
+    for name, (w, h, n, seed, adv, q, spd) in CLIPS.items():
+        if only and name not in only:
+            continue
+        frames = synth_frames(w, h, n, seed)
+        avif = encode(frames, adv, q, spd)
+        samples = avif_samples(avif)
+        ivf = os.path.join(HERE, name + ".ivf")
+        write_ivf(ivf, samples, w, h)
+        obu = b"".join(samples)
+        g = golden_md5(obu)
+        manifest[name] = {"file": name + ".ivf", "w": w, "h": h, "frames": g, "bytes": len(obu),
+                          "encoder": "Pillow AVIF/aom", "advanced": adv, "quality": q, "speed": spd,
+                          "seed": seed}
+        print(name, len(samples), "samples", len(obu), "bytes ->", len(g), "decoded frames",
+              [x["frame_type"] for x in g])
+    json.dump(manifest, open(manifest_path, "w"), indent=1, sort_keys=True)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,100 @@
+// dev_common.cuh — shared device-side definitions for the sm_100a reconstruction kernels.
+//
+// Every per-command routine is written as a CTA-cooperative function
+//     fn(..., int tid, int nthr)
+// whose threads stride over independent output elements and meet at CTA_SYNC().
+// (tests/emu builds the same code for the host with one "thread" per CTA, purely
+// as a debugging aid for arithmetic; it is never part of the product.)
+#pragma once
+#include <stdint.h>
+#include <stddef.h>
+#include "../../include/easyav1_cuda.h"
+
+#if defined(__CUDACC__)
+#define EAV1_DEV __device__ __forceinline__
+#define EAV1_DEVN __device__ __noinline__
+#define CTA_SYNC() __syncthreads()
+#define EAV1_LDG(p) __ldg(p)
+#else
+#define EAV1_DEV static inline
+#define EAV1_DEVN static
+#define CTA_SYNC() ((void)0)
+#define EAV1_LDG(p) (*(p))
+#endif
+
+namespace eav1 {
+
+struct Plane {
+    uint8_t *p;   // base pointer (bytes)
+    int stride;   // bytes
+    int w, h;     // allocated (padded) size in pixels
+};
+
+struct FrameCtx {
+    Plane cur[3];
+    Plane ref[8][3];          // [7] aliases cur (intrabc)
+    int bitdepth_max;
+    int ss_hor, ss_ver;
+    uint8_t *arena;           // per-frame scratch (prep blocks, lap, masks, ...)
+    const uint8_t *payload;   // per-frame coefficients / palettes
+    const Eav1Tables *tab;
+    const uint8_t *masks;     // wedge / inter-intra mask blob
+};
+
+// Per-CTA shared scratch: the 64x64 int32 transform tile (odd pitch), or the MC
+// intermediate rows, or the intra edge/ac buffers -- never live at the same time.
+struct alignas(16) CtaScratch {
+    union {
+        int32_t itx[64 * 65];
+        int16_t mc_mid[(32 + 7) * 128];
+        struct {
+            uint16_t edge[288];      // intra edge array, top-left sample at [EDGE_C]
+            uint16_t edge2[288];     // filtered / upsampled edge
+            int16_t  ac[32 * 32];    // cfl ac
+            int32_t  red[256];       // CTA reduction scratch
+        } ip;
+    };
+};
+
+EAV1_DEV int iclip(int v, int lo, int hi) { return v < lo ? lo : v > hi ? hi : v; }
+EAV1_DEV int imin(int a, int b) { return a < b ? a : b; }
+EAV1_DEV int imax(int a, int b) { return a > b ? a : b; }
+EAV1_DEV int iabs(int a) { return a < 0 ? -a : a; }
+EAV1_DEV int apply_sign(int v, int s) { return s < 0 ? -v : v; }
+EAV1_DEV int ctz32(unsigned v) {
+#if defined(__CUDA_ARCH__)
+    return __ffs(v) - 1;
+#else
+    return __builtin_ctz(v);
+#endif
+}
+EAV1_DEV int clz32(unsigned v) {
+#if defined(__CUDA_ARCH__)
+    return __clz(v);
+#else
+    return __builtin_clz(v);
+#endif
+}
+EAV1_DEV int ulog2(unsigned v) { return 31 - clz32(v); }
+
+// Bit-depth traits: pixel / coefficient types and the multiply width the inverse
+// transforms need (see itx.cuh).
+struct BD8 {
+    typedef uint8_t pixel;
+    typedef int16_t coef;
+    typedef int32_t wide;
+    static constexpr bool hbd = false;
+};
+struct BD16 {
+    typedef uint16_t pixel;
+    typedef int32_t coef;
+    typedef int64_t wide;
+    static constexpr bool hbd = true;
+};
+
+template <typename pixel>
+EAV1_DEV pixel *px_at(const Plane &pl, int x, int y) {
+    return reinterpret_cast<pixel *>(pl.p + (ptrdiff_t)y * pl.stride) + x;
+}
+
+} // namespace eav1

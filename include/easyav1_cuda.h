@@ -1,0 +1,230 @@
+/*
+ * easyav1_cuda.h — C ABI of libeasyav1_cuda.so, the B200 (sm_100a) AV1 reconstruction engine.
+ *
+ * Plain pointers and sizes only (no torch / C++ types). This is the boundary "B5" of
+ * SURVEY.md §8(b); it is what the dav1d host side (entropy decode + block walk, kept in C)
+ * binds instead of dav1d's per-bitdepth DSP objects:
+ *
+ *   reference interface replaced                         entry point here
+ *   ---------------------------------------------------  ---------------------------------
+ *   Dav1dDSPContext tables, ext/dav1d/src/internal.h:62   eav1cu_frame_submit (recorded DSP
+ *     itx.itxfm_add  (src/itx.h:37-72)                      commands, struct Eav1Cmd below:
+ *     mc.*           (src/mc.h:38-162)                      one record per DSP call the host
+ *     ipred.*        (src/ipred.h:43-90) + prepare_intra_   walk would have made)
+ *       edges (src/ipred_prepare.h:80-92)
+ *   f->bd_fn.filter_sbrow* (src/recon.h:57-69;            eav1cu_frame_submit post-filter
+ *     lf_apply_tmpl.c:313-466, cdef_apply_tmpl.c:97,        stage (Eav1FrameDesc.lf/cdef/lr
+ *     lr_apply_tmpl.c:168)                                  side data, whole frame)
+ *   dav1d_apply_grain_{8,16}bpc (src/fg_apply.h)          eav1cu_apply_grain
+ *   Dav1dPicAllocator (include/dav1d/picture.h:133-145)   eav1cu_pic_alloc / _release / _download
+ *   mdct_backward + vorbis_synthesis_blockin              eav1cu_vorbis_imdct_ola
+ *     (ext/minivorbis/minivorbis.h:7054, 9195)
+ *   operator-level (per call) forms used by parity tests  eav1cu_op_* (one launch per call)
+ *
+ * Every function returns 0 on success or a negative EAV1CU_ERR_* code; CUDA errors are
+ * latched in the context (eav1cu_last_error) because the DSP surface it replaces is void.
+ * There is NO CPU fallback: without a CUDA device every entry point fails with
+ * EAV1CU_ERR_NO_DEVICE.
+ */
+#ifndef EASYAV1_CUDA_H
+#define EASYAV1_CUDA_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define EAV1CU_ERR_NO_DEVICE (-1)
+#define EAV1CU_ERR_CUDA      (-2)
+#define EAV1CU_ERR_INVAL     (-3)
+#define EAV1CU_ERR_NOMEM     (-4)
+#define EAV1CU_ERR_NOTABLES  (-5)
+
+typedef struct Eav1cuCtx Eav1cuCtx;
+
+/* ---- constant tables (values come from ext/dav1d/src/tables.c and wedge.c; the host
+ * side uploads its own copies once, the engine never regenerates them) ---------------- */
+typedef struct Eav1Tables {
+    int8_t   mc_subpel_filters[6][15][8]; /* tables.c:445 */
+    int8_t   mc_warp_filter[193][8];      /* tables.c:550 */
+    int8_t   resize_filter[64][8];        /* tables.c:655 */
+    uint8_t  sm_weights[128];             /* tables.c:690 */
+    uint16_t dr_intra_derivative[44];     /* tables.c:719 */
+    int8_t   filter_intra_taps[5][8][8];  /* tables.c:765, canonical [filter][pixel yy*4+xx][tap p0..p6] */
+    uint8_t  obmc_masks[64];              /* tables.c:814 */
+    int16_t  gaussian_sequence[2048];     /* tables.c:832 */
+    uint8_t  sgr_x_by_x[256];             /* tables.c:423 */
+    int8_t   cdef_directions[12][2];      /* tables.c:400, rows 2+dir-2 .. 2+dir+2, in units of a 12-px stride */
+    uint16_t sgr_params[16][2];           /* tables.c:415 */
+} Eav1Tables;
+
+/* ---- recorded reconstruction commands ---------------------------------------------- */
+enum Eav1Op {
+    EAV1_OP_NOP = 0,
+    EAV1_OP_MC,      /* mc.mc / mc.mct / mc_scaled / mct_scaled (emu_edge folded into clamping) */
+    EAV1_OP_WARP,    /* mc.warp8x8 / warp8x8t */
+    EAV1_OP_AVG,     /* mc.avg */
+    EAV1_OP_W_AVG,   /* mc.w_avg */
+    EAV1_OP_MASK,    /* mc.mask */
+    EAV1_OP_W_MASK,  /* mc.w_mask[ss] */
+    EAV1_OP_BLEND,   /* mc.blend */
+    EAV1_OP_BLEND_V, /* mc.blend_v */
+    EAV1_OP_BLEND_H, /* mc.blend_h */
+    EAV1_OP_IPRED,   /* prepare_intra_edges + ipred.intra_pred[m] */
+    EAV1_OP_CFL,     /* ipred.cfl_ac + prepare_intra_edges + ipred.cfl_pred[m] */
+    EAV1_OP_PAL,     /* ipred.pal_pred */
+    EAV1_OP_ITX,     /* itx.itxfm_add[tx][txtp] */
+    EAV1_N_OPS
+};
+
+/* Eav1Cmd.flags */
+#define EAV1_F_DST_ARENA  1  /* destination is the per-frame scratch arena (dst_off, dst_stride) */
+#define EAV1_F_PREP       2  /* MC/WARP: int16 "prep" output instead of pixels */
+#define EAV1_F_BLOCK_HEAD 4  /* first command of a coding block (= scheduling unit) */
+#define EAV1_F_MASK_ARENA 8  /* MASK/BLEND: mask lives in the arena (w_mask output), else in the mask table blob */
+
+/* mask_off for table masks indexes the blob passed to eav1cu_set_masks (wedge + ii masks). */
+
+typedef struct Eav1Cmd {
+    uint8_t  op, plane, w, h;   /* w,h in pixels, 1..128 */
+    int16_t  x, y;              /* destination position in the plane (pixels) when !DST_ARENA */
+    uint32_t dst_off;           /* arena byte offset when DST_ARENA */
+    uint16_t dst_stride;        /* arena stride in elements when DST_ARENA */
+    uint8_t  flags, pad0;
+    union {
+        struct {                /* EAV1_OP_MC */
+            int32_t  sx, sy;    /* integer source position of the block's (0,0) sample (may be out of frame) */
+            int32_t  iw, ih;    /* source plane clamp bounds (emu_edge iw, ih) */
+            uint16_t mx, my;    /* 1/16 subpel (0..15), or 1/1024 fraction for scaled */
+            uint16_t dx, dy;    /* scaled step (0 = unscaled) */
+            uint8_t  ref;       /* 0..6 reference slot, 7 = current frame (intrabc) */
+            uint8_t  filt_h, filt_v; /* 0 regular,1 smooth,2 sharp (8-tap) ; 3 = bilinear */
+            uint8_t  pad;
+        } mc;
+        struct {                /* EAV1_OP_WARP (8x8) */
+            int32_t  sx, sy, iw, ih;
+            int32_t  mx, my;
+            int16_t  abcd[4];
+            uint8_t  ref, pad[3];
+        } warp;
+        struct {                /* AVG / W_AVG / MASK / W_MASK */
+            uint32_t t1, t2;    /* arena byte offsets of the two int16 prep blocks (stride = w) */
+            uint32_t mask_off;  /* MASK: mask source; W_MASK: arena offset the mask is written to */
+            int16_t  weight;    /* W_AVG */
+            uint8_t  sign;      /* W_MASK */
+            uint8_t  ss_hor, ss_ver; /* W_MASK mask subsampling */
+        } comp;
+        struct {                /* BLEND / BLEND_V / BLEND_H */
+            uint32_t tmp_off;   /* arena byte offset of the pixel tmp block (stride = w) */
+            uint32_t mask_off;  /* BLEND: table-blob offset of the ii mask (stride = w) */
+        } blend;
+        struct {                /* IPRED and the edge part of CFL */
+            int16_t  ex, ey;    /* position (pixels, in `plane` of the CURRENT frame) whose neighbours form the edge */
+            int16_t  angle;     /* final angle | flags as passed to intra_pred (or filter idx) */
+            uint8_t  mode;      /* final implementation mode (after prepare_intra_edges) */
+            uint8_t  have;      /* bit0 have_left, bit1 have_top, bit2 z2 corner filter */
+            uint8_t  n_left, n_bl, n_top, n_tr; /* available px counts; 255 = "not needed"; n_bl/n_tr 0 = replicate */
+            uint8_t  tw, th;    /* edge sizes in 4px units */
+            int16_t  max_w, max_h; /* clamped to 16383 */
+            /* CFL extras */
+            int16_t  lx, ly;    /* luma position for cfl_ac */
+            int8_t   alpha;
+            uint8_t  w_pad, h_pad;
+            uint8_t  pad;
+        } ipred;
+        struct {                /* PAL */
+            uint32_t pal_off;   /* payload byte offset: 8 pixels */
+            uint32_t idx_off;   /* payload byte offset: w*h/2 packed indices */
+        } pal;
+        struct {                /* ITX */
+            uint32_t cf_off;    /* payload byte offset of min(w,32)*min(h,32) coefs, column-major */
+            int16_t  eob;
+            uint8_t  tx, txtp;  /* enum RectTxfmSize, enum TxfmType (table index as used by itxfm_add[tx][txtp]) */
+        } itx;
+        uint8_t raw[44];
+    } u;
+} Eav1Cmd; /* 60 bytes */
+
+/* ---- post-filter side data ------------------------------------------------------------
+ * Deblocking and loop restoration are recorded at the DSP-call level as well: the host's
+ * sbrow drivers (lf_apply_tmpl.c:313-466, lr_apply_tmpl.c:107-202) run unchanged against a
+ * recording Dav1dLoopFilterDSPContext / Dav1dLoopRestorationDSPContext, so tile-edge mask
+ * fix-ups, frame-edge skipping and restoration-unit geometry arrive already resolved.
+ * CDEF needs pixel-derived decisions (direction, variance) and is driven entirely on the
+ * device from dav1d's Av1Filter array (cdef_idx, noskip_mask). */
+typedef struct Eav1LfRec {      /* one lf.loop_filter_sb[plane>0][dir] call (loopfilter.h:39-43) */
+    uint16_t x, y;              /* pixel position of `dst` in the plane */
+    uint8_t  plane, dir;        /* dir: 0 = column edges (filter across x), 1 = row edges */
+    uint16_t pad;
+    uint32_t vmask[3];          /* which 4px units have an edge, by filter size class */
+    uint32_t lvl_off;           /* byte offset of `lvl` inside the uploaded level array */
+} Eav1LfRec;                    /* 24 bytes */
+
+enum { EAV1_LR_WIENER7 = 0, EAV1_LR_WIENER5, EAV1_LR_SGR_5X5, EAV1_LR_SGR_3X3, EAV1_LR_SGR_MIX };
+typedef struct Eav1LrRec {      /* one lr.wiener[]/lr.sgr[] call (looprestoration.h:64-70) */
+    uint16_t x, y, w, h;        /* unit position/size in the plane; h = stripe height */
+    uint8_t  plane, edges, kind, pad;
+    union {
+        int16_t filter[2][8];   /* Wiener taps as in LooprestorationParams.filter */
+        struct { uint32_t s0, s1; int16_t w0, w1; } sgr;
+    } p;
+} Eav1LrRec;                    /* 44 bytes */
+
+typedef struct Eav1FrameDesc {
+    int w, h;                 /* visible frame size (luma) */
+    int bpc;                  /* 8, 10, 12 */
+    int layout;               /* Dav1dPixelLayout: 0=I400 1=I420 2=I422 3=I444 */
+    int bw4, bh4;             /* frame size in 4x4 units (f->bw, f->bh) */
+    int sb128;                /* seq_hdr->sb128 */
+    int cur;                  /* picture id being reconstructed (receives the final frame) */
+    int ref[7];               /* picture ids of the 7 references (-1 = none) */
+    /* deblock */
+    const Eav1LfRec *lf_recs; size_t n_lf_recs;
+    const uint8_t *lf_level;  size_t lf_level_bytes; /* copy of f->lf.level */
+    int b4_stride;
+    uint8_t lut_e[64], lut_i[64];  /* Av1FilterLUT.e / .i (lf_mask.h:60-65) */
+    /* cdef */
+    int cdef_enable;
+    int cdef_damping;
+    uint8_t cdef_y_strength[8], cdef_uv_strength[8];
+    const void *lf_mask;      /* Av1Filter[sb128h][sb128w] (1348 bytes each, lf_mask.h:51-58) */
+    int sb128w, sb128h;
+    /* loop restoration */
+    const Eav1LrRec *lr_recs; size_t n_lr_recs;
+} Eav1FrameDesc;
+
+/* ---- lifecycle ------------------------------------------------------------------------ */
+int  eav1cu_device_count(void);
+int  eav1cu_ctx_create(Eav1cuCtx **out, int device);
+void eav1cu_ctx_destroy(Eav1cuCtx *ctx);
+int  eav1cu_last_error(Eav1cuCtx *ctx, char *msg, size_t cap);
+int  eav1cu_set_tables(Eav1cuCtx *ctx, const Eav1Tables *t);
+int  eav1cu_set_masks(Eav1cuCtx *ctx, const uint8_t *blob, size_t bytes);
+int  eav1cu_sync(Eav1cuCtx *ctx);
+
+/* ---- pictures (device-resident reference pool) ---------------------------------------- */
+int  eav1cu_pic_alloc(Eav1cuCtx *ctx, int w, int h, int layout, int bpc);           /* returns id >= 0 */
+int  eav1cu_pic_release(Eav1cuCtx *ctx, int id);
+int  eav1cu_pic_upload(Eav1cuCtx *ctx, int id, const void *const data[3], const ptrdiff_t stride[2]);
+int  eav1cu_pic_download(Eav1cuCtx *ctx, int id, void *const data[3], const ptrdiff_t stride[2]);
+
+/* ---- frame reconstruction --------------------------------------------------------------- */
+/* Reconstruct one frame from its recorded commands (in host walk order) and run the in-loop
+ * post filters; the result stays resident as picture fd->cur. Asynchronous on the context's
+ * stream; eav1cu_pic_download / eav1cu_sync order after it. */
+int  eav1cu_frame_submit(Eav1cuCtx *ctx, const Eav1FrameDesc *fd,
+                         const Eav1Cmd *cmds, size_t n_cmds,
+                         const void *payload, size_t payload_bytes, size_t arena_bytes);
+
+/* Scratch arena access (prep blocks / masks), for operator-level parity tests. */
+int  eav1cu_arena_upload(Eav1cuCtx *ctx, size_t off, const void *src, size_t bytes);
+int  eav1cu_arena_download(Eav1cuCtx *ctx, size_t off, void *dst, size_t bytes);
+/* Number of kernel launches issued so far by this context (bench.py's gpu_launches). */
+long long eav1cu_launch_count(Eav1cuCtx *ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* EASYAV1_CUDA_H */

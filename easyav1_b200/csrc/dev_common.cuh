@@ -13,11 +13,13 @@
 #if defined(__CUDACC__)
 #define EAV1_DEV __device__ __forceinline__
 #define EAV1_DEVN __device__ __noinline__
+#define EAV1_DEVM __device__ __forceinline__
 #define CTA_SYNC() __syncthreads()
 #define EAV1_LDG(p) __ldg(p)
 #else
 #define EAV1_DEV static inline
 #define EAV1_DEVN static
+#define EAV1_DEVM inline
 #define CTA_SYNC() ((void)0)
 #define EAV1_LDG(p) (*(p))
 #endif

@@ -183,6 +183,14 @@ int eav1cu_last_error(Eav1cuCtx *ctx, char *msg, size_t cap)
     return ctx->err;
 }
 
+int eav1cu_host_alloc(void **p, size_t bytes)
+{
+    if (!p) return EAV1CU_ERR_INVAL;
+    return cudaHostAlloc(p, bytes, cudaHostAllocPortable) == cudaSuccess ? 0 : EAV1CU_ERR_NOMEM;
+}
+
+void eav1cu_host_free(void *p) { if (p) cudaFreeHost(p); }
+
 long long eav1cu_launch_count(Eav1cuCtx *ctx) { return ctx ? ctx->n_launches : 0; }
 
 int eav1cu_set_tables(Eav1cuCtx *ctx, const Eav1Tables *t)

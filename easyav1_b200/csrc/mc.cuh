@@ -14,7 +14,7 @@ namespace eav1 {
 template <typename pixel>
 struct SrcView {
     const uint8_t *p; int stride; int iw, ih;
-    EAV1_DEV int at(int x, int y) const {
+    EAV1_DEVM int at(int x, int y) const {
         x = iclip(x, 0, iw - 1); y = iclip(y, 0, ih - 1);
         return reinterpret_cast<const pixel *>(p + (ptrdiff_t)y * stride)[x];
     }

@@ -1,0 +1,62 @@
+"""ctypes loaders for the two in-tree shared libraries (built by __graft_entry__.build())."""
+import ctypes as C
+import os
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ENGINE_SO = os.path.join(HERE, "libeasyav1_cuda.so")
+HOST_SO = os.path.join(HERE, "libdav1d_b200.so")
+
+
+class EngineError(RuntimeError):
+    pass
+
+
+_engine = None
+_host = None
+
+
+def load_engine():
+    """libeasyav1_cuda.so (include/easyav1_cuda.h). Raises if it is missing: no fallback."""
+    global _engine
+    if _engine is None:
+        if not os.path.exists(ENGINE_SO):
+            raise EngineError("libeasyav1_cuda.so is not built (run __graft_entry__.build()); "
+                              "there is no CPU fallback")
+        _engine = C.CDLL(ENGINE_SO, mode=C.RTLD_GLOBAL)
+        _engine.eav1cu_launch_count.restype = C.c_longlong
+    return _engine
+
+
+def load_host(path=None):
+    """libdav1d_b200.so: dav1d public API + eav1_stream_* helpers, bound to the CUDA engine."""
+    global _host
+    if path is not None:
+        return _bind_host(C.CDLL(path, mode=C.RTLD_GLOBAL))
+    if _host is None:
+        load_engine()
+        if not os.path.exists(HOST_SO):
+            raise EngineError("libdav1d_b200.so is not built (run __graft_entry__.build())")
+        _host = _bind_host(C.CDLL(HOST_SO, mode=C.RTLD_GLOBAL))
+    return _host
+
+
+class StreamFrame(C.Structure):
+    _fields_ = [("w", C.c_int), ("h", C.c_int), ("layout", C.c_int), ("bpc", C.c_int),
+                ("frame_type", C.c_int), ("show_frame", C.c_int), ("showable", C.c_int),
+                ("offset", C.c_int64)]
+
+
+def _bind_host(L):
+    L.eav1_stream_open.restype = C.c_void_p
+    L.eav1_stream_open.argtypes = [C.c_char_p, C.c_size_t, C.c_int, C.c_int, C.c_int]
+    L.eav1_stream_next.argtypes = [C.c_void_p, C.POINTER(StreamFrame), C.c_void_p, C.c_size_t,
+                                   C.POINTER(C.c_size_t)]
+    L.eav1_stream_close.argtypes = [C.c_void_p]
+    L.eav1_stream_ctx.restype = C.c_void_p
+    L.eav1_stream_ctx.argtypes = [C.c_void_p]
+    L.eav1rec_frames_submitted.restype = C.c_longlong
+    L.eav1rec_frames_submitted.argtypes = [C.c_void_p]
+    L.eav1rec_launches.restype = C.c_longlong
+    L.eav1rec_launches.argtypes = [C.c_void_p]
+    L.eav1rec_error.argtypes = [C.c_void_p]
+    return L

@@ -19,7 +19,6 @@
  *   Dav1dPicAllocator (include/dav1d/picture.h:133-145)   eav1cu_pic_alloc / _release / _download
  *   mdct_backward + vorbis_synthesis_blockin              eav1cu_vorbis_imdct_ola
  *     (ext/minivorbis/minivorbis.h:7054, 9195)
- *   operator-level (per call) forms used by parity tests  eav1cu_op_* (one launch per call)
  *
  * Every function returns 0 on success or a negative EAV1CU_ERR_* code; CUDA errors are
  * latched in the context (eav1cu_last_error) because the DSP surface it replaces is void.
@@ -209,6 +208,10 @@ int  eav1cu_pic_alloc(Eav1cuCtx *ctx, int w, int h, int layout, int bpc);       
 int  eav1cu_pic_release(Eav1cuCtx *ctx, int id);
 int  eav1cu_pic_upload(Eav1cuCtx *ctx, int id, const void *const data[3], const ptrdiff_t stride[2]);
 int  eav1cu_pic_download(Eav1cuCtx *ctx, int id, void *const data[3], const ptrdiff_t stride[2]);
+
+/* Pinned host memory for output pictures (backs the Dav1dPicAllocator replacement). */
+int  eav1cu_host_alloc(void **p, size_t bytes);
+void eav1cu_host_free(void *p);
 
 /* ---- frame reconstruction --------------------------------------------------------------- */
 /* Reconstruct one frame from its recorded commands (in host walk order) and run the in-loop

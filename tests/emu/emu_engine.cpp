@@ -1,0 +1,130 @@
+// tests/emu/emu_engine.cpp — DEBUGGING AID, TEST INFRASTRUCTURE ONLY.
+//
+// Compiles the device code of easyav1_b200/csrc/*.cuh for the host (one "thread" per CTA,
+// commands executed strictly in recorded order) behind the same eav1cu_* C ABI, so the
+// arithmetic of the kernels and the host-side recorder can be diffed against the reference
+// decoder in the build container, which has no GPU. It is never built into, loaded by or
+// shipped with the product: easyav1_b200 only ever loads libeasyav1_cuda.so and fails
+// loudly without a CUDA device.
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <vector>
+#include <string>
+
+#include "../../include/easyav1_cuda.h"
+#include "../../easyav1_b200/csrc/dev_common.cuh"
+#include "../../easyav1_b200/csrc/exec.cuh"
+#include "../../easyav1_b200/csrc/postfilter.cuh"
+
+using namespace eav1;
+
+struct Picture {
+    bool used = false;
+    int w = 0, h = 0, layout = 0, bpc = 0;
+    std::vector<uint8_t> mem;
+    Plane pl[3];
+};
+
+struct Eav1cuCtx {
+    Eav1Tables tab;
+    bool have_tab = false;
+    std::vector<uint8_t> masks;
+    std::vector<Picture> pics;
+    std::vector<uint8_t> arena;
+    Picture work[2];
+    long long launches = 0;
+    int err = 0;
+};
+
+static void pic_setup(Picture &p, int w, int h, int layout, int bpc)
+{
+    const int hbd = bpc > 8;
+    const int ss_hor = layout != 3, ss_ver = layout == 1;
+    const int aw = (w + 127) & ~127, ah = (h + 127) & ~127;
+    const int cw = layout ? aw >> ss_hor : 0, chh = layout ? ah >> ss_ver : 0;
+    const size_t ystride = (size_t)aw << hbd, cstride = (size_t)cw << hbd;
+    const size_t ybytes = ystride * ah, cbytes = cstride * chh;
+    p.mem.assign(ybytes + 2 * cbytes + 256, 0);
+    p.w = w; p.h = h; p.layout = layout; p.bpc = bpc;
+    uint8_t *b = p.mem.data();
+    p.pl[0] = { b, (int)ystride, aw, ah };
+    p.pl[1] = { b + ybytes, (int)cstride, cw, chh };
+    p.pl[2] = { b + ybytes + cbytes, (int)cstride, cw, chh };
+}
+
+#include "emu_postfilter.inc"
+
+extern "C" {
+
+int eav1cu_device_count(void) { return 1; }
+int eav1cu_ctx_create(Eav1cuCtx **out, int) { *out = new Eav1cuCtx(); return 0; }
+void eav1cu_ctx_destroy(Eav1cuCtx *c) { delete c; }
+int eav1cu_last_error(Eav1cuCtx *c, char *msg, size_t cap) { if (msg && cap) msg[0] = 0; return c->err; }
+int eav1cu_set_tables(Eav1cuCtx *c, const Eav1Tables *t) { c->tab = *t; c->have_tab = true; return 0; }
+int eav1cu_set_masks(Eav1cuCtx *c, const uint8_t *b, size_t n) { c->masks.assign(b, b + n); return 0; }
+int eav1cu_sync(Eav1cuCtx *c) { return c->err; }
+int eav1cu_host_alloc(void **p, size_t n) { *p = malloc(n); return *p ? 0 : EAV1CU_ERR_NOMEM; }
+void eav1cu_host_free(void *p) { free(p); }
+long long eav1cu_launch_count(Eav1cuCtx *c) { return c->launches; }
+
+int eav1cu_pic_alloc(Eav1cuCtx *c, int w, int h, int layout, int bpc)
+{
+    int id = -1;
+    for (size_t i = 0; i < c->pics.size(); i++) if (!c->pics[i].used) { id = (int)i; break; }
+    if (id < 0) { c->pics.emplace_back(); id = (int)c->pics.size() - 1; }
+    pic_setup(c->pics[id], w, h, layout, bpc);
+    c->pics[id].used = true;
+    return id;
+}
+int eav1cu_pic_release(Eav1cuCtx *c, int id) { c->pics[id].used = false; return 0; }
+
+static int pic_copy(Eav1cuCtx *c, int id, void *const data[3], const ptrdiff_t stride[2], bool up)
+{
+    Picture &p = c->pics[id];
+    const int hbd = p.bpc > 8, ss_hor = p.layout != 3, ss_ver = p.layout == 1;
+    for (int pl = 0; pl < (p.layout ? 3 : 1); pl++) {
+        const int w = pl ? (p.w + ss_hor) >> ss_hor : p.w, h = pl ? (p.h + ss_ver) >> ss_ver : p.h;
+        for (int y = 0; y < h; y++) {
+            uint8_t *d = p.pl[pl].p + (size_t)y * p.pl[pl].stride;
+            uint8_t *s = (uint8_t *)data[pl] + (ptrdiff_t)y * stride[!!pl];
+            if (up) memcpy(d, s, (size_t)w << hbd); else memcpy(s, d, (size_t)w << hbd);
+        }
+    }
+    return 0;
+}
+int eav1cu_pic_upload(Eav1cuCtx *c, int id, const void *const data[3], const ptrdiff_t stride[2]) { return pic_copy(c, id, (void *const *)data, stride, true); }
+int eav1cu_pic_download(Eav1cuCtx *c, int id, void *const data[3], const ptrdiff_t stride[2]) { return pic_copy(c, id, data, stride, false); }
+int eav1cu_arena_upload(Eav1cuCtx *c, size_t off, const void *src, size_t n) { if (c->arena.size() < off + n) c->arena.resize(off + n); memcpy(c->arena.data() + off, src, n); return 0; }
+int eav1cu_arena_download(Eav1cuCtx *c, size_t off, void *dst, size_t n) { if (c->arena.size() < off + n) return EAV1CU_ERR_INVAL; memcpy(dst, c->arena.data() + off, n); return 0; }
+
+int eav1cu_frame_submit(Eav1cuCtx *c, const Eav1FrameDesc *fd, const Eav1Cmd *cmds, size_t n,
+                        const void *payload, size_t, size_t arena_bytes)
+{
+    if (!c->have_tab) return EAV1CU_ERR_NOTABLES;
+    Picture &cur = c->pics[fd->cur];
+    FrameCtx fc;
+    memset(&fc, 0, sizeof(fc));
+    for (int i = 0; i < 3; i++) fc.cur[i] = cur.pl[i];
+    for (int r = 0; r < 7; r++) {
+        const Picture &rp = fd->ref[r] >= 0 ? c->pics[fd->ref[r]] : cur;
+        for (int i = 0; i < 3; i++) fc.ref[r][i] = rp.pl[i];
+    }
+    for (int i = 0; i < 3; i++) fc.ref[7][i] = cur.pl[i];
+    fc.bitdepth_max = (1 << fd->bpc) - 1;
+    fc.ss_hor = fd->layout != 3; fc.ss_ver = fd->layout == 1;
+    fc.tab = &c->tab;
+    fc.masks = c->masks.data();
+    if (c->arena.size() < arena_bytes + 16) c->arena.resize(arena_bytes + 16);
+    fc.arena = c->arena.data();
+    fc.payload = (const uint8_t *)payload;
+    static CtaScratch sm;
+    for (size_t i = 0; i < n; i++) {
+        if (fd->bpc > 8) exec_cmd<BD16>(fc, cmds[i], sm, 0, 1);
+        else exec_cmd<BD8>(fc, cmds[i], sm, 0, 1);
+    }
+    c->launches++;
+    return emu_postfilter(c, fd, fc);
+}
+
+} // extern "C"

@@ -36,6 +36,38 @@ recon_level_kernel(FrameCtx fc, const Eav1Cmd *__restrict__ cmds, const Chain *_
     }
 }
 
+template <typename pixel>
+__global__ void __launch_bounds__(128)
+deblock_kernel(PfParams pp, const Eav1LfRec *__restrict__ recs, int n)
+{
+    const int gid = blockIdx.x * blockDim.x + threadIdx.x;
+    const int ri = gid >> 5;
+    if (ri >= n) return;
+    lf_unit<pixel>(pp, recs[ri], gid & 31);
+}
+
+template <typename pixel>
+__global__ void __launch_bounds__(256)
+cdef_kernel(PfParams pp)
+{
+    __shared__ CdefSmem sm[8];
+    const int g = threadIdx.x >> 5;
+    const int bx = (blockIdx.x * 8 + g) * 2, by = blockIdx.y * 2;
+    cdef_block<pixel>(pp, bx, by, bx < pp.bw4 && by < pp.bh4, sm[g], threadIdx.x & 31, 32);
+}
+
+template <typename pixel>
+__global__ void __launch_bounds__(128)
+lr_kernel(PfParams pp, const Eav1LrRec *__restrict__ recs)
+{
+    __shared__ LrSmem sm;
+    __shared__ Eav1LrRec r;
+    if (threadIdx.x < sizeof(Eav1LrRec) / 4)
+        reinterpret_cast<uint32_t *>(&r)[threadIdx.x] = reinterpret_cast<const uint32_t *>(&recs[blockIdx.y])[threadIdx.x];
+    __syncthreads();
+    lr_tile<pixel>(pp, r, blockIdx.x, sm, threadIdx.x, blockDim.x);
+}
+
 // ------------------------------------------------------------------ context
 
 struct Picture {
@@ -60,6 +92,7 @@ struct Eav1cuCtx {
     std::vector<Picture> pics;
     DevBuf cmds, chains, payload, arena, lfrec, lflvl, lrrec, lfmask;
     Picture work[2];           // post-filter ping-pong pictures
+    std::vector<Eav1LfRec> lf_sorted;
     Scheduler sched;
     Schedule plan;
     int err = 0;
@@ -300,11 +333,69 @@ int eav1cu_arena_download(Eav1cuCtx *ctx, size_t off, void *dst, size_t bytes)
 
 static void fill_planes(const Picture &p, Plane out[3]) { for (int i = 0; i < 3; i++) out[i] = p.pl[i]; }
 
-static int postfilter_run(Eav1cuCtx *ctx, const Eav1FrameDesc *fd, const FrameCtx &fc)
+
+static int postfilter_run(Eav1cuCtx *ctx, const Eav1FrameDesc *fd, Picture &A, Picture &cur)
 {
-    (void)ctx; (void)fd; (void)fc;
+    const bool hbd = fd->bpc > 8;
+    const bool has_cdef = fd->cdef_enable != 0, has_lr = fd->n_lr_recs > 0;
+    PfParams pp;
+    memset(&pp, 0, sizeof(pp));
+    pp.bitdepth_max = (1 << fd->bpc) - 1;
+    pp.layout = fd->layout; pp.ss_hor = fd->layout != 3; pp.ss_ver = fd->layout == 1;
+    pp.w = fd->w; pp.h = fd->h; pp.bw4 = fd->bw4; pp.bh4 = fd->bh4;
+    pp.b4_stride = fd->b4_stride;
+    memcpy(pp.lut_e, fd->lut_e, 64); memcpy(pp.lut_i, fd->lut_i, 64);
+    pp.sb128w = fd->sb128w; pp.cdef_damping = fd->cdef_damping;
+    memcpy(pp.cdef_y, fd->cdef_y_strength, 8); memcpy(pp.cdef_uv, fd->cdef_uv_strength, 8);
+    pp.tab = ctx->d_tab;
+    for (int i = 0; i < 3; i++) pp.a[i] = A.pl[i];
+    int r;
+    if (fd->n_lf_recs) {
+        // partition the recorded calls: all column-edge filters run before all row-edge filters
+        std::vector<Eav1LfRec> &v = ctx->lf_sorted;
+        v.resize(fd->n_lf_recs);
+        size_t n0 = 0;
+        for (size_t i = 0; i < fd->n_lf_recs; i++) if (fd->lf_recs[i].dir == 0) v[n0++] = fd->lf_recs[i];
+        size_t n1 = n0;
+        for (size_t i = 0; i < fd->n_lf_recs; i++) if (fd->lf_recs[i].dir != 0) v[n1++] = fd->lf_recs[i];
+        if ((r = upload(ctx, ctx->lfrec, v.data(), v.size() * sizeof(Eav1LfRec)))) return r;
+        if ((r = upload(ctx, ctx->lflvl, fd->lf_level, fd->lf_level_bytes))) return r;
+        pp.level = ctx->lflvl.d;
+        const Eav1LfRec *d = reinterpret_cast<const Eav1LfRec *>(ctx->lfrec.d);
+        for (int pass = 0; pass < 2; pass++) {
+            const size_t off = pass ? n0 : 0, cnt = pass ? n1 - n0 : n0;
+            if (!cnt) continue;
+            const unsigned grid = (unsigned)((cnt * 32 + 127) / 128);
+            if (hbd) deblock_kernel<uint16_t><<<grid, 128, 0, ctx->stream>>>(pp, d + off, (int)cnt);
+            else     deblock_kernel<uint8_t><<<grid, 128, 0, ctx->stream>>>(pp, d + off, (int)cnt);
+            ctx->n_launches++;
+        }
+    }
+    if (has_cdef) {
+        Picture &dst = has_lr ? ctx->work[1] : cur;
+        for (int i = 0; i < 3; i++) pp.b[i] = dst.pl[i];
+        if ((r = upload(ctx, ctx->lfmask, fd->lf_mask, (size_t)fd->sb128w * fd->sb128h * 1348))) return r;
+        pp.lfmask = ctx->lfmask.d;
+        dim3 grid((fd->bw4 / 2 + 8) / 8, (fd->bh4 + 1) / 2);
+        if (hbd) cdef_kernel<uint16_t><<<grid, 256, 0, ctx->stream>>>(pp);
+        else     cdef_kernel<uint8_t><<<grid, 256, 0, ctx->stream>>>(pp);
+        ctx->n_launches++;
+    }
+    if (has_lr) {
+        Picture &src = has_cdef ? ctx->work[1] : A;
+        for (int i = 0; i < 3; i++) { pp.b[i] = src.pl[i]; pp.p[i] = cur.pl[i]; }
+        CK(cudaMemcpyAsync(cur.base, src.base, std::min(cur.bytes, src.bytes), cudaMemcpyDeviceToDevice, ctx->stream));
+        if ((r = upload(ctx, ctx->lrrec, fd->lr_recs, fd->n_lr_recs * sizeof(Eav1LrRec)))) return r;
+        dim3 grid(384 / LR_TW, (unsigned)fd->n_lr_recs);
+        const Eav1LrRec *d = reinterpret_cast<const Eav1LrRec *>(ctx->lrrec.d);
+        if (hbd) lr_kernel<uint16_t><<<grid, 128, 0, ctx->stream>>>(pp, d);
+        else     lr_kernel<uint8_t><<<grid, 128, 0, ctx->stream>>>(pp, d);
+        ctx->n_launches++;
+    }
+    CK(cudaGetLastError());
     return 0;
 }
+
 
 
 int eav1cu_frame_submit(Eav1cuCtx *ctx, const Eav1FrameDesc *fd,
@@ -319,16 +410,25 @@ int eav1cu_frame_submit(Eav1cuCtx *ctx, const Eav1FrameDesc *fd,
     CK(cudaSetDevice(ctx->device));
     Picture &cur = ctx->pics[fd->cur];
     const bool hbd = fd->bpc > 8;
+    const bool has_cdef = fd->cdef_enable != 0, has_lr = fd->n_lr_recs > 0;
+    // recon + deblock happen in A; CDEF / LR then move the frame towards `cur` out of place
+    Picture *A = &cur;
+    if (has_cdef || has_lr) {
+        int r0 = pic_setup(ctx, ctx->work[0], cur.w, cur.h, cur.layout, cur.bpc);
+        if (r0) return r0;
+        if (has_cdef && has_lr && (r0 = pic_setup(ctx, ctx->work[1], cur.w, cur.h, cur.layout, cur.bpc))) return r0;
+        A = &ctx->work[0];
+    }
 
     FrameCtx fc;
     memset(&fc, 0, sizeof(fc));
-    fill_planes(cur, fc.cur);
+    fill_planes(*A, fc.cur);
     for (int r = 0; r < 7; r++) {
         const int id = fd->ref[r];
         if (id >= 0 && id < (int)ctx->pics.size() && ctx->pics[id].base) fill_planes(ctx->pics[id], fc.ref[r]);
-        else fill_planes(cur, fc.ref[r]);
+        else fill_planes(*A, fc.ref[r]);
     }
-    fill_planes(cur, fc.ref[7]);
+    fill_planes(*A, fc.ref[7]);
     fc.bitdepth_max = (1 << fd->bpc) - 1;
     fc.ss_hor = fd->layout != 3;
     fc.ss_ver = fd->layout == 1;
@@ -336,8 +436,8 @@ int eav1cu_frame_submit(Eav1cuCtx *ctx, const Eav1FrameDesc *fd,
     fc.masks = ctx->d_masks;
 
     if (n_cmds) {
-        int pw[3] = { cur.pl[0].w, cur.pl[1].w, cur.pl[2].w };
-        int ph[3] = { cur.pl[0].h, cur.pl[1].h, cur.pl[2].h };
+        int pw[3] = { A->pl[0].w, A->pl[1].w, A->pl[2].w };
+        int ph[3] = { A->pl[0].h, A->pl[1].h, A->pl[2].h };
         ctx->sched.reset(pw, ph);
         ctx->sched.build(cmds, n_cmds, ctx->plan);
         int r;
@@ -358,7 +458,7 @@ int eav1cu_frame_submit(Eav1cuCtx *ctx, const Eav1FrameDesc *fd,
         }
         CK(cudaGetLastError());
     }
-    int r = postfilter_run(ctx, fd, fc);
+    int r = postfilter_run(ctx, fd, *A, cur);
     if (r) return r;
     return ctx->err;
 }

@@ -1,5 +1,501 @@
-// postfilter.cuh — whole-frame in-loop filter kernels (deblock, CDEF, loop restoration).
+// postfilter.cuh — whole-frame in-loop filters: deblocking (K4/D3), CDEF (K5/D5) and loop
+// restoration (K6/D6) of SURVEY.md §8a, as device code shared by the kernels in engine.cu.
+//
+// Unlike the reference, which filters in place superblock row by superblock row and therefore
+// needs line/column backups (cdef_line, lr_lpf_line, lr_bak, pre_lr_border), every stage here
+// reads one resident frame and writes another:
+//     recon+deblock -> A        CDEF: A -> B        LR: (B, stripe borders from A) -> P
+// so each output sample only ever sees the pre-stage samples the specification prescribes.
 #pragma once
 #include "dev_common.cuh"
+
 namespace eav1 {
+
+struct PfParams {
+    Plane a[3];              // deblocked frame (CDEF input, LR stripe-border rows)
+    Plane b[3];              // CDEF output / LR input
+    Plane p[3];              // final picture
+    int bitdepth_max;
+    int ss_hor, ss_ver, layout;
+    int w, h;                // visible luma size
+    int bw4, bh4;
+    // deblock
+    const uint8_t *level;    // copy of f->lf.level
+    int b4_stride;
+    uint8_t lut_e[64], lut_i[64];
+    // cdef
+    const uint8_t *lfmask;   // Av1Filter array (1348 bytes each)
+    int sb128w;
+    int cdef_damping;
+    uint8_t cdef_y[8], cdef_uv[8];
+    const Eav1Tables *tab;
+};
+
+// ------------------------------------------------------------------------------- deblock
+// Behaviour: loop_filter() ext/dav1d/src/loopfilter_tmpl.c:38-170 and the four sb128 wrappers
+// :172-246. One thread filters the four lines of one 4-sample edge unit.
+template <typename pixel>
+EAV1_DEV void lf_edge4(pixel *dst, int E, int I, int H, ptrdiff_t stridea, ptrdiff_t strideb, int wd, int bitdepth_max)
+{
+    const int bd8 = (32 - clz32((unsigned)bitdepth_max)) - 8;
+    const int F = 1 << bd8;
+    E <<= bd8; I <<= bd8; H <<= bd8;
+    const int dmin = -128 * (1 << bd8), dmax = 128 * (1 << bd8) - 1;
+    for (int i = 0; i < 4; i++, dst += stridea) {
+        const int p1 = dst[strideb * -2], p0 = dst[strideb * -1];
+        const int q0 = dst[0], q1 = dst[strideb];
+        int p2 = 0, p3 = 0, q2 = 0, q3 = 0;
+        bool fm = iabs(p1 - p0) <= I && iabs(q1 - q0) <= I && iabs(p0 - q0) * 2 + (iabs(p1 - q1) >> 1) <= E;
+        if (wd > 4) {
+            p2 = dst[strideb * -3]; q2 = dst[strideb * 2];
+            fm = fm && iabs(p2 - p1) <= I && iabs(q2 - q1) <= I;
+            if (wd > 6) {
+                p3 = dst[strideb * -4]; q3 = dst[strideb * 3];
+                fm = fm && iabs(p3 - p2) <= I && iabs(q3 - q2) <= I;
+            }
+        }
+        if (!fm) continue;
+        bool flat8out = false, flat8in = false;
+        int p6 = 0, p5 = 0, p4 = 0, q4 = 0, q5 = 0, q6 = 0;
+        if (wd >= 16) {
+            p6 = dst[strideb * -7]; p5 = dst[strideb * -6]; p4 = dst[strideb * -5];
+            q4 = dst[strideb * 4]; q5 = dst[strideb * 5]; q6 = dst[strideb * 6];
+            flat8out = iabs(p6 - p0) <= F && iabs(p5 - p0) <= F && iabs(p4 - p0) <= F &&
+                       iabs(q4 - q0) <= F && iabs(q5 - q0) <= F && iabs(q6 - q0) <= F;
+        }
+        if (wd >= 6)
+            flat8in = iabs(p2 - p0) <= F && iabs(p1 - p0) <= F && iabs(q1 - q0) <= F && iabs(q2 - q0) <= F;
+        if (wd >= 8)
+            flat8in = flat8in && iabs(p3 - p0) <= F && iabs(q3 - q0) <= F;
+        if (wd >= 16 && flat8out && flat8in) {
+            // 13-tap: out[k] = (sum of a sliding 13-sample window with edge replication, centre x2 ... ) >> 4
+            const int v[14] = { p6, p5, p4, p3, p2, p1, p0, q0, q1, q2, q3, q4, q5, q6 };
+            int out[12];
+            for (int k = 0; k < 12; k++) {
+                // output sample v[k+1]; taps span v[k+1-6 .. k+1+6] clamped, plus centre and its
+                // two neighbours once more (weights 1..1,2,2,2,1..1 collapse to this form)
+                int s = 8;
+                for (int t = -6; t <= 6; t++) s += v[iclip(k + 1 + t, 0, 13)];
+                s += v[k + 1] + v[iclip(k, 0, 13)] + v[iclip(k + 2, 0, 13)];
+                out[k] = s >> 4;
+            }
+            for (int k = 0; k < 12; k++) dst[strideb * (k - 6)] = (pixel)out[k];
+        } else if (wd >= 8 && flat8in) {
+            dst[strideb * -3] = (pixel)((p3 + p3 + p3 + 2 * p2 + p1 + p0 + q0 + 4) >> 3);
+            dst[strideb * -2] = (pixel)((p3 + p3 + p2 + 2 * p1 + p0 + q0 + q1 + 4) >> 3);
+            dst[strideb * -1] = (pixel)((p3 + p2 + p1 + 2 * p0 + q0 + q1 + q2 + 4) >> 3);
+            dst[0]            = (pixel)((p2 + p1 + p0 + 2 * q0 + q1 + q2 + q3 + 4) >> 3);
+            dst[strideb * 1]  = (pixel)((p1 + p0 + q0 + 2 * q1 + q2 + q3 + q3 + 4) >> 3);
+            dst[strideb * 2]  = (pixel)((p0 + q0 + q1 + 2 * q2 + q3 + q3 + q3 + 4) >> 3);
+        } else if (wd == 6 && flat8in) {
+            dst[strideb * -2] = (pixel)((p2 + 2 * p2 + 2 * p1 + 2 * p0 + q0 + 4) >> 3);
+            dst[strideb * -1] = (pixel)((p2 + 2 * p1 + 2 * p0 + 2 * q0 + q1 + 4) >> 3);
+            dst[0]            = (pixel)((p1 + 2 * p0 + 2 * q0 + 2 * q1 + q2 + 4) >> 3);
+            dst[strideb * 1]  = (pixel)((p0 + 2 * q0 + 2 * q1 + 2 * q2 + q2 + 4) >> 3);
+        } else {
+            const bool hev = iabs(p1 - p0) > H || iabs(q1 - q0) > H;
+            if (hev) {
+                int f = iclip(p1 - q1, dmin, dmax);
+                f = iclip(3 * (q0 - p0) + f, dmin, dmax);
+                const int f1 = imin(f + 4, dmax) >> 3, f2 = imin(f + 3, dmax) >> 3;
+                dst[strideb * -1] = (pixel)iclip(p0 + f2, 0, bitdepth_max);
+                dst[0] = (pixel)iclip(q0 - f1, 0, bitdepth_max);
+            } else {
+                int f = iclip(3 * (q0 - p0), dmin, dmax);
+                const int f1 = imin(f + 4, dmax) >> 3, f2 = imin(f + 3, dmax) >> 3;
+                dst[strideb * -1] = (pixel)iclip(p0 + f2, 0, bitdepth_max);
+                dst[0] = (pixel)iclip(q0 - f1, 0, bitdepth_max);
+                f = (f1 + 1) >> 1;
+                dst[strideb * -2] = (pixel)iclip(p1 + f, 0, bitdepth_max);
+                dst[strideb * 1] = (pixel)iclip(q1 - f, 0, bitdepth_max);
+            }
+        }
+    }
+}
+
+// One 4-sample edge unit `u` (0..31) of one recorded loop_filter_sb call.
+template <typename pixel>
+EAV1_DEV void lf_unit(const PfParams &pp, const Eav1LfRec &r, int u)
+{
+    const uint32_t bit = 1u << u;
+    const uint32_t any = r.vmask[0] | r.vmask[1] | r.vmask[2];
+    if (!(any & bit)) return;
+    const Plane &pl = pp.a[r.plane];
+    const ptrdiff_t stride = pl.stride / (ptrdiff_t)sizeof(pixel);
+    const uint8_t *l = pp.level + r.lvl_off + (r.dir ? (size_t)u * 4 : (size_t)u * pp.b4_stride * 4);
+    int L = l[0];
+    if (!L) L = r.dir ? *(l - (ptrdiff_t)pp.b4_stride * 4) : *(l - 4);
+    if (!L) return;
+    const int H = L >> 4, E = pp.lut_e[L], I = pp.lut_i[L];
+    int wd;
+    if (r.plane == 0) wd = 4 << ((r.vmask[2] & bit) ? 2 : (r.vmask[1] & bit) ? 1 : 0);
+    else wd = 4 + 2 * ((r.vmask[1] & bit) ? 1 : 0);
+    if (r.dir == 0) {
+        pixel *dst = px_at<pixel>(pl, r.x, r.y + 4 * u);
+        lf_edge4<pixel>(dst, E, I, H, stride, 1, wd, pp.bitdepth_max);
+    } else {
+        pixel *dst = px_at<pixel>(pl, r.x + 4 * u, r.y);
+        lf_edge4<pixel>(dst, E, I, H, 1, stride, wd, pp.bitdepth_max);
+    }
+}
+
+// ------------------------------------------------------------------------------- CDEF
+// Behaviour: dav1d_cdef_brow (ext/dav1d/src/cdef_apply_tmpl.c:97-308) for the per-8x8
+// decisions, cdef_find_dir_c / cdef_filter_block_c (ext/dav1d/src/cdef_tmpl.c:238-315,
+// :104-215) for the arithmetic. Out of place (a -> b), one 8x8 luma block (+ its chroma)
+// per thread group.
+
+struct CdefSmem {
+    int16_t tile[3][12 * 12];  // padded inputs, INT16_MIN marks "not available"
+    int32_t cost[8];
+    int32_t dir, var;
+};
+
+EAV1_DEV int cdef_constrain(int diff, int threshold, int shift) {
+    const int adiff = iabs(diff);
+    return apply_sign(imin(adiff, imax(0, threshold - (adiff >> shift))), diff);
+}
+
+// load the (w+4)x(h+4) neighbourhood of the block at (x0,y0) into a stride-12 tile
+template <typename pixel>
+EAV1_DEV void cdef_load(const Plane &pl, int x0, int y0, int w, int h, int edges, int16_t *tile, int tid, int nthr)
+{
+    for (int i = tid; i < (w + 4) * (h + 4); i += nthr) {
+        const int ty = i / (w + 4), tx = i - ty * (w + 4);
+        const int x = tx - 2, y = ty - 2;
+        const bool ok = (x >= 0 || (edges & 1)) && (x < w || (edges & 2)) && (y >= 0 || (edges & 4)) && (y < h || (edges & 8));
+        tile[ty * 12 + tx] = ok ? (int16_t)*px_at<pixel>(pl, x0 + x, y0 + y) : (int16_t)-32768;
+    }
+}
+
+template <typename pixel>
+EAV1_DEV void cdef_filter(const Eav1Tables *tab, const Plane &out, int x0, int y0, int w, int h, const int16_t *tile,
+                          int pri, int sec, int dir, int damping, int bitdepth_max, int tid, int nthr)
+{
+    const int bd8 = (32 - clz32((unsigned)bitdepth_max)) - 8;
+    const int pri_tap = 4 - ((pri >> bd8) & 1);
+    const int pri_shift = pri ? imax(0, damping - ulog2(pri)) : 0;
+    const int sec_shift = sec ? damping - ulog2(sec) : 0;
+    for (int i = tid; i < w * h; i += nthr) {
+        const int y = i / w, x = i - y * w;
+        const int16_t *t = tile + (y + 2) * 12 + x + 2;
+        const int px = t[0];
+        int sum = 0, mx = px, mn = px;
+        for (int k = 0; k < 2; k++) {
+            if (pri) {
+                const int off = tab->cdef_directions[dir + 2][k];
+                const int p0 = t[off], p1 = t[-off];
+                const int tap = k ? ((pri_tap & 3) | 2) : pri_tap;
+                sum += tap * cdef_constrain(p0 - px, pri, pri_shift);
+                sum += tap * cdef_constrain(p1 - px, pri, pri_shift);
+                if ((unsigned)p0 < (unsigned)mn) mn = p0;
+                if ((unsigned)p1 < (unsigned)mn) mn = p1;
+                mx = imax(imax(p0, p1), mx);
+            }
+            if (sec) {
+                const int o2 = tab->cdef_directions[dir + 4][k], o3 = tab->cdef_directions[dir][k];
+                const int s0 = t[o2], s1 = t[-o2], s2 = t[o3], s3 = t[-o3];
+                const int tap = 2 - k;
+                sum += tap * (cdef_constrain(s0 - px, sec, sec_shift) + cdef_constrain(s1 - px, sec, sec_shift) +
+                              cdef_constrain(s2 - px, sec, sec_shift) + cdef_constrain(s3 - px, sec, sec_shift));
+                if ((unsigned)s0 < (unsigned)mn) mn = s0;
+                if ((unsigned)s1 < (unsigned)mn) mn = s1;
+                if ((unsigned)s2 < (unsigned)mn) mn = s2;
+                if ((unsigned)s3 < (unsigned)mn) mn = s3;
+                mx = imax(imax(imax(s0, s1), imax(s2, s3)), mx);
+            }
+        }
+        int v = px + ((sum - (sum < 0) + 8) >> 4);
+        if (pri && sec) v = iclip(v, mn, mx);
+        *px_at<pixel>(out, x0 + x, y0 + y) = (pixel)v;
+    }
+}
+
+template <typename pixel>
+EAV1_DEV void cdef_copy(const Plane &in, const Plane &out, int x0, int y0, int w, int h, int tid, int nthr)
+{
+    for (int i = tid; i < w * h; i += nthr) {
+        const int y = i / w, x = i - y * w;
+        *px_at<pixel>(out, x0 + x, y0 + y) = *px_at<pixel>(in, x0 + x, y0 + y);
+    }
+}
+
+// Direction search on the 8x8 block held in tile[0] (interior at +2,+2). Eight cooperating
+// threads each evaluate one direction's cost from its partial sums.
+EAV1_DEV void cdef_dir_cost(const int16_t *tile, int bd8, int n, int32_t *cost)
+{
+    // line index of sample (x,y) for direction n, and number of lines
+    int part[15];
+    for (int i = 0; i < 15; i++) part[i] = 0;
+    for (int y = 0; y < 8; y++)
+        for (int x = 0; x < 8; x++) {
+            const int px = (tile[(y + 2) * 12 + x + 2] >> bd8) - 128;
+            int idx;
+            switch (n) {
+            case 0: idx = y + x; break;
+            case 1: idx = y + (x >> 1); break;
+            case 2: idx = y; break;
+            case 3: idx = 3 + y - (x >> 1); break;
+            case 4: idx = 7 + y - x; break;
+            case 5: idx = 3 - (y >> 1) + x; break;
+            case 6: idx = x; break;
+            default: idx = (y >> 1) + x; break;
+            }
+            part[idx] += px;
+        }
+    const int div_table[7] = { 840, 420, 280, 210, 168, 140, 120 };
+    unsigned c = 0;
+    if (n == 2 || n == 6) {
+        for (int i = 0; i < 8; i++) c += part[i] * part[i];
+        c *= 105;
+    } else if (n == 0 || n == 4) {
+        for (int i = 0; i < 7; i++) c += (part[i] * part[i] + part[14 - i] * part[14 - i]) * div_table[i];
+        c += part[7] * part[7] * 105;
+    } else {
+        for (int m = 0; m < 5; m++) c += part[3 + m] * part[3 + m];
+        c *= 105;
+        for (int m = 0; m < 3; m++) c += (part[m] * part[m] + part[10 - m] * part[10 - m]) * div_table[2 * m + 1];
+    }
+    cost[n] = (int32_t)c;
+}
+
+// One 8x8 luma block at 4x4-unit position (bx,by), bx and by even.
+template <typename pixel>
+EAV1_DEV void cdef_block(const PfParams &pp, int bx, int by, bool valid, CdefSmem &sm, int tid, int nthr)
+{
+    if (!valid) { CTA_SYNC(); CTA_SYNC(); CTA_SYNC(); return; } // keep barrier count equal across groups
+    const int bd8 = (32 - clz32((unsigned)pp.bitdepth_max)) - 8;
+    const int has_chroma = pp.layout != 0;
+    const int cw = 8 >> pp.ss_hor, chh = 8 >> pp.ss_ver;
+    const int lx = bx * 4, ly = by * 4, cx = lx >> pp.ss_hor, cy = ly >> pp.ss_ver;
+    // per-64x64 strength index and per-8x8 "has coefficients" bit (lf_mask.h:51-58)
+    const uint8_t *flt = pp.lfmask + (size_t)((by >> 5) * pp.sb128w + (bx >> 5)) * 1348;
+    const int sb64_idx = ((by & 16) >> 3) + ((bx & 16) >> 4);
+    const int cdef_idx = (int8_t)flt[1280 + sb64_idx];
+    const uint16_t *noskip = reinterpret_cast<const uint16_t *>(flt + 1284) + ((by & 30) >> 1) * 2;
+    const uint32_t noskip_mask = ((uint32_t)noskip[1] << 16) | noskip[0];
+    int y_lvl = 0, uv_lvl = 0;
+    bool active = cdef_idx != -1;
+    if (active) { y_lvl = pp.cdef_y[cdef_idx]; uv_lvl = pp.cdef_uv[cdef_idx]; active = y_lvl || uv_lvl; }
+    if (active) active = (noskip_mask & (3u << (bx & 30))) != 0;
+    // NOTE: several blocks share one CTA, so every block must pass the same CTA_SYNC()s:
+    // inactive blocks are predicated, never early-returned.
+    const int edges = (bx > 0 ? 1 : 0) | (bx + 2 < pp.bw4 ? 2 : 0) | (by > 0 ? 4 : 0) | (by + 2 < pp.bh4 ? 8 : 0);
+    const int y_pri = (y_lvl >> 2) << bd8;
+    int y_sec = y_lvl & 3; y_sec += y_sec == 3; y_sec <<= bd8;
+    const int uv_pri = (uv_lvl >> 2) << bd8;
+    int uv_sec = uv_lvl & 3; uv_sec += uv_sec == 3; uv_sec <<= bd8;
+    const int damping = pp.cdef_damping + bd8;
+
+    if (active) {
+        cdef_load<pixel>(pp.a[0], lx, ly, 8, 8, edges, sm.tile[0], tid, nthr);
+        if (has_chroma && uv_lvl) {
+            cdef_load<pixel>(pp.a[1], cx, cy, cw, chh, edges, sm.tile[1], tid, nthr);
+            cdef_load<pixel>(pp.a[2], cx, cy, cw, chh, edges, sm.tile[2], tid, nthr);
+        }
+    }
+    CTA_SYNC();
+    const bool need_dir = active && (y_pri || uv_pri);
+    if (need_dir)
+        for (int n = tid; n < 8; n += nthr) cdef_dir_cost(sm.tile[0], bd8, n, sm.cost);
+    CTA_SYNC();
+    if (need_dir && tid == 0) {
+        int best = 0;
+        unsigned bc = (unsigned)sm.cost[0];
+        for (int n = 1; n < 8; n++) if ((unsigned)sm.cost[n] > bc) { bc = (unsigned)sm.cost[n]; best = n; }
+        sm.dir = best;
+        sm.var = (int32_t)((bc - (unsigned)sm.cost[best ^ 4]) >> 10);
+    }
+    CTA_SYNC();
+    int dir = 0;
+    unsigned var = 0;
+    if (need_dir) { dir = sm.dir; var = (unsigned)sm.var; }
+    // luma
+    int pri = 0, ydir = 0;
+    bool do_y = false;
+    if (active) {
+        if (y_pri) {
+            const int i = (var >> 6) ? imin(ulog2(var >> 6), 12) : 0;
+            pri = var ? (y_pri * (4 + i) + 8) >> 4 : 0;
+            ydir = dir;
+            do_y = pri || y_sec;
+        } else do_y = y_sec != 0;
+    }
+    if (do_y) cdef_filter<pixel>(pp.tab, pp.b[0], lx, ly, 8, 8, sm.tile[0], pri, y_sec, ydir, damping, pp.bitdepth_max, tid, nthr);
+    else cdef_copy<pixel>(pp.a[0], pp.b[0], lx, ly, 8, 8, tid, nthr);
+    if (has_chroma) {
+        if (active && uv_lvl) {
+            const uint8_t uvd422[8] = { 7, 0, 2, 4, 5, 6, 6, 6 };
+            const int uvdir = uv_pri ? (pp.layout == 2 ? uvd422[dir] : dir) : 0;
+            cdef_filter<pixel>(pp.tab, pp.b[1], cx, cy, cw, chh, sm.tile[1], uv_pri, uv_sec, uvdir, damping - 1, pp.bitdepth_max, tid, nthr);
+            cdef_filter<pixel>(pp.tab, pp.b[2], cx, cy, cw, chh, sm.tile[2], uv_pri, uv_sec, uvdir, damping - 1, pp.bitdepth_max, tid, nthr);
+        } else {
+            cdef_copy<pixel>(pp.a[1], pp.b[1], cx, cy, cw, chh, tid, nthr);
+            cdef_copy<pixel>(pp.a[2], pp.b[2], cx, cy, cw, chh, tid, nthr);
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------- loop restoration
+// Behaviour: wiener_c (ext/dav1d/src/looprestoration_tmpl.c:250-387) and sgr_5x5_c / sgr_3x3_c /
+// sgr_mix_c (:679-1384) with sgr_calc_row_ab (:505-523) and the finish filters (:555-626).
+// The reference streams rows through ring buffers; here each CTA builds the padded input of a
+// <=32-column slice of one restoration-unit stripe in shared memory and evaluates the 2-D
+// definitions directly. Padding rules (lr_apply_tmpl.c:36-98, lf_apply_tmpl.c:41-102): rows
+// above/below the stripe are the two nearest DEBLOCKED (pre-CDEF) rows, the third replicated;
+// at the frame top/bottom and left/right the edge sample is replicated.
+
+#define LR_TW 32
+struct LrSmem {
+    uint16_t in[(64 + 6) * (LR_TW + 6)];
+    union {
+        uint16_t hor[(64 + 6) * LR_TW];                 // Wiener: horizontally filtered rows
+        struct {
+            int32_t a3[(64 + 2) * (LR_TW + 2)]; uint16_t b3[(64 + 2) * (LR_TW + 2)];
+            int32_t a5[34 * (LR_TW + 2)];       uint16_t b5[34 * (LR_TW + 2)];
+        } s;
+    };
+};
+
+template <typename pixel>
+EAV1_DEV void lr_load(const PfParams &pp, const Eav1LrRec &r, int x0, int tw, uint16_t *in, int tid, int nthr)
+{
+    const Plane &B = pp.b[r.plane], &A = pp.a[r.plane];
+    const int ss_ver = r.plane ? pp.ss_ver : 0;
+    const int ph = (pp.h + ss_ver) >> ss_ver;
+    const int W = tw + 6, H = r.h + 6;
+    for (int i = tid; i < W * H; i += nthr) {
+        const int ty = i / W, tx = i - ty * W;
+        const int ry = ty - 3;
+        int cx = x0 + tx - 3;
+        if (cx < 0 && !(r.edges & 1)) cx = 0;
+        if (cx >= r.w && !(r.edges & 2)) cx = r.w - 1;
+        const int ax = r.x + cx;
+        int v;
+        if (ry < 0) {
+            if (r.edges & 4) v = *px_at<pixel>(A, ax, r.y + imax(ry, -2));
+            else v = *px_at<pixel>(B, ax, r.y);
+        } else if (ry >= r.h) {
+            if (r.edges & 8) v = *px_at<pixel>(A, ax, imin(r.y + r.h + imin(ry - r.h, 1), ph - 1));
+            else v = *px_at<pixel>(B, ax, r.y + r.h - 1);
+        } else v = *px_at<pixel>(B, ax, r.y + ry);
+        in[i] = (uint16_t)v;
+    }
+}
+
+template <typename pixel>
+EAV1_DEV void lr_wiener_tile(const PfParams &pp, const Eav1LrRec &r, int x0, int tw, LrSmem &sm, int tid, int nthr)
+{
+    const int bitdepth = 32 - clz32((unsigned)pp.bitdepth_max);
+    const int rb_h = 3 + (bitdepth == 12) * 2, rb_v = 11 - (bitdepth == 12) * 2;
+    const int clip_limit = 1 << (bitdepth + 1 + 7 - rb_h);
+    const int W = tw + 6, H = r.h + 6;
+    lr_load<pixel>(pp, r, x0, tw, sm.in, tid, nthr);
+    CTA_SYNC();
+    for (int i = tid; i < H * tw; i += nthr) {
+        const int ty = i / tw, x = i - ty * tw;
+        const uint16_t *row = sm.in + ty * W + x;
+        int sum = 1 << (bitdepth + 6);
+        if (sizeof(pixel) == 1) sum += row[3] * 128;
+        for (int k = 0; k < 7; k++) sum += row[k] * r.p.filter[0][k];
+        sm.hor[ty * LR_TW + x] = (uint16_t)iclip((sum + (1 << (rb_h - 1))) >> rb_h, 0, clip_limit - 1);
+    }
+    CTA_SYNC();
+    const Plane &P = pp.p[r.plane];
+    for (int i = tid; i < r.h * tw; i += nthr) {
+        const int y = i / tw, x = i - y * tw;
+        int sum = -(1 << (bitdepth + (rb_v - 1)));
+        for (int k = 0; k < 7; k++) sum += sm.hor[(y + k) * LR_TW + x] * r.p.filter[1][k];
+        *px_at<pixel>(P, r.x + x0 + x, r.y + y) = (pixel)iclip((sum + (1 << (rb_v - 1))) >> rb_v, 0, pp.bitdepth_max);
+    }
+    CTA_SYNC();
+}
+
+// box statistics -> (A,B) of sgr_calc_row_ab for the window of radius rad centred at tile
+// position (cx,cy) (tile coordinates: sample (0,0) of the stripe slice sits at in[3*W+3]).
+EAV1_DEV void sgr_ab(const PfParams &pp, const uint16_t *in, int W, int cx, int cy, int rad, int s,
+                     int32_t *A, uint16_t *B)
+{
+    const int bd8 = (32 - clz32((unsigned)pp.bitdepth_max)) - 8;
+    unsigned sum = 0, sumsq = 0;
+    for (int dy = -rad; dy <= rad; dy++)
+        for (int dx = -rad; dx <= rad; dx++) {
+            const unsigned v = in[(cy + 3 + dy) * W + cx + 3 + dx];
+            sum += v; sumsq += v * v;
+        }
+    const int n = rad == 1 ? 9 : 25, one_by_x = rad == 1 ? 455 : 164;
+    const int a = (int)((sumsq + ((1u << (2 * bd8)) >> 1)) >> (2 * bd8));
+    const int b = (int)((sum + ((1u << bd8) >> 1)) >> bd8);
+    const unsigned p = (unsigned)imax(a * n - b * b, 0);
+    const unsigned z = (p * (unsigned)s + (1u << 19)) >> 20;
+    const unsigned x = pp.tab->sgr_x_by_x[z < 255 ? z : 255];
+    *A = (int32_t)((x * sum * (unsigned)one_by_x + (1u << 11)) >> 12);
+    *B = (uint16_t)x;
+}
+
+template <typename pixel>
+EAV1_DEV void lr_sgr_tile(const PfParams &pp, const Eav1LrRec &r, int x0, int tw, LrSmem &sm, int tid, int nthr)
+{
+    const int W = tw + 6, SW = tw + 2, h = r.h;
+    const bool do5 = r.kind != EAV1_LR_SGR_3X3, do3 = r.kind != EAV1_LR_SGR_5X5;
+    lr_load<pixel>(pp, r, x0, tw, sm.in, tid, nthr);
+    CTA_SYNC();
+    if (do3)
+        for (int i = tid; i < (h + 2) * SW; i += nthr) {
+            const int ty = i / SW, tx = i - ty * SW;
+            sgr_ab(pp, sm.in, W, tx - 1, ty - 1, 1, (int)r.p.sgr.s1, &sm.s.a3[i], &sm.s.b3[i]);
+        }
+    const int n5 = (h + 1) / 2 + 1; // rows -1, 1, 3, ...
+    if (do5)
+        for (int i = tid; i < n5 * SW; i += nthr) {
+            const int ty = i / SW, tx = i - ty * SW;
+            sgr_ab(pp, sm.in, W, tx - 1, 2 * ty - 1, 2, (int)r.p.sgr.s0, &sm.s.a5[i], &sm.s.b5[i]);
+        }
+    CTA_SYNC();
+    const Plane &P = pp.p[r.plane];
+    for (int i = tid; i < h * tw; i += nthr) {
+        const int y = i / tw, x = i - y * tw;
+        const int src = sm.in[(y + 3) * W + x + 3];
+        int t3 = 0, t5 = 0;
+        if (do3) {
+            const int32_t *A = sm.s.a3 + (y + 1) * SW + x + 1;
+            const uint16_t *Bq = sm.s.b3 + (y + 1) * SW + x + 1;
+            const int a = (Bq[0] + Bq[-1] + Bq[1] + Bq[-SW] + Bq[SW]) * 4 + (Bq[-SW - 1] + Bq[SW - 1] + Bq[-SW + 1] + Bq[SW + 1]) * 3;
+            const int b = (A[0] + A[-1] + A[1] + A[-SW] + A[SW]) * 4 + (A[-SW - 1] + A[SW - 1] + A[-SW + 1] + A[SW + 1]) * 3;
+            t3 = (b - a * src + (1 << 8)) >> 9;
+        }
+        if (do5) {
+            if (!(y & 1)) {
+                const int32_t *A0 = sm.s.a5 + (y >> 1) * SW + x + 1, *A1 = A0 + SW;
+                const uint16_t *B0 = sm.s.b5 + (y >> 1) * SW + x + 1, *B1 = B0 + SW;
+                const int a = (B0[0] + B1[0]) * 6 + (B0[-1] + B1[-1] + B0[1] + B1[1]) * 5;
+                const int b = (A0[0] + A1[0]) * 6 + (A0[-1] + A1[-1] + A0[1] + A1[1]) * 5;
+                t5 = (b - a * src + (1 << 8)) >> 9;
+            } else {
+                const int32_t *A1 = sm.s.a5 + ((y + 1) >> 1) * SW + x + 1;
+                const uint16_t *B1 = sm.s.b5 + ((y + 1) >> 1) * SW + x + 1;
+                const int a = B1[0] * 6 + (B1[-1] + B1[1]) * 5;
+                const int b = A1[0] * 6 + (A1[-1] + A1[1]) * 5;
+                t5 = (b - a * src + (1 << 7)) >> 8;
+            }
+        }
+        int v;
+        if (r.kind == EAV1_LR_SGR_MIX) v = r.p.sgr.w0 * t5 + r.p.sgr.w1 * t3;
+        else if (r.kind == EAV1_LR_SGR_5X5) v = r.p.sgr.w0 * t5;
+        else v = r.p.sgr.w1 * t3;
+        *px_at<pixel>(P, r.x + x0 + x, r.y + y) = (pixel)iclip(src + ((v + (1 << 10)) >> 11), 0, pp.bitdepth_max);
+    }
+    CTA_SYNC();
+}
+
+template <typename pixel>
+EAV1_DEV void lr_tile(const PfParams &pp, const Eav1LrRec &r, int slice, LrSmem &sm, int tid, int nthr)
+{
+    const int x0 = slice * LR_TW;
+    if (x0 >= r.w) return; // uniform across the CTA
+    const int tw = imin(LR_TW, r.w - x0);
+    if (r.kind <= EAV1_LR_WIENER5) lr_wiener_tile<pixel>(pp, r, x0, tw, sm, tid, nthr);
+    else lr_sgr_tile<pixel>(pp, r, x0, tw, sm, tid, nthr);
+}
+
 } // namespace eav1

@@ -9,6 +9,7 @@
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <algorithm>
 #include <vector>
 #include <string>
 
@@ -103,14 +104,21 @@ int eav1cu_frame_submit(Eav1cuCtx *c, const Eav1FrameDesc *fd, const Eav1Cmd *cm
 {
     if (!c->have_tab) return EAV1CU_ERR_NOTABLES;
     Picture &cur = c->pics[fd->cur];
+    const bool has_cdef = fd->cdef_enable != 0, has_lr = fd->n_lr_recs > 0;
+    Picture *A = &cur;
+    if (has_cdef || has_lr) {
+        pic_setup(c->work[0], cur.w, cur.h, cur.layout, cur.bpc);
+        if (has_cdef && has_lr) pic_setup(c->work[1], cur.w, cur.h, cur.layout, cur.bpc);
+        A = &c->work[0];
+    }
     FrameCtx fc;
     memset(&fc, 0, sizeof(fc));
-    for (int i = 0; i < 3; i++) fc.cur[i] = cur.pl[i];
+    for (int i = 0; i < 3; i++) fc.cur[i] = A->pl[i];
     for (int r = 0; r < 7; r++) {
-        const Picture &rp = fd->ref[r] >= 0 ? c->pics[fd->ref[r]] : cur;
+        const Picture &rp = fd->ref[r] >= 0 ? c->pics[fd->ref[r]] : *A;
         for (int i = 0; i < 3; i++) fc.ref[r][i] = rp.pl[i];
     }
-    for (int i = 0; i < 3; i++) fc.ref[7][i] = cur.pl[i];
+    for (int i = 0; i < 3; i++) fc.ref[7][i] = A->pl[i];
     fc.bitdepth_max = (1 << fd->bpc) - 1;
     fc.ss_hor = fd->layout != 3; fc.ss_ver = fd->layout == 1;
     fc.tab = &c->tab;
@@ -124,7 +132,7 @@ int eav1cu_frame_submit(Eav1cuCtx *c, const Eav1FrameDesc *fd, const Eav1Cmd *cm
         else exec_cmd<BD8>(fc, cmds[i], sm, 0, 1);
     }
     c->launches++;
-    return emu_postfilter(c, fd, fc);
+    return emu_postfilter(c, fd, *A, cur);
 }
 
 } // extern "C"

@@ -83,6 +83,24 @@ struct DevBuf {
     uint8_t *h = nullptr; size_t hcap = 0; // pinned staging
 };
 
+// A frame ready to launch: every list it needs is resident in device memory. The streaming
+// path points these at the context's reusable buffers; eav1cu_frame_stage() gives a frame
+// its own copies so it can be replayed with no host work (bench.py's device-resident leg).
+struct FramePlan {
+    Eav1FrameDesc fd;
+    const Eav1Cmd *d_cmds = nullptr;
+    const Chain *d_chains = nullptr;
+    const uint8_t *d_payload = nullptr;
+    std::vector<uint32_t> level_start;
+    size_t arena_bytes = 0, payload_bytes = 0, n_cmds = 0;
+    const Eav1LfRec *d_lf = nullptr; size_t n_lf0 = 0, n_lf1 = 0;
+    const uint8_t *d_lflvl = nullptr;
+    const uint8_t *d_lfmask = nullptr;
+    const Eav1LrRec *d_lr = nullptr; size_t n_lr = 0;
+    std::vector<void *> owned;   // device allocations owned by a staged plan
+    long long launches = 0;
+};
+
 struct Eav1cuCtx {
     int device = 0;
     cudaStream_t stream = nullptr;
@@ -98,7 +116,18 @@ struct Eav1cuCtx {
     int err = 0;
     std::string errmsg;
     std::mutex mu;
-    long long n_launches = 0;
+    long long n_launches = 0, h2d_bytes = 0, d2h_bytes = 0, n_frames = 0;
+    bool own_stream = true;
+    // optional per-stage device timing (bench.py's roofline leg)
+    bool stage_timing = false;
+    struct Span { cudaEvent_t a, b; int stage; int launches; };
+    std::vector<Span> spans;
+    std::vector<cudaEvent_t> ev_pool;
+    double stage_ms[4] = {0, 0, 0, 0};
+    long long stage_launches[4] = {0, 0, 0, 0}, stage_calls[4] = {0, 0, 0, 0};
+    bool capture = false;
+    FramePlan live;
+    std::vector<FramePlan *> staged;
 };
 
 static int fail(Eav1cuCtx *c, int code, const char *what, cudaError_t e = cudaSuccess)
@@ -143,6 +172,7 @@ static int upload(Eav1cuCtx *ctx, DevBuf &b, const void *src, size_t bytes)
     if (r) return r;
     memcpy(b.h, src, bytes);
     CK(cudaMemcpyAsync(b.d, b.h, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    ctx->h2d_bytes += (long long)bytes;
     return 0;
 }
 
@@ -205,7 +235,10 @@ void eav1cu_ctx_destroy(Eav1cuCtx *ctx)
     free_buf(ctx->lfrec); free_buf(ctx->lflvl); free_buf(ctx->lrrec); free_buf(ctx->lfmask);
     if (ctx->d_tab) cudaFree(ctx->d_tab);
     if (ctx->d_masks) cudaFree(ctx->d_masks);
-    cudaStreamDestroy(ctx->stream);
+    for (auto &sp : ctx->spans) { cudaEventDestroy(sp.a); cudaEventDestroy(sp.b); }
+    for (cudaEvent_t e : ctx->ev_pool) cudaEventDestroy(e);
+    for (FramePlan *sp : ctx->staged) { for (void *d : sp->owned) cudaFree(d); delete sp; }
+    if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
 
@@ -280,7 +313,7 @@ int eav1cu_pic_release(Eav1cuCtx *ctx, int id)
 
 static int pic_copy(Eav1cuCtx *ctx, int id, void *const data[3], const ptrdiff_t stride[2], bool to_device)
 {
-    if (!ctx || id < 0 || id >= (int)ctx->pics.size() || !ctx->pics[id].used) return EAV1CU_ERR_INVAL;
+    if (!ctx || id < 0 || id >= (int)ctx->pics.size() || !ctx->pics[id].base) return EAV1CU_ERR_INVAL;
     CK(cudaSetDevice(ctx->device));
     Picture &p = ctx->pics[id];
     const int hbd = p.bpc > 8;
@@ -288,6 +321,7 @@ static int pic_copy(Eav1cuCtx *ctx, int id, void *const data[3], const ptrdiff_t
     for (int pl = 0; pl < (p.layout ? 3 : 1); pl++) {
         const int w = pl ? (p.w + ss_hor) >> ss_hor : p.w;
         const int h = pl ? (p.h + ss_ver) >> ss_ver : p.h;
+        if (to_device) ctx->h2d_bytes += ((long long)w << hbd) * h; else ctx->d2h_bytes += ((long long)w << hbd) * h;
         if (to_device)
             CK(cudaMemcpy2DAsync(p.pl[pl].p, p.pl[pl].stride, data[pl], stride[!!pl], (size_t)w << hbd, h,
                                  cudaMemcpyHostToDevice, ctx->stream));
@@ -333,11 +367,143 @@ int eav1cu_arena_download(Eav1cuCtx *ctx, size_t off, void *dst, size_t bytes)
 
 static void fill_planes(const Picture &p, Plane out[3]) { for (int i = 0; i < 3; i++) out[i] = p.pl[i]; }
 
+} // extern "C"
 
-static int postfilter_run(Eav1cuCtx *ctx, const Eav1FrameDesc *fd, Picture &A, Picture &cur)
+static cudaEvent_t ev_get(Eav1cuCtx *ctx)
 {
-    const bool hbd = fd->bpc > 8;
+    if (!ctx->ev_pool.empty()) { cudaEvent_t e = ctx->ev_pool.back(); ctx->ev_pool.pop_back(); return e; }
+    cudaEvent_t e = nullptr;
+    cudaEventCreate(&e);
+    return e;
+}
+
+struct StageTimer {
+    Eav1cuCtx *ctx; int stage; long long l0; cudaEvent_t a = nullptr;
+    StageTimer(Eav1cuCtx *c, int st) : ctx(c), stage(st), l0(c->n_launches) {
+        if (ctx->stage_timing) { a = ev_get(ctx); cudaEventRecord(a, ctx->stream); }
+    }
+    ~StageTimer() {
+        if (!a) return;
+        cudaEvent_t b = ev_get(ctx);
+        cudaEventRecord(b, ctx->stream);
+        ctx->spans.push_back({a, b, stage, (int)(ctx->n_launches - l0)});
+    }
+};
+
+struct Uploader {
+    // either reuses a context DevBuf (streaming) or allocates a private device copy (staged)
+    Eav1cuCtx *ctx; FramePlan *own;
+    int put(DevBuf &b, const void *src, size_t bytes, const uint8_t **out) {
+        *out = nullptr;
+        if (!bytes) return 0;
+        if (!own) {
+            int r = upload(ctx, b, src, bytes);
+            *out = b.d;
+            return r;
+        }
+        void *d = nullptr;
+        CK(cudaMalloc(&d, bytes));
+        own->owned.push_back(d);
+        CK(cudaMemcpyAsync(d, src, bytes, cudaMemcpyHostToDevice, ctx->stream));
+        CK(cudaStreamSynchronize(ctx->stream));
+        *out = (const uint8_t *)d;
+        return 0;
+    }
+};
+
+static int plan_build(Eav1cuCtx *ctx, FramePlan &pl, bool staged, const Eav1FrameDesc *fd,
+                      const Eav1Cmd *cmds, size_t n_cmds,
+                      const void *payload, size_t payload_bytes, size_t arena_bytes)
+{
+    if (fd->cur < 0 || fd->cur >= (int)ctx->pics.size() || !ctx->pics[fd->cur].base)
+        return fail(ctx, EAV1CU_ERR_INVAL, "bad current picture id");
+    Picture &cur = ctx->pics[fd->cur];
+    pl.fd = *fd;
+    pl.fd.lf_recs = nullptr; pl.fd.lf_level = nullptr; pl.fd.lf_mask = nullptr; pl.fd.lr_recs = nullptr;
     const bool has_cdef = fd->cdef_enable != 0, has_lr = fd->n_lr_recs > 0;
+    int r;
+    if (has_cdef || has_lr) {
+        if ((r = pic_setup(ctx, ctx->work[0], cur.w, cur.h, cur.layout, cur.bpc))) return r;
+        if (has_cdef && has_lr && (r = pic_setup(ctx, ctx->work[1], cur.w, cur.h, cur.layout, cur.bpc))) return r;
+    }
+    Uploader up{ctx, staged ? &pl : nullptr};
+    const uint8_t *d;
+    pl.level_start.clear();
+    pl.arena_bytes = arena_bytes; pl.payload_bytes = payload_bytes; pl.n_cmds = n_cmds;
+    if (n_cmds) {
+        int pw[3] = { cur.pl[0].w, cur.pl[1].w, cur.pl[2].w };
+        int ph[3] = { cur.pl[0].h, cur.pl[1].h, cur.pl[2].h };
+        ctx->sched.reset(pw, ph);
+        ctx->sched.build(cmds, n_cmds, ctx->plan);
+        if ((r = up.put(ctx->cmds, cmds, n_cmds * sizeof(Eav1Cmd), &d))) return r;
+        pl.d_cmds = reinterpret_cast<const Eav1Cmd *>(d);
+        if ((r = up.put(ctx->chains, ctx->plan.chains.data(), ctx->plan.chains.size() * sizeof(Chain), &d))) return r;
+        pl.d_chains = reinterpret_cast<const Chain *>(d);
+        if ((r = up.put(ctx->payload, payload, payload_bytes, &pl.d_payload))) return r;
+        if ((r = ensure(ctx, ctx->arena, arena_bytes + 16, false))) return r;
+        pl.level_start = ctx->plan.level_start;
+    }
+    if (fd->n_lf_recs) {
+        // partition the recorded calls: all column-edge filters run before all row-edge filters
+        std::vector<Eav1LfRec> &v = ctx->lf_sorted;
+        v.resize(fd->n_lf_recs);
+        size_t n0 = 0;
+        for (size_t i = 0; i < fd->n_lf_recs; i++) if (fd->lf_recs[i].dir == 0) v[n0++] = fd->lf_recs[i];
+        size_t n1 = n0;
+        for (size_t i = 0; i < fd->n_lf_recs; i++) if (fd->lf_recs[i].dir != 0) v[n1++] = fd->lf_recs[i];
+        if ((r = up.put(ctx->lfrec, v.data(), v.size() * sizeof(Eav1LfRec), &d))) return r;
+        pl.d_lf = reinterpret_cast<const Eav1LfRec *>(d);
+        pl.n_lf0 = n0; pl.n_lf1 = n1 - n0;
+        if ((r = up.put(ctx->lflvl, fd->lf_level, fd->lf_level_bytes, &pl.d_lflvl))) return r;
+    } else { pl.n_lf0 = pl.n_lf1 = 0; }
+    if (has_cdef)
+        if ((r = up.put(ctx->lfmask, fd->lf_mask, (size_t)fd->sb128w * fd->sb128h * 1348, &pl.d_lfmask))) return r;
+    pl.n_lr = fd->n_lr_recs;
+    if (has_lr) {
+        if ((r = up.put(ctx->lrrec, fd->lr_recs, fd->n_lr_recs * sizeof(Eav1LrRec), &d))) return r;
+        pl.d_lr = reinterpret_cast<const Eav1LrRec *>(d);
+    }
+    return 0;
+}
+
+static int plan_launch(Eav1cuCtx *ctx, FramePlan &pl)
+{
+    const Eav1FrameDesc *fd = &pl.fd;
+    Picture &cur = ctx->pics[fd->cur];
+    const bool hbd = fd->bpc > 8;
+    const bool has_cdef = fd->cdef_enable != 0, has_lr = pl.n_lr > 0;
+    cudaStream_t st = ctx->stream;
+    long long n0 = ctx->n_launches;
+    // recon + deblock happen in A; CDEF / LR then move the frame towards `cur` out of place
+    Picture &A = (has_cdef || has_lr) ? ctx->work[0] : cur;
+
+    FrameCtx fc;
+    memset(&fc, 0, sizeof(fc));
+    fill_planes(A, fc.cur);
+    for (int r = 0; r < 7; r++) {
+        const int id = fd->ref[r];
+        if (id >= 0 && id < (int)ctx->pics.size() && ctx->pics[id].base) fill_planes(ctx->pics[id], fc.ref[r]);
+        else fill_planes(A, fc.ref[r]);
+    }
+    fill_planes(A, fc.ref[7]);
+    fc.bitdepth_max = (1 << fd->bpc) - 1;
+    fc.ss_hor = fd->layout != 3;
+    fc.ss_ver = fd->layout == 1;
+    fc.tab = ctx->d_tab;
+    fc.masks = ctx->d_masks;
+    fc.arena = ctx->arena.d;
+    fc.payload = pl.d_payload;
+    if (pl.level_start.size() > 1) {
+    StageTimer tm(ctx, 0);
+    for (size_t l = 0; l + 1 < pl.level_start.size(); l++) {
+        const uint32_t a = pl.level_start[l], b = pl.level_start[l + 1];
+        if (a == b) continue;
+        if (hbd) recon_level_kernel<BD16><<<b - a, 128, 0, st>>>(fc, pl.d_cmds, pl.d_chains + a);
+        else     recon_level_kernel<BD8><<<b - a, 128, 0, st>>>(fc, pl.d_cmds, pl.d_chains + a);
+        ctx->n_launches++;
+    }
+    }
+
     PfParams pp;
     memset(&pp, 0, sizeof(pp));
     pp.bitdepth_max = (1 << fd->bpc) - 1;
@@ -349,54 +515,44 @@ static int postfilter_run(Eav1cuCtx *ctx, const Eav1FrameDesc *fd, Picture &A, P
     memcpy(pp.cdef_y, fd->cdef_y_strength, 8); memcpy(pp.cdef_uv, fd->cdef_uv_strength, 8);
     pp.tab = ctx->d_tab;
     for (int i = 0; i < 3; i++) pp.a[i] = A.pl[i];
-    int r;
-    if (fd->n_lf_recs) {
-        // partition the recorded calls: all column-edge filters run before all row-edge filters
-        std::vector<Eav1LfRec> &v = ctx->lf_sorted;
-        v.resize(fd->n_lf_recs);
-        size_t n0 = 0;
-        for (size_t i = 0; i < fd->n_lf_recs; i++) if (fd->lf_recs[i].dir == 0) v[n0++] = fd->lf_recs[i];
-        size_t n1 = n0;
-        for (size_t i = 0; i < fd->n_lf_recs; i++) if (fd->lf_recs[i].dir != 0) v[n1++] = fd->lf_recs[i];
-        if ((r = upload(ctx, ctx->lfrec, v.data(), v.size() * sizeof(Eav1LfRec)))) return r;
-        if ((r = upload(ctx, ctx->lflvl, fd->lf_level, fd->lf_level_bytes))) return r;
-        pp.level = ctx->lflvl.d;
-        const Eav1LfRec *d = reinterpret_cast<const Eav1LfRec *>(ctx->lfrec.d);
-        for (int pass = 0; pass < 2; pass++) {
-            const size_t off = pass ? n0 : 0, cnt = pass ? n1 - n0 : n0;
-            if (!cnt) continue;
-            const unsigned grid = (unsigned)((cnt * 32 + 127) / 128);
-            if (hbd) deblock_kernel<uint16_t><<<grid, 128, 0, ctx->stream>>>(pp, d + off, (int)cnt);
-            else     deblock_kernel<uint8_t><<<grid, 128, 0, ctx->stream>>>(pp, d + off, (int)cnt);
-            ctx->n_launches++;
-        }
+    pp.level = pl.d_lflvl;
+    if (pl.n_lf0 + pl.n_lf1) {
+    StageTimer tm(ctx, 1);
+    for (int pass = 0; pass < 2; pass++) {
+        const size_t off = pass ? pl.n_lf0 : 0, cnt = pass ? pl.n_lf1 : pl.n_lf0;
+        if (!cnt) continue;
+        const unsigned grid = (unsigned)((cnt * 32 + 127) / 128);
+        if (hbd) deblock_kernel<uint16_t><<<grid, 128, 0, st>>>(pp, pl.d_lf + off, (int)cnt);
+        else     deblock_kernel<uint8_t><<<grid, 128, 0, st>>>(pp, pl.d_lf + off, (int)cnt);
+        ctx->n_launches++;
+    }
     }
     if (has_cdef) {
+        StageTimer tm(ctx, 2);
         Picture &dst = has_lr ? ctx->work[1] : cur;
         for (int i = 0; i < 3; i++) pp.b[i] = dst.pl[i];
-        if ((r = upload(ctx, ctx->lfmask, fd->lf_mask, (size_t)fd->sb128w * fd->sb128h * 1348))) return r;
-        pp.lfmask = ctx->lfmask.d;
+        pp.lfmask = pl.d_lfmask;
         dim3 grid((fd->bw4 / 2 + 8) / 8, (fd->bh4 + 1) / 2);
-        if (hbd) cdef_kernel<uint16_t><<<grid, 256, 0, ctx->stream>>>(pp);
-        else     cdef_kernel<uint8_t><<<grid, 256, 0, ctx->stream>>>(pp);
+        if (hbd) cdef_kernel<uint16_t><<<grid, 256, 0, st>>>(pp);
+        else     cdef_kernel<uint8_t><<<grid, 256, 0, st>>>(pp);
         ctx->n_launches++;
     }
     if (has_lr) {
+        StageTimer tm(ctx, 3);
         Picture &src = has_cdef ? ctx->work[1] : A;
         for (int i = 0; i < 3; i++) { pp.b[i] = src.pl[i]; pp.p[i] = cur.pl[i]; }
-        CK(cudaMemcpyAsync(cur.base, src.base, std::min(cur.bytes, src.bytes), cudaMemcpyDeviceToDevice, ctx->stream));
-        if ((r = upload(ctx, ctx->lrrec, fd->lr_recs, fd->n_lr_recs * sizeof(Eav1LrRec)))) return r;
-        dim3 grid(384 / LR_TW, (unsigned)fd->n_lr_recs);
-        const Eav1LrRec *d = reinterpret_cast<const Eav1LrRec *>(ctx->lrrec.d);
-        if (hbd) lr_kernel<uint16_t><<<grid, 128, 0, ctx->stream>>>(pp, d);
-        else     lr_kernel<uint8_t><<<grid, 128, 0, ctx->stream>>>(pp, d);
+        CK(cudaMemcpyAsync(cur.base, src.base, std::min(cur.bytes, src.bytes), cudaMemcpyDeviceToDevice, st));
+        dim3 grid(384 / LR_TW, (unsigned)pl.n_lr);
+        if (hbd) lr_kernel<uint16_t><<<grid, 128, 0, st>>>(pp, pl.d_lr);
+        else     lr_kernel<uint8_t><<<grid, 128, 0, st>>>(pp, pl.d_lr);
         ctx->n_launches++;
     }
     CK(cudaGetLastError());
+    pl.launches = ctx->n_launches - n0;
     return 0;
 }
 
-
+extern "C" {
 
 int eav1cu_frame_submit(Eav1cuCtx *ctx, const Eav1FrameDesc *fd,
                         const Eav1Cmd *cmds, size_t n_cmds,
@@ -405,62 +561,130 @@ int eav1cu_frame_submit(Eav1cuCtx *ctx, const Eav1FrameDesc *fd,
     if (!ctx || !fd) return EAV1CU_ERR_INVAL;
     if (ctx->err) return ctx->err;
     if (!ctx->have_tab) return fail(ctx, EAV1CU_ERR_NOTABLES, "eav1cu_set_tables not called");
-    if (fd->cur < 0 || fd->cur >= (int)ctx->pics.size() || !ctx->pics[fd->cur].used)
-        return fail(ctx, EAV1CU_ERR_INVAL, "bad current picture id");
     CK(cudaSetDevice(ctx->device));
-    Picture &cur = ctx->pics[fd->cur];
-    const bool hbd = fd->bpc > 8;
-    const bool has_cdef = fd->cdef_enable != 0, has_lr = fd->n_lr_recs > 0;
-    // recon + deblock happen in A; CDEF / LR then move the frame towards `cur` out of place
-    Picture *A = &cur;
-    if (has_cdef || has_lr) {
-        int r0 = pic_setup(ctx, ctx->work[0], cur.w, cur.h, cur.layout, cur.bpc);
-        if (r0) return r0;
-        if (has_cdef && has_lr && (r0 = pic_setup(ctx, ctx->work[1], cur.w, cur.h, cur.layout, cur.bpc))) return r0;
-        A = &ctx->work[0];
-    }
-
-    FrameCtx fc;
-    memset(&fc, 0, sizeof(fc));
-    fill_planes(*A, fc.cur);
-    for (int r = 0; r < 7; r++) {
-        const int id = fd->ref[r];
-        if (id >= 0 && id < (int)ctx->pics.size() && ctx->pics[id].base) fill_planes(ctx->pics[id], fc.ref[r]);
-        else fill_planes(*A, fc.ref[r]);
-    }
-    fill_planes(*A, fc.ref[7]);
-    fc.bitdepth_max = (1 << fd->bpc) - 1;
-    fc.ss_hor = fd->layout != 3;
-    fc.ss_ver = fd->layout == 1;
-    fc.tab = ctx->d_tab;
-    fc.masks = ctx->d_masks;
-
-    if (n_cmds) {
-        int pw[3] = { A->pl[0].w, A->pl[1].w, A->pl[2].w };
-        int ph[3] = { A->pl[0].h, A->pl[1].h, A->pl[2].h };
-        ctx->sched.reset(pw, ph);
-        ctx->sched.build(cmds, n_cmds, ctx->plan);
-        int r;
-        if ((r = upload(ctx, ctx->cmds, cmds, n_cmds * sizeof(Eav1Cmd)))) return r;
-        if ((r = upload(ctx, ctx->chains, ctx->plan.chains.data(), ctx->plan.chains.size() * sizeof(Chain)))) return r;
-        if ((r = upload(ctx, ctx->payload, payload, payload_bytes))) return r;
-        if ((r = ensure(ctx, ctx->arena, arena_bytes + 16, false))) return r;
-        fc.arena = ctx->arena.d;
-        fc.payload = ctx->payload.d;
-        const Eav1Cmd *d_cmds = reinterpret_cast<const Eav1Cmd *>(ctx->cmds.d);
-        const Chain *d_chains = reinterpret_cast<const Chain *>(ctx->chains.d);
-        for (size_t l = 0; l + 1 < ctx->plan.level_start.size(); l++) {
-            const uint32_t a = ctx->plan.level_start[l], b = ctx->plan.level_start[l + 1];
-            if (a == b) continue;
-            if (hbd) recon_level_kernel<BD16><<<b - a, 128, 0, ctx->stream>>>(fc, d_cmds, d_chains + a);
-            else     recon_level_kernel<BD8><<<b - a, 128, 0, ctx->stream>>>(fc, d_cmds, d_chains + a);
-            ctx->n_launches++;
-        }
-        CK(cudaGetLastError());
-    }
-    int r = postfilter_run(ctx, fd, *A, cur);
+    int r = plan_build(ctx, ctx->live, false, fd, cmds, n_cmds, payload, payload_bytes, arena_bytes);
     if (r) return r;
+    if ((r = plan_launch(ctx, ctx->live))) return r;
+    ctx->n_frames++;
+    if (ctx->capture) {
+        // keep a replayable copy of this frame (bench.py's device-resident leg)
+        FramePlan *sp = new FramePlan();
+        if ((r = plan_build(ctx, *sp, true, fd, cmds, n_cmds, payload, payload_bytes, arena_bytes))) { delete sp; return r; }
+        ctx->staged.push_back(sp);
+    }
     return ctx->err;
+}
+
+size_t eav1cu_abi_sizeof(int which)
+{
+    switch (which) {
+    case 0: return sizeof(Eav1Cmd);
+    case 1: return sizeof(Eav1LfRec);
+    case 2: return sizeof(Eav1LrRec);
+    case 3: return sizeof(Eav1FrameDesc);
+    case 4: return sizeof(Eav1StagedInfo);
+    case 5: return sizeof(Eav1Tables);
+    default: return 0;
+    }
+}
+
+int eav1cu_plan_levels(const Eav1Cmd *cmds, size_t n_cmds, const int plane_w[3], const int plane_h[3],
+                       uint32_t *chain_first, uint32_t *chain_level, size_t cap)
+{
+    if (!cmds || !plane_w || !plane_h) return EAV1CU_ERR_INVAL;
+    Scheduler sc;
+    Schedule plan;
+    sc.reset(plane_w, plane_h);
+    sc.build(cmds, n_cmds, plan);
+    size_t k = 0;
+    for (size_t l = 0; l + 1 < plan.level_start.size(); l++)
+        for (uint32_t c = plan.level_start[l]; c < plan.level_start[l + 1]; c++, k++)
+            if (k < cap) {
+                if (chain_first) chain_first[k] = plan.chains[c].first;
+                if (chain_level) chain_level[k] = (uint32_t)l;
+            }
+    return (int)plan.chains.size();
+}
+
+int eav1cu_counters(Eav1cuCtx *ctx, long long out[4])
+{
+    if (!ctx || !out) return EAV1CU_ERR_INVAL;
+    out[0] = ctx->n_launches; out[1] = ctx->h2d_bytes; out[2] = ctx->d2h_bytes; out[3] = ctx->n_frames;
+    return 0;
+}
+
+int eav1cu_set_stage_timing(Eav1cuCtx *ctx, int on)
+{
+    if (!ctx) return EAV1CU_ERR_INVAL;
+    ctx->stage_timing = on != 0;
+    return 0;
+}
+
+int eav1cu_stage_times(Eav1cuCtx *ctx, double ms[4], long long launches[4], long long calls[4], int reset)
+{
+    if (!ctx) return EAV1CU_ERR_INVAL;
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaStreamSynchronize(ctx->stream));
+    for (auto &sp : ctx->spans) {
+        float t = 0.f;
+        if (cudaEventElapsedTime(&t, sp.a, sp.b) == cudaSuccess) {
+            ctx->stage_ms[sp.stage] += t;
+            ctx->stage_launches[sp.stage] += sp.launches;
+            ctx->stage_calls[sp.stage]++;
+        }
+        ctx->ev_pool.push_back(sp.a); ctx->ev_pool.push_back(sp.b);
+    }
+    ctx->spans.clear();
+    for (int i = 0; i < 4; i++) {
+        if (ms) ms[i] = ctx->stage_ms[i];
+        if (launches) launches[i] = ctx->stage_launches[i];
+        if (calls) calls[i] = ctx->stage_calls[i];
+        if (reset) { ctx->stage_ms[i] = 0; ctx->stage_launches[i] = 0; ctx->stage_calls[i] = 0; }
+    }
+    return 0;
+}
+
+int eav1cu_set_capture(Eav1cuCtx *ctx, int on)
+{
+    if (!ctx) return EAV1CU_ERR_INVAL;
+    ctx->capture = on != 0;
+    return 0;
+}
+
+int eav1cu_staged_count(Eav1cuCtx *ctx) { return ctx ? (int)ctx->staged.size() : 0; }
+
+int eav1cu_staged_replay(Eav1cuCtx *ctx, int idx)
+{
+    if (!ctx || idx < 0 || idx >= (int)ctx->staged.size()) return EAV1CU_ERR_INVAL;
+    if (ctx->err) return ctx->err;
+    return plan_launch(ctx, *ctx->staged[idx]);
+}
+
+int eav1cu_staged_info(Eav1cuCtx *ctx, int idx, Eav1StagedInfo *out)
+{
+    if (!ctx || !out || idx < 0 || idx >= (int)ctx->staged.size()) return EAV1CU_ERR_INVAL;
+    const FramePlan &p = *ctx->staged[idx];
+    memset(out, 0, sizeof(*out));
+    out->cur = p.fd.cur; out->w = p.fd.w; out->h = p.fd.h; out->bpc = p.fd.bpc; out->layout = p.fd.layout;
+    out->n_levels = p.level_start.empty() ? 0 : (int)p.level_start.size() - 1;
+    out->n_chains = p.level_start.empty() ? 0 : (int)p.level_start.back();
+    out->launches = (int)p.launches;
+    out->n_lf = (int)(p.n_lf0 + p.n_lf1); out->n_lr = (int)p.n_lr;
+    out->cdef = p.fd.cdef_enable;
+    out->n_cmds = (long long)p.n_cmds; out->payload_bytes = (long long)p.payload_bytes;
+    for (int i = 0; i < 7; i++) if (p.fd.ref[i] >= 0) out->inter = 1;
+    return 0;
+}
+
+int eav1cu_set_stream(Eav1cuCtx *ctx, void *cuda_stream)
+{
+    if (!ctx) return EAV1CU_ERR_INVAL;
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaStreamSynchronize(ctx->stream));
+    if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
+    ctx->stream = (cudaStream_t)cuda_stream;
+    ctx->own_stream = false;
+    return 0;
 }
 
 } // extern "C"

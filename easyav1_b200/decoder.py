@@ -32,6 +32,11 @@ class Decoder:
         return info, self.buf.raw[:used.value]
 
     @property
+    def engine(self):
+        """Eav1cuCtx* behind this stream (measurement hooks of include/easyav1_cuda.h)."""
+        return self.L.eav1rec_engine(self.L.eav1_stream_ctx(self.h))
+
+    @property
     def launches(self):
         return self.L.eav1rec_launches(self.L.eav1_stream_ctx(self.h))
 

@@ -409,6 +409,8 @@ int eav1rec_frame_end(Eav1Rec *r, const Dav1dFrameContext *f)
 /* for tools / tests: how many frames went through the engine and whether it failed */
 long long eav1rec_frames_submitted(const Dav1dContext *c) { Eav1Rec *r = eav1rec_for_ctx(c); return r ? r->frames_submitted : -1; }
 int eav1rec_error(const Dav1dContext *c) { Eav1Rec *r = eav1rec_for_ctx(c); return r ? r->error : -1; }
+/* the engine context behind a Dav1dContext, for measurement (bench.py) */
+Eav1cuCtx *eav1rec_engine(const Dav1dContext *c) { Eav1Rec *r = eav1rec_for_ctx(c); return r ? r->cu : NULL; }
 long long eav1rec_launches(const Dav1dContext *c) { Eav1Rec *r = eav1rec_for_ctx(c); return r ? eav1cu_launch_count(r->cu) : -1; }
 
 /* Drop-in for dav1d_get_picture (ext/dav1d/src/lib.c:458): the DSP surface we replace is void,

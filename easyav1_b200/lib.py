@@ -23,7 +23,22 @@ def load_engine():
             raise EngineError("libeasyav1_cuda.so is not built (run __graft_entry__.build()); "
                               "there is no CPU fallback")
         _engine = C.CDLL(ENGINE_SO, mode=C.RTLD_GLOBAL)
-        _engine.eav1cu_launch_count.restype = C.c_longlong
+        E = _engine
+        E.eav1cu_launch_count.restype = C.c_longlong
+        E.eav1cu_launch_count.argtypes = [C.c_void_p]
+        E.eav1cu_counters.argtypes = [C.c_void_p, C.POINTER(C.c_longlong)]
+        E.eav1cu_set_capture.argtypes = [C.c_void_p, C.c_int]
+        E.eav1cu_staged_count.argtypes = [C.c_void_p]
+        E.eav1cu_staged_replay.argtypes = [C.c_void_p, C.c_int]
+        E.eav1cu_staged_info.argtypes = [C.c_void_p, C.c_int, C.POINTER(StagedInfo)]
+        E.eav1cu_set_stream.argtypes = [C.c_void_p, C.c_void_p]
+        E.eav1cu_set_stage_timing.argtypes = [C.c_void_p, C.c_int]
+        E.eav1cu_stage_times.argtypes = [C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_longlong),
+                                         C.POINTER(C.c_longlong), C.c_int]
+        E.eav1cu_sync.argtypes = [C.c_void_p]
+        E.eav1cu_pic_download.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_void_p),
+                                          C.POINTER(C.c_ssize_t)]
+        E.eav1cu_last_error.argtypes = [C.c_void_p, C.c_char_p, C.c_size_t]
     return _engine
 
 
@@ -38,6 +53,13 @@ def load_host(path=None):
             raise EngineError("libdav1d_b200.so is not built (run __graft_entry__.build())")
         _host = _bind_host(C.CDLL(HOST_SO, mode=C.RTLD_GLOBAL))
     return _host
+
+
+class StagedInfo(C.Structure):
+    _fields_ = [("cur", C.c_int), ("w", C.c_int), ("h", C.c_int), ("bpc", C.c_int), ("layout", C.c_int),
+                ("n_levels", C.c_int), ("n_chains", C.c_int), ("launches", C.c_int),
+                ("n_lf", C.c_int), ("n_lr", C.c_int), ("cdef", C.c_int), ("inter", C.c_int),
+                ("n_cmds", C.c_longlong), ("payload_bytes", C.c_longlong)]
 
 
 class StreamFrame(C.Structure):
@@ -59,4 +81,6 @@ def _bind_host(L):
     L.eav1rec_launches.restype = C.c_longlong
     L.eav1rec_launches.argtypes = [C.c_void_p]
     L.eav1rec_error.argtypes = [C.c_void_p]
+    L.eav1rec_engine.restype = C.c_void_p
+    L.eav1rec_engine.argtypes = [C.c_void_p]
     return L

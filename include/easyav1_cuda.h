@@ -227,6 +227,39 @@ int  eav1cu_arena_download(Eav1cuCtx *ctx, size_t off, void *dst, size_t bytes);
 /* Number of kernel launches issued so far by this context (bench.py's gpu_launches). */
 long long eav1cu_launch_count(Eav1cuCtx *ctx);
 
+/* Measurement support. With capture on, every frame passed to eav1cu_frame_submit also keeps
+ * a private device-resident copy of its work lists, so the frame can be re-launched with no
+ * host work and no host->device traffic (bench.py's `value` leg: inputs resident in HBM).
+ * Replaying the staged frames in submit order reproduces the original pictures, because each
+ * frame reads the same reference slots it read the first time. */
+typedef struct Eav1StagedInfo {
+    int cur, w, h, bpc, layout;
+    int n_levels, n_chains, launches;
+    int n_lf, n_lr, cdef, inter;
+    long long n_cmds, payload_bytes;
+} Eav1StagedInfo;
+/* sizeof() of the ABI structs as compiled (0 Eav1Cmd, 1 Eav1LfRec, 2 Eav1LrRec, 3 Eav1FrameDesc,
+ * 4 Eav1StagedInfo, 5 Eav1Tables), so bindings can verify their mirrors. */
+size_t eav1cu_abi_sizeof(int which);
+/* Host-only: the dependency levels eav1cu_frame_submit would give these commands. Chains
+ * (coding blocks) come back sorted by level; returns the number of chains. Needs no device. */
+int  eav1cu_plan_levels(const Eav1Cmd *cmds, size_t n_cmds, const int plane_w[3], const int plane_h[3],
+                        uint32_t *chain_first, uint32_t *chain_level, size_t cap);
+/* out[0] kernel launches, out[1] host->device bytes, out[2] device->host bytes, out[3] frames */
+int  eav1cu_counters(Eav1cuCtx *ctx, long long out[4]);
+int  eav1cu_set_capture(Eav1cuCtx *ctx, int on);
+/* Per-stage device time (CUDA events on the context's stream around each stage of every
+ * frame): index 0 reconstruction levels, 1 deblock, 2 CDEF, 3 loop restoration. Accumulated
+ * milliseconds, kernel launches and stage invocations since the last reset. */
+int  eav1cu_set_stage_timing(Eav1cuCtx *ctx, int on);
+int  eav1cu_stage_times(Eav1cuCtx *ctx, double ms[4], long long launches[4], long long calls[4], int reset);
+int  eav1cu_staged_count(Eav1cuCtx *ctx);
+int  eav1cu_staged_replay(Eav1cuCtx *ctx, int idx);
+int  eav1cu_staged_info(Eav1cuCtx *ctx, int idx, Eav1StagedInfo *out);
+/* Run on a caller-owned cudaStream_t (passed as void*) so the caller can record its own
+ * events around the launches; the context never destroys a stream it did not create. */
+int  eav1cu_set_stream(Eav1cuCtx *ctx, void *cuda_stream);
+
 #ifdef __cplusplus
 }
 #endif

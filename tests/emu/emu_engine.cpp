@@ -103,6 +103,19 @@ int eav1cu_frame_submit(Eav1cuCtx *c, const Eav1FrameDesc *fd, const Eav1Cmd *cm
                         const void *payload, size_t, size_t arena_bytes)
 {
     if (!c->have_tab) return EAV1CU_ERR_NOTABLES;
+    if (getenv("EAV1_EMU_NULL")) {  // host-cost profiling: record only
+        static size_t tot_cmds, tot_lf, tot_lr, frames;
+        tot_cmds += n; tot_lf += fd->n_lf_recs; tot_lr += fd->n_lr_recs; frames++;
+        if (getenv("EAV1_EMU_STATS")) {
+            size_t hist[16] = {0}, px[16] = {0};
+            for (size_t i = 0; i < n; i++) { hist[cmds[i].op & 15]++; px[cmds[i].op & 15] += (size_t)cmds[i].w * cmds[i].h; }
+            fprintf(stderr, "frame %zu cmds %zu lf %zu lr %zu cdef %d |", frames, n, (size_t)fd->n_lf_recs, (size_t)fd->n_lr_recs, fd->cdef_enable);
+            static const char *nm[] = {"nop","mc","warp","avg","wavg","mask","wmask","blend","blendv","blendh","ipred","cfl","pal","itx"};
+            for (int o = 1; o < 14; o++) if (hist[o]) fprintf(stderr, " %s %zu/%zuk", nm[o], hist[o], px[o] >> 10);
+            fprintf(stderr, "\n");
+        }
+        return 0;
+    }
     Picture &cur = c->pics[fd->cur];
     const bool has_cdef = fd->cdef_enable != 0, has_lr = fd->n_lr_recs > 0;
     Picture *A = &cur;

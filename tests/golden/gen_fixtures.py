@@ -158,7 +158,14 @@ CLIPS = {
     "cif_intra": (352, 288, 2, 12, {"enable-cdef": "1", "enable-restoration": "1"}, 55, 6),
     "cif_inter": (352, 288, 8, 13, {"enable-cdef": "1", "enable-restoration": "1"}, 55, 6),
     "c1_360p": (640, 360, 12, 1, {"enable-cdef": "1", "enable-restoration": "1"}, 55, 6),
-    "c2_1080p": (1920, 1080, 6, 7, {"enable-cdef": "1", "enable-restoration": "1"}, 55, 6),
+    "c2_1080p": (1920, 1080, 6, 7, {"enable-cdef": "1", "enable-restoration": "1"}, 60, 4, 6.0),
+    # slower encoder presets switch on the tools speed 6 never picks: loop restoration
+    # (Wiener + SGR), OBMC (blend_v/blend_h), wedge / inter-intra / diff-weighted masks
+    "cif_tools_s4": (352, 288, 7, 21, {"enable-cdef": "1", "enable-restoration": "1"}, 60, 4, 8.0),
+    "cif_tools_s2": (352, 288, 7, 22, {"enable-cdef": "1", "enable-restoration": "1"}, 50, 2, 10.0),
+    # the bench workload (BASELINE.json configs[1]): same recipe, 120 frames. Speed 4 because
+    # speed 6 never signals loop restoration on this content (checked from the recorded frames)
+    "c2_1080p_bench": (1920, 1080, 120, 7, {"enable-cdef": "1", "enable-restoration": "1"}, 60, 4, 6.0),
 }
 
 
@@ -166,10 +173,12 @@ def main():
     only = sys.argv[1:]
     manifest_path = os.path.join(HERE, "manifest.json")
     manifest = json.load(open(manifest_path)) if os.path.exists(manifest_path) else {}
-    for name, (w, h, n, seed, adv, q, spd) in CLIPS.items():
+    for name, spec in CLIPS.items():
+        w, h, n, seed, adv, q, spd = spec[:7]
+        noise = spec[7] if len(spec) > 7 else 3.0
         if only and name not in only:
             continue
-        frames = synth_frames(w, h, n, seed)
+        frames = synth_frames(w, h, n, seed, noise=noise)
         avif = encode(frames, adv, q, spd)
         samples = avif_samples(avif)
         ivf = os.path.join(HERE, name + ".ivf")
@@ -178,7 +187,7 @@ def main():
         g = golden_md5(obu)
         manifest[name] = {"file": name + ".ivf", "w": w, "h": h, "frames": g, "bytes": len(obu),
                           "encoder": "Pillow AVIF/aom", "advanced": adv, "quality": q, "speed": spd,
-                          "seed": seed}
+                          "seed": seed, "noise": noise}
         print(name, len(samples), "samples", len(obu), "bytes ->", len(g), "decoded frames",
               [x["frame_type"] for x in g])
     json.dump(manifest, open(manifest_path, "w"), indent=1, sort_keys=True)

@@ -18,21 +18,72 @@ using namespace eav1;
 
 // ------------------------------------------------------------------ kernels
 
+// One launch reconstructs a whole frame. CTAs draw chain tickets in decode order (which is a
+// topological order of the dependency graph, sched.h), wait until the listed producer chains
+// have published their done flag, run the chain, publish their own flag. A CTA only ever waits
+// for tickets smaller than its own, and those are held by CTAs that are already running, so the
+// kernel makes progress for any grid size. Flags hold the launch epoch, so they never need
+// clearing; ctrl[0] is the ticket counter, ctrl[1] counts retired CTAs (the last one re-arms both).
+struct ReconArgs {
+    const Eav1Cmd *cmds;
+    const Chain *chains;
+    const uint32_t *dep_start;
+    const uint32_t *deps;
+    uint32_t *done;
+    uint32_t *ctrl;
+    uint32_t n_chains;
+    uint32_t epoch;
+};
+
+__device__ __forceinline__ uint32_t ld_acquire(const uint32_t *p)
+{
+    uint32_t v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+
+__device__ __forceinline__ void st_release(uint32_t *p, uint32_t v)
+{
+    asm volatile("st.release.gpu.global.u32 [%0], %1;" :: "l"(p), "r"(v) : "memory");
+}
+
 template <typename BD>
 __global__ void __launch_bounds__(128)
-recon_level_kernel(FrameCtx fc, const Eav1Cmd *__restrict__ cmds, const Chain *__restrict__ chains)
+recon_frame_kernel(FrameCtx fc, ReconArgs ra)
 {
     __shared__ CtaScratch sm;
     __shared__ Eav1Cmd cur;
-    const Chain ch = chains[blockIdx.x];
-    for (uint32_t k = 0; k < ch.count; k++) {
-        // stage the command in shared memory (60 bytes = 15 words)
-        if (threadIdx.x < sizeof(Eav1Cmd) / 4)
-            reinterpret_cast<uint32_t *>(&cur)[threadIdx.x] =
-                reinterpret_cast<const uint32_t *>(&cmds[ch.first + k])[threadIdx.x];
+    __shared__ uint32_t s_ticket;
+    for (;;) {
+        if (threadIdx.x == 0) s_ticket = atomicAdd(&ra.ctrl[0], 1u);
         __syncthreads();
-        exec_cmd<BD>(fc, cur, sm, threadIdx.x, blockDim.x);
+        const uint32_t t = s_ticket;
+        if (t >= ra.n_chains) break;
+        const uint32_t d0 = ra.dep_start[t], d1 = ra.dep_start[t + 1];
+        for (uint32_t d = d0 + threadIdx.x; d < d1; d += blockDim.x) {
+            const uint32_t *flag = &ra.done[ra.deps[d]];
+            unsigned ns = 20;
+            while (ld_acquire(flag) != ra.epoch) { __nanosleep(ns); if (ns < 320) ns <<= 1; }
+        }
         __syncthreads();
+        const Chain ch = ra.chains[t];
+        for (uint32_t k = 0; k < ch.count; k++) {
+            // stage the command in shared memory (60 bytes = 15 words)
+            if (threadIdx.x < sizeof(Eav1Cmd) / 4)
+                reinterpret_cast<uint32_t *>(&cur)[threadIdx.x] =
+                    reinterpret_cast<const uint32_t *>(&ra.cmds[ch.first + k])[threadIdx.x];
+            __syncthreads();
+            exec_cmd<BD>(fc, cur, sm, threadIdx.x, blockDim.x);
+            __syncthreads();
+        }
+        if (threadIdx.x == 0) {
+            __threadfence();
+            st_release(&ra.done[t], ra.epoch);
+        }
+    }
+    if (threadIdx.x == 0) {
+        const uint32_t retired = atomicAdd(&ra.ctrl[1], 1u);
+        if (retired == gridDim.x - 1) { ra.ctrl[1] = 0; ra.ctrl[0] = 0; __threadfence(); }
     }
 }
 
@@ -90,8 +141,9 @@ struct FramePlan {
     Eav1FrameDesc fd;
     const Eav1Cmd *d_cmds = nullptr;
     const Chain *d_chains = nullptr;
+    const uint32_t *d_dep_start = nullptr, *d_deps = nullptr;
+    uint32_t n_chains = 0, n_deps = 0, n_levels = 0;
     const uint8_t *d_payload = nullptr;
-    std::vector<uint32_t> level_start;
     size_t arena_bytes = 0, payload_bytes = 0, n_cmds = 0;
     const Eav1LfRec *d_lf = nullptr; size_t n_lf0 = 0, n_lf1 = 0;
     const uint8_t *d_lflvl = nullptr;
@@ -112,7 +164,13 @@ struct Eav1cuCtx {
     Picture work[2];           // post-filter ping-pong pictures
     std::vector<Eav1LfRec> lf_sorted;
     Scheduler sched;
+    DepGraph graph;
     Schedule plan;
+    DevBuf depstart, deps;
+    uint32_t *d_done = nullptr; size_t done_cap = 0;
+    uint32_t *d_ctrl = nullptr;
+    uint32_t epoch = 0;
+    int recon_grid = 148 * 4;
     int err = 0;
     std::string errmsg;
     std::mutex mu;
@@ -216,9 +274,18 @@ int eav1cu_ctx_create(Eav1cuCtx **out, int device)
     ctx->device = device;
     if (cudaSetDevice(device) != cudaSuccess ||
         cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess ||
-        cudaMalloc(&ctx->d_tab, sizeof(Eav1Tables)) != cudaSuccess) {
+        cudaMalloc(&ctx->d_tab, sizeof(Eav1Tables)) != cudaSuccess ||
+        cudaMalloc(&ctx->d_ctrl, 64) != cudaSuccess || cudaMemset(ctx->d_ctrl, 0, 64) != cudaSuccess) {
         delete ctx;
         return EAV1CU_ERR_CUDA;
+    }
+    {
+        // persistent grid: every SM filled to the occupancy the kernel reaches (multiple of the SM count)
+        int sms = 148, per8 = 4, per16 = 4;
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per8, recon_frame_kernel<BD8>, 128, 0);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per16, recon_frame_kernel<BD16>, 128, 0);
+        ctx->recon_grid = sms * std::max(1, std::min(per8, per16));
     }
     *out = ctx;
     return 0;
@@ -233,6 +300,9 @@ void eav1cu_ctx_destroy(Eav1cuCtx *ctx)
     for (auto &p : ctx->work) if (p.base) cudaFree(p.base);
     free_buf(ctx->cmds); free_buf(ctx->chains); free_buf(ctx->payload); free_buf(ctx->arena);
     free_buf(ctx->lfrec); free_buf(ctx->lflvl); free_buf(ctx->lrrec); free_buf(ctx->lfmask);
+    free_buf(ctx->depstart); free_buf(ctx->deps);
+    if (ctx->d_done) cudaFree(ctx->d_done);
+    if (ctx->d_ctrl) cudaFree(ctx->d_ctrl);
     if (ctx->d_tab) cudaFree(ctx->d_tab);
     if (ctx->d_masks) cudaFree(ctx->d_masks);
     for (auto &sp : ctx->spans) { cudaEventDestroy(sp.a); cudaEventDestroy(sp.b); }
@@ -428,20 +498,35 @@ static int plan_build(Eav1cuCtx *ctx, FramePlan &pl, bool staged, const Eav1Fram
     }
     Uploader up{ctx, staged ? &pl : nullptr};
     const uint8_t *d;
-    pl.level_start.clear();
+    pl.n_chains = pl.n_deps = pl.n_levels = 0;
     pl.arena_bytes = arena_bytes; pl.payload_bytes = payload_bytes; pl.n_cmds = n_cmds;
     if (n_cmds) {
         int pw[3] = { cur.pl[0].w, cur.pl[1].w, cur.pl[2].w };
         int ph[3] = { cur.pl[0].h, cur.pl[1].h, cur.pl[2].h };
         ctx->sched.reset(pw, ph);
-        ctx->sched.build(cmds, n_cmds, ctx->plan);
+        ctx->sched.build_graph(cmds, n_cmds, ctx->graph);
+        const DepGraph &g = ctx->graph;
         if ((r = up.put(ctx->cmds, cmds, n_cmds * sizeof(Eav1Cmd), &d))) return r;
         pl.d_cmds = reinterpret_cast<const Eav1Cmd *>(d);
-        if ((r = up.put(ctx->chains, ctx->plan.chains.data(), ctx->plan.chains.size() * sizeof(Chain), &d))) return r;
+        if ((r = up.put(ctx->chains, g.chains.data(), g.chains.size() * sizeof(Chain), &d))) return r;
         pl.d_chains = reinterpret_cast<const Chain *>(d);
+        if ((r = up.put(ctx->depstart, g.dep_start.data(), g.dep_start.size() * 4, &d))) return r;
+        pl.d_dep_start = reinterpret_cast<const uint32_t *>(d);
+        // never hand the kernel a null list, even when no chain has a producer
+        static const uint32_t zero = 0;
+        if ((r = up.put(ctx->deps, g.deps.empty() ? &zero : g.deps.data(), std::max<size_t>(g.deps.size(), 1) * 4, &d))) return r;
+        pl.d_deps = reinterpret_cast<const uint32_t *>(d);
+        pl.n_chains = (uint32_t)g.chains.size(); pl.n_deps = (uint32_t)g.deps.size();
+        if (staged) { Scheduler::levels(g, ctx->plan); pl.n_levels = (uint32_t)ctx->plan.level_start.size() - 1; }
         if ((r = up.put(ctx->payload, payload, payload_bytes, &pl.d_payload))) return r;
         if ((r = ensure(ctx, ctx->arena, arena_bytes + 16, false))) return r;
-        pl.level_start = ctx->plan.level_start;
+        if (g.chains.size() > ctx->done_cap) {
+            if (ctx->d_done) { CK(cudaStreamSynchronize(ctx->stream)); cudaFree(ctx->d_done); ctx->d_done = nullptr; }
+            const size_t cap = g.chains.size() * 2 + 4096;
+            CK(cudaMalloc(&ctx->d_done, cap * 4));
+            CK(cudaMemsetAsync(ctx->d_done, 0, cap * 4, ctx->stream));
+            ctx->done_cap = cap;
+        }
     }
     if (fd->n_lf_recs) {
         // partition the recorded calls: all column-edge filters run before all row-edge filters
@@ -493,15 +578,16 @@ static int plan_launch(Eav1cuCtx *ctx, FramePlan &pl)
     fc.masks = ctx->d_masks;
     fc.arena = ctx->arena.d;
     fc.payload = pl.d_payload;
-    if (pl.level_start.size() > 1) {
-    StageTimer tm(ctx, 0);
-    for (size_t l = 0; l + 1 < pl.level_start.size(); l++) {
-        const uint32_t a = pl.level_start[l], b = pl.level_start[l + 1];
-        if (a == b) continue;
-        if (hbd) recon_level_kernel<BD16><<<b - a, 128, 0, st>>>(fc, pl.d_cmds, pl.d_chains + a);
-        else     recon_level_kernel<BD8><<<b - a, 128, 0, st>>>(fc, pl.d_cmds, pl.d_chains + a);
+    if (pl.n_chains) {
+        StageTimer tm(ctx, 0);
+        if (pl.n_chains > ctx->done_cap) return fail(ctx, EAV1CU_ERR_INVAL, "done-flag array smaller than the staged frame");
+        ReconArgs ra;
+        ra.cmds = pl.d_cmds; ra.chains = pl.d_chains; ra.dep_start = pl.d_dep_start; ra.deps = pl.d_deps;
+        ra.done = ctx->d_done; ra.ctrl = ctx->d_ctrl; ra.n_chains = pl.n_chains; ra.epoch = ++ctx->epoch;
+        const unsigned grid = std::min<unsigned>(pl.n_chains, (unsigned)ctx->recon_grid);
+        if (hbd) recon_frame_kernel<BD16><<<grid, 128, 0, st>>>(fc, ra);
+        else     recon_frame_kernel<BD8><<<grid, 128, 0, st>>>(fc, ra);
         ctx->n_launches++;
-    }
     }
 
     PfParams pp;
@@ -666,8 +752,8 @@ int eav1cu_staged_info(Eav1cuCtx *ctx, int idx, Eav1StagedInfo *out)
     const FramePlan &p = *ctx->staged[idx];
     memset(out, 0, sizeof(*out));
     out->cur = p.fd.cur; out->w = p.fd.w; out->h = p.fd.h; out->bpc = p.fd.bpc; out->layout = p.fd.layout;
-    out->n_levels = p.level_start.empty() ? 0 : (int)p.level_start.size() - 1;
-    out->n_chains = p.level_start.empty() ? 0 : (int)p.level_start.back();
+    out->n_levels = (int)p.n_levels;
+    out->n_chains = (int)p.n_chains;
     out->launches = (int)p.launches;
     out->n_lf = (int)(p.n_lf0 + p.n_lf1); out->n_lr = (int)p.n_lr;
     out->cdef = p.fd.cdef_enable;

@@ -196,11 +196,14 @@ def e2e_pass(host, obu, cap, buf):
 
 
 def stage_bytes(info, P):
-    """Algorithmic HBM bytes per frame and stage: recon = write P (+ read one
-    reference P on inter frames) + the coefficient/side payload actually shipped; each post
-    filter = read P + write P."""
-    recon = P + (P if info.inter else 0) + info.payload_bytes
-    return [recon, 2 * P if info.n_lf else 0, 2 * P if info.cdef else 0, 2 * P if info.n_lr else 0]
+    """Algorithmic HBM bytes per frame and stage (SURVEY.md §8(d), 8-bit samples). The
+    "residual + prediction" row (read ref P + coefs + write P) is split over our two kernels:
+    motion compensation reads one reference sample and writes one sample per predicted sample;
+    the dataflow kernel reads the coefficient/palette payload actually shipped and reads +
+    writes every sample its commands touch. Each post filter = read P + write P."""
+    mc = 2 * info.mc_px
+    recon = info.payload_bytes + 2 * info.unit_px
+    return [recon, 2 * P if info.n_lf else 0, 2 * P if info.cdef else 0, 2 * P if info.n_lr else 0, mc]
 
 
 def run_ours(args, man, obu):
@@ -298,7 +301,7 @@ def run_ours(args, man, obu):
         barrier()
         clk = clocks.stop()
         cnt1 = (C.c_longlong * 4)(); E.eav1cu_counters(eng, cnt1)
-        ms = (C.c_double * 4)(); ln = (C.c_longlong * 4)(); calls = (C.c_longlong * 4)()
+        ms = (C.c_double * 6)(); ln = (C.c_longlong * 6)(); calls = (C.c_longlong * 6)()
         E.eav1cu_stage_times(eng, ms, ln, calls, 1)
         E.eav1cu_set_stage_timing(eng, 0)
         assert last_frame_md5() == man["frames"][-1]["md5"], "timed replay differs from the golden MD5"
@@ -321,22 +324,22 @@ def run_ours(args, man, obu):
     e2e_t = max_over_ranks(time.perf_counter() - t_all0)
 
     # ---- roofline of the stage with the largest share of device time
-    tot_bytes = [0, 0, 0, 0]
+    tot_bytes = [0, 0, 0, 0, 0]
     for si in infos:
         sb = stage_bytes(si, P)
-        for k in range(4):
+        for k in range(5):
             tot_bytes[k] += sb[k]
-    names = ["recon_level_kernel (all dependency levels of a frame)", "deblock_kernel (cols+rows)",
-             "cdef_kernel", "lr_kernel (+ plane copy)"]
-    stage_ms = [ms[k] / args.steps for k in range(4)]          # per step (= per 120 frames)
-    dom = max(range(4), key=lambda k: stage_ms[k])
+    names = ["recon_frame_kernel (dataflow: intra, residual, compound, blend)", "deblock_kernel (cols+rows)",
+             "cdef_kernel", "lr_kernel (+ plane copy)", "mc_kernel (motion compensation)"]
+    stage_ms = [ms[k] / args.steps for k in range(5)]          # per step (= per 120 frames)
+    dom = max(range(5), key=lambda k: stage_ms[k])
     peak, peak_src = measured_peak()
     achieved = (tot_bytes[dom] / 1e9) / (stage_ms[dom] / 1e3) if stage_ms[dom] > 0 else 0.0
     stages = {names[k].split(" ")[0]: {"ms_per_step": round(stage_ms[k], 4),
                                        "launches_per_step": int(ln[k] // args.steps),
                                        "alg_bytes_per_step": int(tot_bytes[k]),
                                        "gbs": round((tot_bytes[k] / 1e9) / (stage_ms[k] / 1e3), 2) if stage_ms[k] > 0 else None}
-              for k in range(4)}
+              for k in range(5)}
     all_bytes = sum(tot_bytes)
     out = {
         "metric": METRIC, "value": world * n_frames * args.steps / (dev_ms / 1e3), "unit": UNIT,

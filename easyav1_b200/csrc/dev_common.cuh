@@ -14,7 +14,8 @@
 #define EAV1_DEV __device__ __forceinline__
 #define EAV1_DEVN __device__ __noinline__
 #define EAV1_DEVM __device__ __forceinline__
-#define CTA_SYNC() __syncthreads()
+// group barrier: a work group is either one warp (nthr == 32) or the whole CTA; `nthr` must be in scope
+#define CTA_SYNC() do { if (nthr <= 32) __syncwarp(); else __syncthreads(); } while (0)
 #define EAV1_LDG(p) __ldg(p)
 #else
 #define EAV1_DEV static inline
@@ -22,6 +23,8 @@
 #define EAV1_DEVM inline
 #define CTA_SYNC() ((void)0)
 #define EAV1_LDG(p) (*(p))
+struct alignas(8) uint2 { uint32_t x, y; };
+struct alignas(16) uint4 { uint32_t x, y, z, w; };
 #endif
 
 namespace eav1 {
@@ -45,6 +48,10 @@ struct FrameCtx {
 
 // Per-CTA shared scratch: the 64x64 int32 transform tile (odd pitch), or the MC
 // intermediate rows, or the intra edge/ac buffers -- never live at the same time.
+// A single warp working on commands of at most 32x32 pixels only touches the first
+// EAV1_WARP_SCRATCH bytes (32x33 int32 tile, (32+7)x32 int16 rows, the whole `ip` part), so four
+// warps of a CTA can each own such a slice.
+#define EAV1_WARP_SCRATCH 4224
 struct alignas(16) CtaScratch {
     union {
         int32_t itx[64 * 65];

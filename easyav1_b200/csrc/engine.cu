@@ -4,6 +4,7 @@
 #include <cuda_runtime.h>
 #include <stdio.h>
 #include <string.h>
+#include <stdlib.h>
 #include <mutex>
 #include <string>
 #include <vector>
@@ -24,14 +25,23 @@ using namespace eav1;
 // for tickets smaller than its own, and those are held by CTAs that are already running, so the
 // kernel makes progress for any grid size. Flags hold the launch epoch, so they never need
 // clearing; ctrl[0] is the ticket counter, ctrl[1] counts retired CTAs (the last one re-arms both).
+// What a worker needs to run one chain, fetched with a single 32-byte load once it holds a ticket.
+struct alignas(32) ChainRec {
+    uint32_t first, count;      // commands [first, first+count)
+    uint32_t dep_off, n_deps;   // producers: deps[dep_off .. dep_off+n_deps) (chain ids)
+    uint32_t id;                // this chain's id (index of its done flag)
+    uint32_t pad[3];            // pad[0]: some later unit waits for this one
+};
+
 struct ReconArgs {
     const Eav1Cmd *cmds;
-    const Chain *chains;
-    const uint32_t *dep_start;
     const uint32_t *deps;
+    const ChainRec *big;          // chains run by a whole CTA, in decode order
+    const ChainRec *small;        // chains run by one warp, in decode order
     uint32_t *done;
-    uint32_t *ctrl;
-    uint32_t n_chains;
+    uint32_t *ctrl;               // [0] big tickets, [1] small tickets, [2] retired workers
+    uint32_t n_big, n_small;
+    uint32_t n_big_ctas, n_workers;
     uint32_t epoch;
 };
 
@@ -47,43 +57,102 @@ __device__ __forceinline__ void st_release(uint32_t *p, uint32_t v)
     asm volatile("st.release.gpu.global.u32 [%0], %1;" :: "l"(p), "r"(v) : "memory");
 }
 
+#define EAV1_CMD_STAGE 4   // commands fetched into shared memory per round trip
+
+struct WorkerSmem {
+    Eav1Cmd cmd[EAV1_CMD_STAGE];
+    uint32_t ticket;
+};
+
+// One work group (a CTA of 128 threads or a single warp) draining one ticket list.
+template <typename BD>
+__device__ __forceinline__ void recon_worker(const FrameCtx &fc, const ReconArgs &ra, const ChainRec *recs,
+                                             uint32_t n_list, uint32_t *counter, CtaScratch &sm, WorkerSmem &ws,
+                                             int tid, int nthr)
+{
+    uint32_t next = 0;
+    if (tid == 0) next = atomicAdd(counter, 1u);
+    for (;;) {
+        if (tid == 0) ws.ticket = next;
+        CTA_SYNC();
+        const uint32_t k = ws.ticket;
+        if (k >= n_list) break;
+        const uint4 r0 = *reinterpret_cast<const uint4 *>(&recs[k]);
+        const uint32_t id = recs[k].id, fed = recs[k].pad[0];
+        // draw the following ticket now: the round trip hides behind this chain's work
+        if (tid == 0) next = atomicAdd(counter, 1u);
+        const uint32_t first = r0.x, count = r0.y, d0 = r0.z, nd = r0.w;
+        for (uint32_t d = tid; d < nd; d += nthr) {
+            const uint32_t *flag = &ra.done[ra.deps[d0 + d]];
+            unsigned ns = 20;
+            while (ld_acquire(flag) != ra.epoch) { __nanosleep(ns); if (ns < 320) ns <<= 1; }
+        }
+        if (nd) CTA_SYNC();
+        for (uint32_t base = 0; base < count; base += EAV1_CMD_STAGE) {
+            const uint32_t n = min(count - base, (uint32_t)EAV1_CMD_STAGE);
+            const uint32_t *src = reinterpret_cast<const uint32_t *>(&ra.cmds[first + base]);
+            uint32_t *dst = reinterpret_cast<uint32_t *>(ws.cmd);
+            for (uint32_t i = tid; i < n * (sizeof(Eav1Cmd) / 4); i += nthr) dst[i] = src[i];
+            CTA_SYNC();
+            for (uint32_t c = 0; c < n; c++) {
+                exec_cmd<BD>(fc, ws.cmd[c], sm, tid, nthr);
+                CTA_SYNC();
+            }
+        }
+        if (fed && tid == 0) {   // nobody polls the flag of a unit without consumers
+            __threadfence();
+            st_release(&ra.done[id], ra.epoch);
+        }
+    }
+    if (tid == 0) {
+        const uint32_t retired = atomicAdd(&ra.ctrl[2], 1u);
+        if (retired == ra.n_workers - 1) { ra.ctrl[0] = 0; ra.ctrl[1] = 0; ra.ctrl[2] = 0; __threadfence(); }
+    }
+}
+
 template <typename BD>
 __global__ void __launch_bounds__(128)
 recon_frame_kernel(FrameCtx fc, ReconArgs ra)
 {
-    __shared__ CtaScratch sm;
-    __shared__ Eav1Cmd cur;
-    __shared__ uint32_t s_ticket;
-    for (;;) {
-        if (threadIdx.x == 0) s_ticket = atomicAdd(&ra.ctrl[0], 1u);
-        __syncthreads();
-        const uint32_t t = s_ticket;
-        if (t >= ra.n_chains) break;
-        const uint32_t d0 = ra.dep_start[t], d1 = ra.dep_start[t + 1];
-        for (uint32_t d = d0 + threadIdx.x; d < d1; d += blockDim.x) {
-            const uint32_t *flag = &ra.done[ra.deps[d]];
-            unsigned ns = 20;
-            while (ld_acquire(flag) != ra.epoch) { __nanosleep(ns); if (ns < 320) ns <<= 1; }
-        }
-        __syncthreads();
-        const Chain ch = ra.chains[t];
-        for (uint32_t k = 0; k < ch.count; k++) {
-            // stage the command in shared memory (60 bytes = 15 words)
-            if (threadIdx.x < sizeof(Eav1Cmd) / 4)
-                reinterpret_cast<uint32_t *>(&cur)[threadIdx.x] =
-                    reinterpret_cast<const uint32_t *>(&ra.cmds[ch.first + k])[threadIdx.x];
-            __syncthreads();
-            exec_cmd<BD>(fc, cur, sm, threadIdx.x, blockDim.x);
-            __syncthreads();
-        }
-        if (threadIdx.x == 0) {
-            __threadfence();
-            st_release(&ra.done[t], ra.epoch);
-        }
+    __shared__ alignas(16) unsigned char scratch[4 * EAV1_WARP_SCRATCH > sizeof(CtaScratch) ? 4 * EAV1_WARP_SCRATCH : sizeof(CtaScratch)];
+    __shared__ WorkerSmem ws[4];
+    if (blockIdx.x < ra.n_big_ctas) {
+        recon_worker<BD>(fc, ra, ra.big, ra.n_big, &ra.ctrl[0], *reinterpret_cast<CtaScratch *>(scratch),
+                         ws[0], threadIdx.x, 128);
+    } else {
+        const int w = threadIdx.x >> 5;
+        recon_worker<BD>(fc, ra, ra.small, ra.n_small, &ra.ctrl[1],
+                         *reinterpret_cast<CtaScratch *>(scratch + w * EAV1_WARP_SCRATCH),
+                         ws[w], threadIdx.x & 31, 32);
     }
-    if (threadIdx.x == 0) {
-        const uint32_t retired = atomicAdd(&ra.ctrl[1], 1u);
-        if (retired == gridDim.x - 1) { ra.ctrl[1] = 0; ra.ctrl[0] = 0; __threadfence(); }
+}
+
+// Phase 1: motion compensation from reference pictures. One warp per work item (a block or a
+// 32x32 tile of it); items are independent, so this is a plain grid with no flags or tickets.
+template <typename BD>
+__global__ void __launch_bounds__(128)
+mc_kernel(FrameCtx fc, const Eav1Cmd *__restrict__ cmds, const uint32_t *__restrict__ items, uint32_t n_items)
+{
+    __shared__ alignas(16) unsigned char scratch[4 * EAV1_WARP_SCRATCH];
+    __shared__ Eav1Cmd cmd[4];
+    const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t it = blockIdx.x * 4 + w;
+    if (it >= n_items) return;
+    const uint32_t item = items[it];
+    const uint32_t ci = item & 0xffffff;
+    if (lane < (int)(sizeof(Eav1Cmd) / 4))
+        reinterpret_cast<uint32_t *>(&cmd[w])[lane] = reinterpret_cast<const uint32_t *>(&cmds[ci])[lane];
+    __syncwarp();
+    const Eav1Cmd &c = cmd[w];
+    CtaScratch &sm = *reinterpret_cast<CtaScratch *>(scratch + w * EAV1_WARP_SCRATCH);
+    if (c.op == EAV1_OP_MC) {
+        if (c.u.mc.dx) exec_mc_rect<BD>(fc, c, 0, 0, c.w, c.h, sm, lane, 32);
+        else {
+            const int x0 = (int)((item >> 24) & 3) * 32, y0 = (int)((item >> 26) & 3) * 32;
+            exec_mc_rect<BD>(fc, c, x0, y0, min(32, c.w - x0), min(32, c.h - y0), sm, lane, 32);
+        }
+    } else if (c.op == EAV1_OP_WARP) {
+        exec_warp<BD>(fc, c, sm, lane, 32);
     }
 }
 
@@ -140,9 +209,12 @@ struct DevBuf {
 struct FramePlan {
     Eav1FrameDesc fd;
     const Eav1Cmd *d_cmds = nullptr;
-    const Chain *d_chains = nullptr;
-    const uint32_t *d_dep_start = nullptr, *d_deps = nullptr;
-    uint32_t n_chains = 0, n_deps = 0, n_levels = 0;
+    const uint32_t *d_deps = nullptr, *d_items = nullptr;
+    const ChainRec *d_recs = nullptr;
+    uint32_t n_items = 0;
+    long long mc_px = 0, unit_px = 0;
+    uint32_t n_chains = 0, n_deps = 0, n_levels = 0, n_big = 0, n_small = 0;
+    double big_share = 0;
     const uint8_t *d_payload = nullptr;
     size_t arena_bytes = 0, payload_bytes = 0, n_cmds = 0;
     const Eav1LfRec *d_lf = nullptr; size_t n_lf0 = 0, n_lf1 = 0;
@@ -166,11 +238,15 @@ struct Eav1cuCtx {
     Scheduler sched;
     DepGraph graph;
     Schedule plan;
-    DevBuf depstart, deps;
+    DevBuf deps, recs, items;
+    UnitGraph units;
+    std::vector<ChainRec> rec_tmp;
+    std::vector<uint8_t> fed_tmp;
     uint32_t *d_done = nullptr; size_t done_cap = 0;
     uint32_t *d_ctrl = nullptr;
     uint32_t epoch = 0;
     int recon_grid = 148 * 4;
+    int warp_mode = 1;   // 0: every chain on a CTA, 1: independent small chains on warps, 2: all small chains on warps
     int err = 0;
     std::string errmsg;
     std::mutex mu;
@@ -181,8 +257,8 @@ struct Eav1cuCtx {
     struct Span { cudaEvent_t a, b; int stage; int launches; };
     std::vector<Span> spans;
     std::vector<cudaEvent_t> ev_pool;
-    double stage_ms[4] = {0, 0, 0, 0};
-    long long stage_launches[4] = {0, 0, 0, 0}, stage_calls[4] = {0, 0, 0, 0};
+    double stage_ms[EAV1CU_N_STAGES] = {};
+    long long stage_launches[EAV1CU_N_STAGES] = {}, stage_calls[EAV1CU_N_STAGES] = {};
     bool capture = false;
     FramePlan live;
     std::vector<FramePlan *> staged;
@@ -287,6 +363,7 @@ int eav1cu_ctx_create(Eav1cuCtx **out, int device)
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per16, recon_frame_kernel<BD16>, 128, 0);
         ctx->recon_grid = sms * std::max(1, std::min(per8, per16));
     }
+    if (const char *e = getenv("EAV1_WARP_MODE")) ctx->warp_mode = atoi(e);
     *out = ctx;
     return 0;
 }
@@ -300,7 +377,7 @@ void eav1cu_ctx_destroy(Eav1cuCtx *ctx)
     for (auto &p : ctx->work) if (p.base) cudaFree(p.base);
     free_buf(ctx->cmds); free_buf(ctx->chains); free_buf(ctx->payload); free_buf(ctx->arena);
     free_buf(ctx->lfrec); free_buf(ctx->lflvl); free_buf(ctx->lrrec); free_buf(ctx->lfmask);
-    free_buf(ctx->depstart); free_buf(ctx->deps);
+    free_buf(ctx->deps); free_buf(ctx->recs); free_buf(ctx->items);
     if (ctx->d_done) cudaFree(ctx->d_done);
     if (ctx->d_ctrl) cudaFree(ctx->d_ctrl);
     if (ctx->d_tab) cudaFree(ctx->d_tab);
@@ -504,25 +581,69 @@ static int plan_build(Eav1cuCtx *ctx, FramePlan &pl, bool staged, const Eav1Fram
         int pw[3] = { cur.pl[0].w, cur.pl[1].w, cur.pl[2].w };
         int ph[3] = { cur.pl[0].h, cur.pl[1].h, cur.pl[2].h };
         ctx->sched.reset(pw, ph);
-        ctx->sched.build_graph(cmds, n_cmds, ctx->graph);
-        const DepGraph &g = ctx->graph;
+        ctx->sched.build_units(cmds, n_cmds, ctx->units);
+        const UnitGraph &g = ctx->units;
         if ((r = up.put(ctx->cmds, cmds, n_cmds * sizeof(Eav1Cmd), &d))) return r;
         pl.d_cmds = reinterpret_cast<const Eav1Cmd *>(d);
-        if ((r = up.put(ctx->chains, g.chains.data(), g.chains.size() * sizeof(Chain), &d))) return r;
-        pl.d_chains = reinterpret_cast<const Chain *>(d);
-        if ((r = up.put(ctx->depstart, g.dep_start.data(), g.dep_start.size() * 4, &d))) return r;
-        pl.d_dep_start = reinterpret_cast<const uint32_t *>(d);
-        // never hand the kernel a null list, even when no chain has a producer
+        // never hand the kernel a null list, even when nothing has a producer
         static const uint32_t zero = 0;
         if ((r = up.put(ctx->deps, g.deps.empty() ? &zero : g.deps.data(), std::max<size_t>(g.deps.size(), 1) * 4, &d))) return r;
         pl.d_deps = reinterpret_cast<const uint32_t *>(d);
-        pl.n_chains = (uint32_t)g.chains.size(); pl.n_deps = (uint32_t)g.deps.size();
-        if (staged) { Scheduler::levels(g, ctx->plan); pl.n_levels = (uint32_t)ctx->plan.level_start.size() - 1; }
+        pl.n_items = (uint32_t)g.mc_items.size();
+        if (staged) {
+            pl.mc_px = pl.unit_px = 0;
+            for (uint32_t it : g.mc_items) {
+                const Eav1Cmd &c = cmds[it & 0xffffff];
+                const int x0 = (int)((it >> 24) & 3) * 32, y0 = (int)((it >> 26) & 3) * 32;
+                pl.mc_px += (c.op == EAV1_OP_MC && !c.u.mc.dx) ? (long long)std::min(32, c.w - x0) * std::min(32, c.h - y0) : (long long)c.w * c.h;
+            }
+            for (uint32_t ci : g.unit_cmd) pl.unit_px += (long long)cmds[ci].w * cmds[ci].h;
+        }
+        if (pl.n_items) {
+            if ((r = up.put(ctx->items, g.mc_items.data(), g.mc_items.size() * 4, &d))) return r;
+            pl.d_items = reinterpret_cast<const uint32_t *>(d);
+        }
+        pl.n_chains = (uint32_t)g.unit_cmd.size(); pl.n_deps = (uint32_t)g.deps.size();
+        if (staged) pl.n_levels = Scheduler::unit_levels(g);
+        if (pl.n_chains) {
+            // Two ticket lists, each in decode order. A unit runs on a single warp when it is at
+            // most 32x32 (scratch size) and neither waits for nor feeds another unit (only
+            // throughput matters); everything else gets a whole CTA (latency matters).
+            const size_t nc = g.unit_cmd.size();
+            std::vector<uint8_t> &fed = ctx->fed_tmp;
+            fed.assign(nc, 0);
+            for (uint32_t p : g.deps) fed[p] = 1;
+            std::vector<ChainRec> &rt = ctx->rec_tmp;
+            rt.resize(nc);
+            size_t nb = 0;
+            double px_big = 0, px_small = 0;
+            for (int pass = 0; pass < 2; pass++) {
+                size_t pos = pass ? nb : 0;
+                for (size_t u = 0; u < nc; u++) {
+                    const Eav1Cmd &c = cmds[g.unit_cmd[u]];
+                    const bool linked = fed[u] || g.dep_start[u + 1] != g.dep_start[u];
+                    bool big = c.w > 32 || c.h > 32;
+                    if (ctx->warp_mode == 0) big = true;
+                    else if (ctx->warp_mode == 1) big |= linked;
+                    if (big != (pass == 0)) continue;
+                    ChainRec &rc = rt[pos++];
+                    rc.first = g.unit_cmd[u]; rc.count = 1;
+                    rc.dep_off = g.dep_start[u]; rc.n_deps = g.dep_start[u + 1] - g.dep_start[u];
+                    rc.id = (uint32_t)u; rc.pad[0] = fed[u]; rc.pad[1] = rc.pad[2] = 0;
+                    if (big) px_big += (double)c.w * c.h; else px_small += (double)c.w * c.h;
+                }
+                if (!pass) nb = pos;
+            }
+            pl.n_big = (uint32_t)nb; pl.n_small = (uint32_t)(nc - nb);
+            pl.big_share = px_big + px_small > 0 ? px_big / (px_big + px_small) : 0;
+            if ((r = up.put(ctx->recs, rt.data(), rt.size() * sizeof(ChainRec), &d))) return r;
+            pl.d_recs = reinterpret_cast<const ChainRec *>(d);
+        } else { pl.n_big = pl.n_small = 0; }
         if ((r = up.put(ctx->payload, payload, payload_bytes, &pl.d_payload))) return r;
         if ((r = ensure(ctx, ctx->arena, arena_bytes + 16, false))) return r;
-        if (g.chains.size() > ctx->done_cap) {
+        if (g.unit_cmd.size() > ctx->done_cap) {
             if (ctx->d_done) { CK(cudaStreamSynchronize(ctx->stream)); cudaFree(ctx->d_done); ctx->d_done = nullptr; }
-            const size_t cap = g.chains.size() * 2 + 4096;
+            const size_t cap = g.unit_cmd.size() * 2 + 4096;
             CK(cudaMalloc(&ctx->d_done, cap * 4));
             CK(cudaMemsetAsync(ctx->d_done, 0, cap * 4, ctx->stream));
             ctx->done_cap = cap;
@@ -578,13 +699,29 @@ static int plan_launch(Eav1cuCtx *ctx, FramePlan &pl)
     fc.masks = ctx->d_masks;
     fc.arena = ctx->arena.d;
     fc.payload = pl.d_payload;
+    if (pl.n_items) {
+        StageTimer tm(ctx, 4);
+        const unsigned grid = (pl.n_items + 3) / 4;
+        if (hbd) mc_kernel<BD16><<<grid, 128, 0, st>>>(fc, pl.d_cmds, pl.d_items, pl.n_items);
+        else     mc_kernel<BD8><<<grid, 128, 0, st>>>(fc, pl.d_cmds, pl.d_items, pl.n_items);
+        ctx->n_launches++;
+    }
     if (pl.n_chains) {
         StageTimer tm(ctx, 0);
         if (pl.n_chains > ctx->done_cap) return fail(ctx, EAV1CU_ERR_INVAL, "done-flag array smaller than the staged frame");
         ReconArgs ra;
-        ra.cmds = pl.d_cmds; ra.chains = pl.d_chains; ra.dep_start = pl.d_dep_start; ra.deps = pl.d_deps;
-        ra.done = ctx->d_done; ra.ctrl = ctx->d_ctrl; ra.n_chains = pl.n_chains; ra.epoch = ++ctx->epoch;
-        const unsigned grid = std::min<unsigned>(pl.n_chains, (unsigned)ctx->recon_grid);
+        ra.cmds = pl.d_cmds; ra.deps = pl.d_deps;
+        ra.done = ctx->d_done; ra.ctrl = ctx->d_ctrl; ra.epoch = ++ctx->epoch;
+        ra.big = pl.d_recs; ra.small = pl.d_recs + pl.n_big;
+        ra.n_big = pl.n_big; ra.n_small = pl.n_small;
+        // CTAs are split between the two kinds in proportion to their pixel work
+        unsigned grid = (unsigned)ctx->recon_grid;
+        unsigned big_ctas = pl.n_big ? std::max(1u, (unsigned)(grid * pl.big_share + 0.5)) : 0;
+        big_ctas = std::min(big_ctas, pl.n_big);
+        unsigned small_ctas = pl.n_small ? std::min<unsigned>((pl.n_small + 3) / 4, std::max(1u, grid - std::min(grid - 1, big_ctas))) : 0;
+        if (!pl.n_small) big_ctas = std::min<unsigned>(pl.n_big, grid);
+        grid = big_ctas + small_ctas;
+        ra.n_big_ctas = big_ctas; ra.n_workers = big_ctas + 4 * small_ctas;
         if (hbd) recon_frame_kernel<BD16><<<grid, 128, 0, st>>>(fc, ra);
         else     recon_frame_kernel<BD8><<<grid, 128, 0, st>>>(fc, ra);
         ctx->n_launches++;
@@ -706,7 +843,7 @@ int eav1cu_set_stage_timing(Eav1cuCtx *ctx, int on)
     return 0;
 }
 
-int eav1cu_stage_times(Eav1cuCtx *ctx, double ms[4], long long launches[4], long long calls[4], int reset)
+int eav1cu_stage_times(Eav1cuCtx *ctx, double *ms, long long *launches, long long *calls, int reset)
 {
     if (!ctx) return EAV1CU_ERR_INVAL;
     CK(cudaSetDevice(ctx->device));
@@ -721,7 +858,7 @@ int eav1cu_stage_times(Eav1cuCtx *ctx, double ms[4], long long launches[4], long
         ctx->ev_pool.push_back(sp.a); ctx->ev_pool.push_back(sp.b);
     }
     ctx->spans.clear();
-    for (int i = 0; i < 4; i++) {
+    for (int i = 0; i < EAV1CU_N_STAGES; i++) {
         if (ms) ms[i] = ctx->stage_ms[i];
         if (launches) launches[i] = ctx->stage_launches[i];
         if (calls) calls[i] = ctx->stage_calls[i];
@@ -754,6 +891,8 @@ int eav1cu_staged_info(Eav1cuCtx *ctx, int idx, Eav1StagedInfo *out)
     out->cur = p.fd.cur; out->w = p.fd.w; out->h = p.fd.h; out->bpc = p.fd.bpc; out->layout = p.fd.layout;
     out->n_levels = (int)p.n_levels;
     out->n_chains = (int)p.n_chains;
+    out->n_big = (int)p.n_big; out->n_small = (int)p.n_small;
+    out->n_mc_items = (int)p.n_items; out->mc_px = p.mc_px; out->unit_px = p.unit_px;
     out->launches = (int)p.launches;
     out->n_lf = (int)(p.n_lf0 + p.n_lf1); out->n_lr = (int)p.n_lr;
     out->cdef = p.fd.cdef_enable;

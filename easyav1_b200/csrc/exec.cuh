@@ -10,6 +10,62 @@
 
 namespace eav1 {
 
+// Motion compensation of the sub-rectangle (x0,y0,w,h) of command c (whole block, or one
+// 32x32 tile of it when the block is spread over several warps).
+template <typename BD>
+EAV1_DEV void exec_mc_rect(const FrameCtx &fc, const Eav1Cmd &c, int x0, int y0, int w, int h,
+                           CtaScratch &sm, int tid, int nthr)
+{
+    typedef typename BD::pixel pixel;
+    pixel *dst8 = nullptr;
+    int16_t *dst16 = nullptr;
+    int dstride;
+    if (c.flags & EAV1_F_DST_ARENA) {
+        dstride = c.dst_stride;
+        if (c.flags & EAV1_F_PREP) dst16 = reinterpret_cast<int16_t *>(fc.arena + c.dst_off) + y0 * dstride + x0;
+        else dst8 = reinterpret_cast<pixel *>(fc.arena + c.dst_off) + y0 * dstride + x0;
+    } else {
+        const Plane &pl = fc.cur[c.plane];
+        dst8 = px_at<pixel>(pl, c.x + x0, c.y + y0);
+        dstride = pl.stride / (int)sizeof(pixel);
+    }
+    const Plane &rp = fc.ref[c.u.mc.ref][c.plane];
+    SrcView<pixel> src;
+    src.p = rp.p; src.stride = rp.stride;
+    src.iw = c.u.mc.iw; src.ih = c.u.mc.ih;
+    if (c.u.mc.dx)   // scaled references are never tiled (x0 == y0 == 0)
+        mc_scaled_block<BD>(fc.tab, src, c.u.mc.sx, c.u.mc.sy, w, h, c.u.mc.mx, c.u.mc.my,
+                            c.u.mc.dx, c.u.mc.dy, c.u.mc.filt_h, c.u.mc.filt_v, dst8, dst16, dstride,
+                            fc.bitdepth_max, tid, nthr);
+    else
+        mc_block<BD>(fc.tab, src, c.u.mc.sx + x0, c.u.mc.sy + y0, w, h, c.w, c.h, c.u.mc.mx, c.u.mc.my,
+                     c.u.mc.filt_h, c.u.mc.filt_v, dst8, dst16, dstride, fc.bitdepth_max, sm.mc_mid, tid, nthr);
+}
+
+template <typename BD>
+EAV1_DEV void exec_warp(const FrameCtx &fc, const Eav1Cmd &c, CtaScratch &sm, int tid, int nthr)
+{
+    typedef typename BD::pixel pixel;
+    pixel *dst8 = nullptr;
+    int16_t *dst16 = nullptr;
+    int dstride;
+    if (c.flags & EAV1_F_DST_ARENA) {
+        dstride = c.dst_stride;
+        if (c.flags & EAV1_F_PREP) dst16 = reinterpret_cast<int16_t *>(fc.arena + c.dst_off);
+        else dst8 = reinterpret_cast<pixel *>(fc.arena + c.dst_off);
+    } else {
+        const Plane &pl = fc.cur[c.plane];
+        dst8 = px_at<pixel>(pl, c.x, c.y);
+        dstride = pl.stride / (int)sizeof(pixel);
+    }
+    const Plane &rp = fc.ref[c.u.warp.ref][c.plane];
+    SrcView<pixel> src;
+    src.p = rp.p; src.stride = rp.stride;
+    src.iw = c.u.warp.iw; src.ih = c.u.warp.ih;
+    warp8x8_block<BD>(fc.tab, src, c.u.warp.sx, c.u.warp.sy, c.u.warp.abcd, c.u.warp.mx, c.u.warp.my,
+                      dst8, dst16, dstride, fc.bitdepth_max, sm.mc_mid, tid, nthr);
+}
+
 template <typename BD>
 EAV1_DEV void exec_cmd(const FrameCtx &fc, const Eav1Cmd &c, CtaScratch &sm, int tid, int nthr)
 {
@@ -29,29 +85,12 @@ EAV1_DEV void exec_cmd(const FrameCtx &fc, const Eav1Cmd &c, CtaScratch &sm, int
         dstride = pl.stride / (int)sizeof(pixel);
     }
     switch (c.op) {
-    case EAV1_OP_MC: {
-        const Plane &rp = fc.ref[c.u.mc.ref][c.plane];
-        SrcView<pixel> src;
-        src.p = rp.p; src.stride = rp.stride;
-        src.iw = c.u.mc.iw; src.ih = c.u.mc.ih;
-        if (c.u.mc.dx)
-            mc_scaled_block<BD>(fc.tab, src, c.u.mc.sx, c.u.mc.sy, c.w, c.h, c.u.mc.mx, c.u.mc.my,
-                                c.u.mc.dx, c.u.mc.dy, c.u.mc.filt_h, c.u.mc.filt_v, dst8, dst16, dstride,
-                                bdmax, tid, nthr);
-        else
-            mc_block<BD>(fc.tab, src, c.u.mc.sx, c.u.mc.sy, c.w, c.h, c.u.mc.mx, c.u.mc.my,
-                         c.u.mc.filt_h, c.u.mc.filt_v, dst8, dst16, dstride, bdmax, sm.mc_mid, tid, nthr);
+    case EAV1_OP_MC:
+        exec_mc_rect<BD>(fc, c, 0, 0, c.w, c.h, sm, tid, nthr);
         break;
-    }
-    case EAV1_OP_WARP: {
-        const Plane &rp = fc.ref[c.u.warp.ref][c.plane];
-        SrcView<pixel> src;
-        src.p = rp.p; src.stride = rp.stride;
-        src.iw = c.u.warp.iw; src.ih = c.u.warp.ih;
-        warp8x8_block<BD>(fc.tab, src, c.u.warp.sx, c.u.warp.sy, c.u.warp.abcd, c.u.warp.mx, c.u.warp.my,
-                          dst8, dst16, dstride, bdmax, sm.mc_mid, tid, nthr);
+    case EAV1_OP_WARP:
+        exec_warp<BD>(fc, c, sm, tid, nthr);
         break;
-    }
     case EAV1_OP_AVG:
         comp_avg<BD>(dst8, dstride, (const int16_t *)(fc.arena + c.u.comp.t1), (const int16_t *)(fc.arena + c.u.comp.t2),
                      c.w, c.h, bdmax, tid, nthr);

@@ -139,7 +139,7 @@ EAV1_DEV void edge_upsample(uint16_t *out, int hsz, const uint16_t *in, int from
 // Predict a w x h block into dst (stride in pixels) from the edge array (edge[EDGE_C] = top-left).
 // edge2 is scratch of the same size.
 template <typename pixel>
-EAV1_DEV void ipred_block(const Eav1Tables *tab, pixel *dst, int stride, uint16_t *edge, uint16_t *edge2,
+EAV1_DEVN void ipred_block(const Eav1Tables *tab, pixel *dst, int stride, uint16_t *edge, uint16_t *edge2,
                           int mode, int w, int h, int angle_in, int max_w, int max_h,
                           int bitdepth_max, int tid, int nthr)
 {

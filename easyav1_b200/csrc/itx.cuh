@@ -489,7 +489,7 @@ EAV1_DEV TxDim tx_dim(int tx) {
 
 // dst += inverse_transform(coef). `s` is the CTA's shared tile (>= 64*65 int32).
 template <typename BD>
-EAV1_DEV void itx_add(typename BD::pixel *dst, int dst_stride /*pixels*/, const typename BD::coef *coeff,
+EAV1_DEVN void itx_add(typename BD::pixel *dst, int dst_stride /*pixels*/, const typename BD::coef *coeff,
                       int eob, int tx, int txtp, int bitdepth_max, int32_t *s, int tid, int nthr)
 {
     typedef typename BD::wide W;

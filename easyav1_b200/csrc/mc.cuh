@@ -46,11 +46,191 @@ EAV1_DEV int tap8_v(const SrcView<pixel> &s, int x, int y, const int8_t *f) {
     return sum;
 }
 
+
+// ---- 8-bit fast path helpers -------------------------------------------------------------
+// 32 bits starting `sh` bits into the 64-bit value hi:lo (sh in 0,8,16,24)
+EAV1_DEV uint32_t funnel_r(uint32_t lo, uint32_t hi, int sh) {
+#if defined(__CUDA_ARCH__)
+    return __funnelshift_r(lo, hi, sh);
+#else
+    return (uint32_t)((((uint64_t)hi << 32) | lo) >> sh);
+#endif
+}
+// acc + sum of four (unsigned pixel byte) x (signed filter byte) products
+EAV1_DEV int dot4_us(uint32_t px4, uint32_t f4, int acc) {
+#if defined(__CUDA_ARCH__)
+    int d;
+    asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(px4), "r"(f4), "r"(acc));
+    return d;
+#else
+    for (int k = 0; k < 4; k++) acc += (int)((px4 >> (8 * k)) & 0xff) * (int)(int8_t)((f4 >> (8 * k)) & 0xff);
+    return acc;
+#endif
+}
+
+// 16 pixels of row y starting at the 4-aligned column xa, as four little-endian words.
+// `inside` promises the addressed window needs no edge replication.
+EAV1_DEV void fetch16(const SrcView<uint8_t> &s, int xa, int y, bool inside, uint32_t W[4]) {
+    if (inside) {
+        const uint32_t *p = reinterpret_cast<const uint32_t *>(s.p + (ptrdiff_t)y * s.stride + xa);
+        W[0] = p[0]; W[1] = p[1]; W[2] = p[2]; W[3] = p[3];
+    } else {
+#pragma unroll
+        for (int i = 0; i < 4; i++)
+            W[i] = (uint32_t)s.at(xa + 4 * i, y) | ((uint32_t)s.at(xa + 4 * i + 1, y) << 8) |
+                   ((uint32_t)s.at(xa + 4 * i + 2, y) << 16) | ((uint32_t)s.at(xa + 4 * i + 3, y) << 24);
+    }
+}
+// 4 pixels at (x..x+3, y) as one word
+EAV1_DEV uint32_t fetch4(const SrcView<uint8_t> &s, int x, int y, bool inside) {
+    if (inside) {
+        const int a = x & 3;
+        const uint32_t *p = reinterpret_cast<const uint32_t *>(s.p + (ptrdiff_t)y * s.stride + (x - a));
+        const uint32_t lo = p[0];
+        return a ? funnel_r(lo, p[1], 8 * a) : lo;
+    }
+    return (uint32_t)s.at(x, y) | ((uint32_t)s.at(x + 1, y) << 8) | ((uint32_t)s.at(x + 2, y) << 16) |
+           ((uint32_t)s.at(x + 3, y) << 24);
+}
+// horizontal 8-tap on 4 adjacent outputs whose first tap sits at column x0 of row y
+EAV1_DEV void hfilt4(const SrcView<uint8_t> &s, int x0, int y, bool inside, uint32_t f0, uint32_t f1, int sum[4]) {
+    const int a = x0 & 3;
+    uint32_t W[4];
+    fetch16(s, x0 - a, y, inside, W);
+    const int sh = 8 * a;
+    const uint32_t v0 = funnel_r(W[0], W[1], sh), v1 = funnel_r(W[1], W[2], sh), v2 = funnel_r(W[2], W[3], sh);
+#pragma unroll
+    for (int j = 0; j < 4; j++)
+        sum[j] = dot4_us(funnel_r(v0, v1, 8 * j), f0, dot4_us(funnel_r(v1, v2, 8 * j), f1, 0));
+}
+EAV1_DEV void store4_px(uint8_t *d, const int v[4]) {
+    const uint32_t w = (uint32_t)v[0] | ((uint32_t)v[1] << 8) | ((uint32_t)v[2] << 16) | ((uint32_t)v[3] << 24);
+    if (((uintptr_t)d & 3) == 0) *reinterpret_cast<uint32_t *>(d) = w;
+    else { d[0] = (uint8_t)v[0]; d[1] = (uint8_t)v[1]; d[2] = (uint8_t)v[2]; d[3] = (uint8_t)v[3]; }
+}
+EAV1_DEV void store4_i16(int16_t *d, const int v[4]) {
+    // prep destinations are 8-byte aligned (arena offsets are 16-aligned, strides multiples of 4)
+    uint2 w;
+    w.x = (uint32_t)(uint16_t)v[0] | ((uint32_t)(uint16_t)v[1] << 16);
+    w.y = (uint32_t)(uint16_t)v[2] | ((uint32_t)(uint16_t)v[3] << 16);
+    *reinterpret_cast<uint2 *>(d) = w;
+}
+
+// 8-bit put/prep for w >= 4, four horizontally adjacent samples per work item. Arithmetic is
+// the reference's (mc_tmpl.c:130-187, :247-306) with intermediate_bits = 4 and no prep bias.
+EAV1_DEVN void mc_block8_fast(const Eav1Tables *tab, const SrcView<uint8_t> &src, int sx, int sy,
+                             int w, int h, int fw, int fh, int mx, int my, int filt_h, int filt_v,
+                             uint8_t *dst8, int16_t *dst16, int dstride, int16_t *mid, int tid, int nthr)
+{
+    const int lq = ulog2((unsigned)w) - 2, qmask = (1 << lq) - 1;     // quads per row = 1 << lq
+    const bool inside = sx >= 3 && sy >= 3 && sx + w + 12 <= src.iw && sy + h + 4 <= src.ih;
+    uint32_t fh0 = 0, fh1 = 0;
+    int fv[8];
+    if (mx) {
+        const uint32_t *f = reinterpret_cast<const uint32_t *>(subpel_filter(tab, filt_h, mx, fw));
+        fh0 = f[0]; fh1 = f[1];
+    }
+    if (my) {
+        const int8_t *f = subpel_filter(tab, filt_v, my, fh);
+#pragma unroll
+        for (int k = 0; k < 8; k++) fv[k] = f[k];
+    }
+    if (!mx && !my) {
+        for (int it = tid; it < (h << lq); it += nthr) {
+            const int y = it >> lq, x = (it & qmask) << 2;
+            const uint32_t v = fetch4(src, sx + x, sy + y, inside);
+            int o[4];
+#pragma unroll
+            for (int j = 0; j < 4; j++) o[j] = (int)((v >> (8 * j)) & 0xff);
+            if (dst8) store4_px(dst8 + y * dstride + x, o);
+            else {
+#pragma unroll
+                for (int j = 0; j < 4; j++) o[j] <<= 4;
+                store4_i16(dst16 + y * dstride + x, o);
+            }
+        }
+    } else if (mx && !my) {
+        for (int it = tid; it < (h << lq); it += nthr) {
+            const int y = it >> lq, x = (it & qmask) << 2;
+            int sum[4];
+            hfilt4(src, sx + x - 3, sy + y, inside, fh0, fh1, sum);
+            if (dst8) {
+#pragma unroll
+                for (int j = 0; j < 4; j++) sum[j] = iclip((sum[j] + 34) >> 6, 0, 255);
+                store4_px(dst8 + y * dstride + x, sum);
+            } else {
+#pragma unroll
+                for (int j = 0; j < 4; j++) sum[j] = (sum[j] + 2) >> 2;
+                store4_i16(dst16 + y * dstride + x, sum);
+            }
+        }
+    } else if (!mx) {
+        for (int it = tid; it < (h << lq); it += nthr) {
+            const int y = it >> lq, x = (it & qmask) << 2;
+            int sum[4] = { 0, 0, 0, 0 };
+#pragma unroll
+            for (int k = 0; k < 8; k++) {
+                const uint32_t v = fetch4(src, sx + x, sy + y + k - 3, inside);
+#pragma unroll
+                for (int j = 0; j < 4; j++) sum[j] += fv[k] * (int)((v >> (8 * j)) & 0xff);
+            }
+            if (dst8) {
+#pragma unroll
+                for (int j = 0; j < 4; j++) sum[j] = iclip((sum[j] + 32) >> 6, 0, 255);
+                store4_px(dst8 + y * dstride + x, sum);
+            } else {
+#pragma unroll
+                for (int j = 0; j < 4; j++) sum[j] = (sum[j] + 2) >> 2;
+                store4_i16(dst16 + y * dstride + x, sum);
+            }
+        }
+    } else {
+        for (int y0 = 0; y0 < h; y0 += 32) {
+            const int th = imin(32, h - y0);
+            for (int it = tid; it < ((th + 7) << lq); it += nthr) {
+                const int r = it >> lq, x = (it & qmask) << 2;
+                int sum[4];
+                hfilt4(src, sx + x - 3, sy + y0 + r - 3, inside, fh0, fh1, sum);
+#pragma unroll
+                for (int j = 0; j < 4; j++) sum[j] = (sum[j] + 2) >> 2;
+                store4_i16(mid + r * w + x, sum);
+            }
+            CTA_SYNC();
+            for (int it = tid; it < (th << lq); it += nthr) {
+                const int r = it >> lq, x = (it & qmask) << 2;
+                int sum[4] = { 0, 0, 0, 0 };
+#pragma unroll
+                for (int k = 0; k < 8; k++) {
+                    const uint2 m = *reinterpret_cast<const uint2 *>(mid + (r + k) * w + x);
+                    sum[0] += fv[k] * (int)(int16_t)(m.x & 0xffff);
+                    sum[1] += fv[k] * (int)(int16_t)(m.x >> 16);
+                    sum[2] += fv[k] * (int)(int16_t)(m.y & 0xffff);
+                    sum[3] += fv[k] * (int)(int16_t)(m.y >> 16);
+                }
+                if (dst8) {
+#pragma unroll
+                    for (int j = 0; j < 4; j++) sum[j] = iclip((sum[j] + 512) >> 10, 0, 255);
+                    store4_px(dst8 + (y0 + r) * dstride + x, sum);
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 4; j++) sum[j] = (sum[j] + 32) >> 6;
+                    store4_i16(dst16 + (y0 + r) * dstride + x, sum);
+                }
+            }
+            CTA_SYNC();
+        }
+        return;
+    }
+    CTA_SYNC();
+}
+
 // Unscaled put/prep. dst8 (pixels) xor dst16 (prep) receives a w x h block with the given
 // stride (elements). `mid` is CTA scratch of at least (32+7)*128 int16.
+// (w,h) is the rectangle produced; (fw,fh) the dimensions of the whole prediction block, which
+// select the 4-tap or 8-tap filter set -- they differ when a block is produced tile by tile.
 template <typename BD>
-EAV1_DEV void mc_block(const Eav1Tables *tab, const SrcView<typename BD::pixel> &src, int sx, int sy,
-                       int w, int h, int mx, int my, int filt_h, int filt_v,
+EAV1_DEVN void mc_block(const Eav1Tables *tab, const SrcView<typename BD::pixel> &src, int sx, int sy,
+                       int w, int h, int fw, int fh, int mx, int my, int filt_h, int filt_v,
                        typename BD::pixel *dst8, int16_t *dst16, int dstride,
                        int bitdepth_max, int16_t *mid, int tid, int nthr)
 {
@@ -58,6 +238,12 @@ EAV1_DEV void mc_block(const Eav1Tables *tab, const SrcView<typename BD::pixel> 
     const int ib = intermediate_bits(bitdepth_max);
     const int bias = PrepBias<BD>::v;
     const bool bilin = filt_h == 3;
+    if constexpr (!BD::hbd) {
+        if (w >= 4 && !bilin && (!dst16 || (dstride & 3) == 0)) {
+            mc_block8_fast(tab, src, sx, sy, w, h, fw, fh, mx, my, filt_h, filt_v, dst8, dst16, dstride, mid, tid, nthr);
+            return;
+        }
+    }
     if (!mx && !my) {
         for (int i = tid; i < w * h; i += nthr) {
             const int y = i / w, x = i - y * w;
@@ -108,15 +294,15 @@ EAV1_DEV void mc_block(const Eav1Tables *tab, const SrcView<typename BD::pixel> 
         }
         return;
     }
-    const int8_t *fh = mx ? subpel_filter(tab, filt_h, mx, w) : nullptr;
-    const int8_t *fv = my ? subpel_filter(tab, filt_v, my, h) : nullptr;
-    if (fh && fv) {
+    const int8_t *fh_ = mx ? subpel_filter(tab, filt_h, mx, fw) : nullptr;
+    const int8_t *fv = my ? subpel_filter(tab, filt_v, my, fh) : nullptr;
+    if (fh_ && fv) {
         const int sh1 = 6 - ib, r1 = (1 << sh1) >> 1;
         for (int y0 = 0; y0 < h; y0 += 32) {
             const int th = imin(32, h - y0);
             for (int i = tid; i < (th + 7) * w; i += nthr) {
                 const int r = i / w, x = i - r * w;
-                mid[i] = (int16_t)((tap8_h(src, sx + x, sy + y0 + r - 3, fh) + r1) >> sh1);
+                mid[i] = (int16_t)((tap8_h(src, sx + x, sy + y0 + r - 3, fh_) + r1) >> sh1);
             }
             CTA_SYNC();
             for (int i = tid; i < th * w; i += nthr) {
@@ -133,8 +319,8 @@ EAV1_DEV void mc_block(const Eav1Tables *tab, const SrcView<typename BD::pixel> 
     }
     for (int i = tid; i < w * h; i += nthr) {
         const int y = i / w, x = i - y * w;
-        if (fh) {
-            const int sum = tap8_h(src, sx + x, sy + y, fh);
+        if (fh_) {
+            const int sum = tap8_h(src, sx + x, sy + y, fh_);
             if (dst8) dst8[y * dstride + x] = (pixel)iclip((sum + 32 + ((1 << (6 - ib)) >> 1)) >> 6, 0, bitdepth_max);
             else dst16[y * dstride + x] = (int16_t)(((sum + ((1 << (6 - ib)) >> 1)) >> (6 - ib)) - bias);
         } else {
@@ -149,7 +335,7 @@ EAV1_DEV void mc_block(const Eav1Tables *tab, const SrcView<typename BD::pixel> 
 // Scaled put/prep: (mx,my) are 1/1024 positions of sample (0,0), (dx,dy) the per-sample steps.
 // (sx,sy) addresses the sample the reference's `src` pointer points at.
 template <typename BD>
-EAV1_DEV void mc_scaled_block(const Eav1Tables *tab, const SrcView<typename BD::pixel> &src, int sx, int sy,
+EAV1_DEVN void mc_scaled_block(const Eav1Tables *tab, const SrcView<typename BD::pixel> &src, int sx, int sy,
                               int w, int h, int mx, int my, int dx, int dy, int filt_h, int filt_v,
                               typename BD::pixel *dst8, int16_t *dst16, int dstride,
                               int bitdepth_max, int tid, int nthr)
@@ -201,7 +387,7 @@ EAV1_DEV void mc_scaled_block(const Eav1Tables *tab, const SrcView<typename BD::
 
 // 8x8 affine warp. (sx,sy) addresses the sample the reference's `src` pointer points at.
 template <typename BD>
-EAV1_DEV void warp8x8_block(const Eav1Tables *tab, const SrcView<typename BD::pixel> &src, int sx, int sy,
+EAV1_DEVN void warp8x8_block(const Eav1Tables *tab, const SrcView<typename BD::pixel> &src, int sx, int sy,
                             const int16_t abcd[4], int mx, int my,
                             typename BD::pixel *dst8, int16_t *dst16, int dstride,
                             int bitdepth_max, int16_t *mid, int tid, int nthr)
@@ -230,44 +416,82 @@ EAV1_DEV void warp8x8_block(const Eav1Tables *tab, const SrcView<typename BD::pi
 }
 
 // ---- compound / blend ------------------------------------------------------------------
+// Four samples of two int16 prep blocks (stride w, 8-byte aligned when w >= 4)
+EAV1_DEV void load4_i16(const int16_t *p, int v[4]) {
+    const uint2 m = *reinterpret_cast<const uint2 *>(p);
+    v[0] = (int16_t)(m.x & 0xffff); v[1] = (int16_t)(m.x >> 16);
+    v[2] = (int16_t)(m.y & 0xffff); v[3] = (int16_t)(m.y >> 16);
+}
+template <typename pixel>
+EAV1_DEV void store4_any(pixel *d, const int v[4]) {
+    if constexpr (sizeof(pixel) == 1) store4_px(reinterpret_cast<uint8_t *>(d), v);
+    else { d[0] = (pixel)v[0]; d[1] = (pixel)v[1]; d[2] = (pixel)v[2]; d[3] = (pixel)v[3]; }
+}
+
+// avg / w_avg / mask share one loop: out = clip((a*wa + b*wb + rnd) >> sh) with per-sample weights
+// for mask (mc_tmpl.c:628-680). mode 0 avg, 1 w_avg, 2 mask.
+template <typename BD, int MODE>
+EAV1_DEV void comp_blend3(typename BD::pixel *dst, int dstride, const int16_t *t1, const int16_t *t2,
+                          int w, int h, int weight, const uint8_t *mask, int bitdepth_max, int tid, int nthr)
+{
+    const int ib = intermediate_bits(bitdepth_max);
+    const int sh = MODE == 0 ? ib + 1 : MODE == 1 ? ib + 4 : ib + 6;
+    const int rnd = MODE == 0 ? (1 << ib) + PrepBias<BD>::v * 2
+                  : MODE == 1 ? (8 << ib) + PrepBias<BD>::v * 16 : (32 << ib) + PrepBias<BD>::v * 64;
+    if (w >= 4) {
+        const int lq = ulog2((unsigned)w) - 2, qmask = (1 << lq) - 1;
+        for (int it = tid; it < (h << lq); it += nthr) {
+            const int y = it >> lq, x = (it & qmask) << 2, i = y * w + x;
+            int a[4], b[4], o[4];
+            load4_i16(t1 + i, a); load4_i16(t2 + i, b);
+            uint32_t m4 = 0;
+            if (MODE == 2) {
+                const uint8_t *mp = mask + i;
+                if (((uintptr_t)mp & 3) == 0) m4 = *reinterpret_cast<const uint32_t *>(mp);
+                else m4 = (uint32_t)mp[0] | ((uint32_t)mp[1] << 8) | ((uint32_t)mp[2] << 16) | ((uint32_t)mp[3] << 24);
+            }
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                int v;
+                if (MODE == 0) v = a[j] + b[j];
+                else if (MODE == 1) v = a[j] * weight + b[j] * (16 - weight);
+                else { const int m = (int)((m4 >> (8 * j)) & 0xff); v = a[j] * m + b[j] * (64 - m); }
+                o[j] = iclip((v + rnd) >> sh, 0, bitdepth_max);
+            }
+            store4_any(dst + y * dstride + x, o);
+        }
+    } else {
+        for (int i = tid; i < w * h; i += nthr) {
+            const int y = i / w, x = i - y * w;
+            int v;
+            if (MODE == 0) v = t1[i] + t2[i];
+            else if (MODE == 1) v = t1[i] * weight + t2[i] * (16 - weight);
+            else { const int m = mask[i]; v = t1[i] * m + t2[i] * (64 - m); }
+            dst[y * dstride + x] = (typename BD::pixel)iclip((v + rnd) >> sh, 0, bitdepth_max);
+        }
+    }
+    CTA_SYNC();
+}
+
 template <typename BD>
 EAV1_DEV void comp_avg(typename BD::pixel *dst, int dstride, const int16_t *t1, const int16_t *t2,
                        int w, int h, int bitdepth_max, int tid, int nthr)
 {
-    const int ib = intermediate_bits(bitdepth_max), sh = ib + 1;
-    const int rnd = (1 << ib) + PrepBias<BD>::v * 2;
-    for (int i = tid; i < w * h; i += nthr) {
-        const int y = i / w, x = i - y * w;
-        dst[y * dstride + x] = (typename BD::pixel)iclip((t1[i] + t2[i] + rnd) >> sh, 0, bitdepth_max);
-    }
-    CTA_SYNC();
+    comp_blend3<BD, 0>(dst, dstride, t1, t2, w, h, 0, nullptr, bitdepth_max, tid, nthr);
 }
 
 template <typename BD>
 EAV1_DEV void comp_w_avg(typename BD::pixel *dst, int dstride, const int16_t *t1, const int16_t *t2,
                          int w, int h, int weight, int bitdepth_max, int tid, int nthr)
 {
-    const int ib = intermediate_bits(bitdepth_max), sh = ib + 4;
-    const int rnd = (8 << ib) + PrepBias<BD>::v * 16;
-    for (int i = tid; i < w * h; i += nthr) {
-        const int y = i / w, x = i - y * w;
-        dst[y * dstride + x] = (typename BD::pixel)iclip((t1[i] * weight + t2[i] * (16 - weight) + rnd) >> sh, 0, bitdepth_max);
-    }
-    CTA_SYNC();
+    comp_blend3<BD, 1>(dst, dstride, t1, t2, w, h, weight, nullptr, bitdepth_max, tid, nthr);
 }
 
 template <typename BD>
 EAV1_DEV void comp_mask(typename BD::pixel *dst, int dstride, const int16_t *t1, const int16_t *t2,
                         int w, int h, const uint8_t *mask, int bitdepth_max, int tid, int nthr)
 {
-    const int ib = intermediate_bits(bitdepth_max), sh = ib + 6;
-    const int rnd = (32 << ib) + PrepBias<BD>::v * 64;
-    for (int i = tid; i < w * h; i += nthr) {
-        const int y = i / w, x = i - y * w;
-        const int m = mask[i];
-        dst[y * dstride + x] = (typename BD::pixel)iclip((t1[i] * m + t2[i] * (64 - m) + rnd) >> sh, 0, bitdepth_max);
-    }
-    CTA_SYNC();
+    comp_blend3<BD, 2>(dst, dstride, t1, t2, w, h, 0, mask, bitdepth_max, tid, nthr);
 }
 
 // w_mask: blends and writes the (optionally 2x1 / 2x2 down-sampled) mask, stride w>>ss_hor.

@@ -27,6 +27,18 @@ struct DepGraph {
     std::vector<uint32_t> deps;
 };
 
+// Two-phase plan of a frame. Phase 1: motion compensation from reference pictures (MC with
+// ref != 7, WARP) depends on nothing inside the frame, so all of it runs first as independent
+// work items of at most 32x32 samples. Phase 2: every other command is a unit of the dataflow
+// graph (producers = last phase-2 writers of the 4x4 cells it reads or rewrites, plus phase-2
+// writers of the scratch regions it reads). Scratch regions are single-assignment (recorder).
+struct UnitGraph {
+    std::vector<uint32_t> mc_items;    // cmd index | tile_x << 24 | tile_y << 26
+    std::vector<uint32_t> unit_cmd;    // phase-2 units in decode order
+    std::vector<uint32_t> dep_start;   // unit_cmd.size() + 1
+    std::vector<uint32_t> deps;        // producer unit ids (smaller than the consumer)
+};
+
 // level view of the same graph (analysis / tests): level = 1 + max level of the producers
 struct Schedule {
     std::vector<Chain> chains;          // sorted by level
@@ -66,6 +78,60 @@ public:
         g.dep_start.push_back((uint32_t)g.deps.size());
     }
 
+    static bool is_ref_mc(const Eav1Cmd &c) {
+        return (c.op == EAV1_OP_MC && c.u.mc.ref != 7) || c.op == EAV1_OP_WARP;
+    }
+
+    void build_units(const Eav1Cmd *cmds, size_t n, UnitGraph &g) {
+        g.mc_items.clear(); g.unit_cmd.clear(); g.dep_start.clear(); g.deps.clear();
+        mark_.clear();
+        prod_.clear();
+        for (size_t i = 0; i < n; i++) {
+            const Eav1Cmd &c = cmds[i];
+            if (c.flags & EAV1_F_BLOCK_HEAD) prod_.clear();
+            if (c.op == EAV1_OP_NOP) continue;
+            if (is_ref_mc(c)) {
+                bool clean = true;
+                if (!(c.flags & EAV1_F_DST_ARENA)) clean = !stamped(c.plane, c.x, c.y, c.x + c.w, c.y + c.h);
+                if (clean) {
+                    if (c.op == EAV1_OP_WARP || c.u.mc.dx) g.mc_items.push_back((uint32_t)i);
+                    else
+                        for (int ty = 0; ty * 32 < c.h; ty++)
+                            for (int tx = 0; tx * 32 < c.w; tx++)
+                                g.mc_items.push_back((uint32_t)i | (uint32_t)tx << 24 | (uint32_t)ty << 26);
+                    continue;
+                }
+            }
+            const uint32_t id = (uint32_t)g.unit_cmd.size();
+            cur_ = id + 1;
+            mark_.push_back(0);
+            g.dep_start.push_back((uint32_t)g.deps.size());
+            out_ = &g.deps;
+            touch(c, false);
+            arena_reads(c);
+            touch(c, true);
+            if (c.flags & EAV1_F_DST_ARENA)
+                prod_.push_back({c.dst_off, c.dst_off + (uint32_t)c.w * c.h * ((c.flags & EAV1_F_PREP) ? 2u : 2u), id});
+            if (c.op == EAV1_OP_W_MASK)
+                prod_.push_back({c.u.comp.mask_off, c.u.comp.mask_off + (uint32_t)c.w * c.h, id});
+            g.unit_cmd.push_back((uint32_t)i);
+        }
+        g.dep_start.push_back((uint32_t)g.deps.size());
+    }
+
+    // level of every unit (analysis): 1 + max level of its producers
+    static uint32_t unit_levels(const UnitGraph &g, std::vector<uint32_t> *lvl_out = nullptr) {
+        std::vector<uint32_t> lvl(g.unit_cmd.size(), 0);
+        uint32_t mx = 0;
+        for (size_t u = 0; u < lvl.size(); u++) {
+            uint32_t lv = 0;
+            for (uint32_t d = g.dep_start[u]; d < g.dep_start[u + 1]; d++) lv = std::max(lv, lvl[g.deps[d]] + 1);
+            lvl[u] = lv; mx = std::max(mx, lv);
+        }
+        if (lvl_out) lvl_out->swap(lvl);
+        return g.unit_cmd.empty() ? 0 : mx + 1;
+    }
+
     static void levels(const DepGraph &g, Schedule &out) {
         const size_t nc = g.chains.size();
         std::vector<uint32_t> lvl(nc, 0);
@@ -97,6 +163,36 @@ private:
     std::vector<uint32_t> mark_;      // per chain: consumer (index+1) that already listed it
     std::vector<uint32_t> *out_ = nullptr;
     uint32_t cur_ = 0;
+    struct Prod { uint32_t lo, hi, unit; };
+    std::vector<Prod> prod_;          // phase-2 writers of scratch regions of the current block
+
+    bool stamped(int p, int x0, int y0, int x1, int y1) const {
+        int cx0 = std::max(x0, 0) >> 2, cy0 = std::max(y0, 0) >> 2;
+        int cx1 = std::min((x1 + 3) >> 2, cw_[p]), cy1 = std::min((y1 + 3) >> 2, ch_[p]);
+        for (int cy = cy0; cy < cy1; cy++)
+            for (int cx = cx0; cx < cx1; cx++)
+                if (last_[p][(size_t)cy * cw_[p] + cx]) return true;
+        return false;
+    }
+
+    void arena_dep(uint32_t off) {
+        for (const Prod &p : prod_)
+            if (off >= p.lo && off < p.hi && mark_[p.unit] != cur_) { mark_[p.unit] = cur_; out_->push_back(p.unit); }
+    }
+
+    void arena_reads(const Eav1Cmd &c) {
+        if (prod_.empty()) return;
+        switch (c.op) {
+        case EAV1_OP_AVG: case EAV1_OP_W_AVG: case EAV1_OP_MASK: case EAV1_OP_W_MASK:
+            arena_dep(c.u.comp.t1); arena_dep(c.u.comp.t2);
+            if (c.op == EAV1_OP_MASK && (c.flags & EAV1_F_MASK_ARENA)) arena_dep(c.u.comp.mask_off);
+            break;
+        case EAV1_OP_BLEND: case EAV1_OP_BLEND_V: case EAV1_OP_BLEND_H:
+            arena_dep(c.u.blend.tmp_off);
+            break;
+        default: break;
+        }
+    }
 
     void rect(int p, int x0, int y0, int x1, int y1, bool write) {
         // [x0,x1) x [y0,y1) in pixels

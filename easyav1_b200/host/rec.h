@@ -70,6 +70,7 @@ Eav1Rec *eav1rec_for_ctx(const Dav1dContext *c);
 Eav1Cmd *eav1rec_push(Eav1Rec *r);
 uint32_t eav1rec_payload(Eav1Rec *r, const void *src, size_t bytes, size_t align);
 uint32_t eav1rec_region(Eav1Rec *r, int reg, size_t elem_bytes);
+uint32_t eav1rec_region_new(Eav1Rec *r, int reg, size_t bytes);
 Eav1LfRec *eav1rec_push_lf(Eav1Rec *r);
 Eav1LrRec *eav1rec_push_lr(Eav1Rec *r);
 void eav1rec_block_begin(Eav1Rec *r, const Dav1dTaskContext *t, int bs);

@@ -83,6 +83,18 @@ uint32_t eav1rec_region(Eav1Rec *r, int reg, size_t elem_bytes)
     return r->region_off[reg];
 }
 
+/* A producer starts a fresh region every time (single assignment): no command ever overwrites
+ * scratch that an earlier command of the frame still has to read, so the engine is free to run
+ * all motion compensation of a frame before anything else. */
+uint32_t eav1rec_region_new(Eav1Rec *r, int reg, size_t bytes)
+{
+    size_t off = (r->arena_used + 15) & ~(size_t)15;
+    r->region_off[reg] = (uint32_t)off;
+    r->arena_used = off + bytes;
+    r->region_live[reg] = 1;
+    return (uint32_t)off;
+}
+
 Eav1LfRec *eav1rec_push_lf(Eav1Rec *r)
 {
     r->lf = grow(r->lf, &r->cap_lf, r->n_lf + 1, sizeof(Eav1LfRec));

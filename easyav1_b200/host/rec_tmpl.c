@@ -43,7 +43,7 @@ static void set_dst(Eav1Rec *r, Eav1Cmd *c, const void *dst, int w, int h, int r
         c->plane = (uint8_t)pl; c->x = (int16_t)x; c->y = (int16_t)y;
     } else {
         c->flags |= EAV1_F_DST_ARENA;
-        c->dst_off = eav1rec_region(r, reg, elem);
+        c->dst_off = eav1rec_region_new(r, reg, (size_t)imax(w * h, r->blk_w * r->blk_h) * elem);
         c->dst_stride = (uint16_t)w;
     }
 }
@@ -109,13 +109,17 @@ static int resolve_src(Eav1Rec *r, const pixel *src, int *ref, int *plane, int *
     return 0;
 }
 
-static uint32_t tmp_region(Eav1Rec *r, const int16_t *tmp)
+/* produce != 0: the caller writes the prep block; a write at the start of the scratch buffer
+ * opens a fresh region (warp8x8t fills one region tile by tile at inner offsets) */
+static uint32_t tmp_region(Eav1Rec *r, const int16_t *tmp, int produce)
 {
     const int16_t *base = r->t->scratch.compinter[0];
     const ptrdiff_t off = tmp - base;
     const int idx = off >= 128 * 128;
     const ptrdiff_t inner = off - idx * 128 * 128;
-    return eav1rec_region(r, idx ? REG_TMP1 : REG_TMP0, 2) + (uint32_t)(inner * 2);
+    const int reg = idx ? REG_TMP1 : REG_TMP0;
+    if (produce && inner == 0) return eav1rec_region_new(r, reg, (size_t)r->blk_w * r->blk_h * 2);
+    return eav1rec_region(r, reg, 2) + (uint32_t)(inner * 2);
 }
 
 static void rec_mc_any(const int filter, pixel *dst8, int16_t *dst16, const pixel *src,
@@ -131,7 +135,7 @@ static void rec_mc_any(const int filter, pixel *dst8, int16_t *dst16, const pixe
     } else {
         c->w = (uint8_t)w; c->h = (uint8_t)h;
         c->flags |= EAV1_F_DST_ARENA | EAV1_F_PREP;
-        c->dst_off = tmp_region(r, dst16);
+        c->dst_off = tmp_region(r, dst16, 1);
         c->dst_stride = (uint16_t)w;
     }
     c->plane = (c->flags & EAV1_F_DST_ARENA) ? (uint8_t)plane : c->plane;
@@ -180,7 +184,7 @@ static void rec_warp_any(pixel *dst8, int16_t *dst16, const ptrdiff_t dstride, c
     } else {
         c->w = c->h = 8;
         c->flags |= EAV1_F_DST_ARENA | EAV1_F_PREP;
-        c->dst_off = tmp_region(r, dst16);
+        c->dst_off = tmp_region(r, dst16, 1);
         c->dst_stride = (uint16_t)dstride;
         c->plane = (uint8_t)plane;
     }
@@ -200,8 +204,8 @@ static Eav1Cmd *rec_comp(int op, pixel *dst, const int16_t *t1, const int16_t *t
     Eav1Cmd *c = eav1rec_push(r);
     c->op = (uint8_t)op;
     set_dst(r, c, dst, w, h, REG_LAP, sizeof(pixel));
-    c->u.comp.t1 = tmp_region(r, t1);
-    c->u.comp.t2 = tmp_region(r, t2);
+    c->u.comp.t1 = tmp_region(r, t1, 0);
+    c->u.comp.t2 = tmp_region(r, t2, 0);
     return c;
 }
 static void rec_avg(pixel *dst, ptrdiff_t ds, const int16_t *t1, const int16_t *t2, int w, int h HIGHBD_DECL_SUFFIX)
@@ -224,7 +228,8 @@ static void rec_w_mask_any(int ss_hor, int ss_ver, pixel *dst, const int16_t *t1
 {
     REC();
     Eav1Cmd *c = rec_comp(EAV1_OP_W_MASK, dst, t1, t2, w, h);
-    c->u.comp.mask_off = eav1rec_region(r, REG_SEGMASK, 1) + (uint32_t)(mask - r->t->scratch.seg_mask);
+    if (mask == r->t->scratch.seg_mask) c->u.comp.mask_off = eav1rec_region_new(r, REG_SEGMASK, (size_t)r->blk_w * r->blk_h);
+    else c->u.comp.mask_off = eav1rec_region(r, REG_SEGMASK, 1) + (uint32_t)(mask - r->t->scratch.seg_mask);
     c->u.comp.sign = (uint8_t)sign; c->u.comp.ss_hor = (uint8_t)ss_hor; c->u.comp.ss_ver = (uint8_t)ss_ver;
 }
 static void rec_w_mask_444(pixel *dst, ptrdiff_t ds, const int16_t *t1, const int16_t *t2, int w, int h, uint8_t *mask, int sign HIGHBD_DECL_SUFFIX)

@@ -236,7 +236,10 @@ typedef struct Eav1StagedInfo {
     int cur, w, h, bpc, layout;
     int n_levels, n_chains, launches;
     int n_lf, n_lr, cdef, inter;
+    int n_big, n_small;      /* dataflow units run by a whole CTA / by a single warp */
+    int n_mc_items, pad;     /* phase-1 motion-compensation work items (<= 32x32 each) */
     long long n_cmds, payload_bytes;
+    long long mc_px, unit_px; /* samples produced by phase 1 / touched by phase-2 units */
 } Eav1StagedInfo;
 /* sizeof() of the ABI structs as compiled (0 Eav1Cmd, 1 Eav1LfRec, 2 Eav1LrRec, 3 Eav1FrameDesc,
  * 4 Eav1StagedInfo, 5 Eav1Tables), so bindings can verify their mirrors. */
@@ -249,10 +252,12 @@ int  eav1cu_plan_levels(const Eav1Cmd *cmds, size_t n_cmds, const int plane_w[3]
 int  eav1cu_counters(Eav1cuCtx *ctx, long long out[4]);
 int  eav1cu_set_capture(Eav1cuCtx *ctx, int on);
 /* Per-stage device time (CUDA events on the context's stream around each stage of every
- * frame): index 0 reconstruction levels, 1 deblock, 2 CDEF, 3 loop restoration. Accumulated
+ * frame): index 0 dataflow reconstruction (intra, residual, compound/blend), 1 deblock, 2 CDEF,
+ * 3 loop restoration, 4 motion compensation. Each array has EAV1CU_N_STAGES entries: accumulated
  * milliseconds, kernel launches and stage invocations since the last reset. */
+#define EAV1CU_N_STAGES 6
 int  eav1cu_set_stage_timing(Eav1cuCtx *ctx, int on);
-int  eav1cu_stage_times(Eav1cuCtx *ctx, double ms[4], long long launches[4], long long calls[4], int reset);
+int  eav1cu_stage_times(Eav1cuCtx *ctx, double *ms, long long *launches, long long *calls, int reset);
 int  eav1cu_staged_count(Eav1cuCtx *ctx);
 int  eav1cu_staged_replay(Eav1cuCtx *ctx, int idx);
 int  eav1cu_staged_info(Eav1cuCtx *ctx, int idx, Eav1StagedInfo *out);

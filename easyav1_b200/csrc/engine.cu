@@ -246,7 +246,7 @@ struct Eav1cuCtx {
     uint32_t *d_ctrl = nullptr;
     uint32_t epoch = 0;
     int recon_grid = 148 * 4;
-    int warp_mode = 1;   // 0: every chain on a CTA, 1: independent small chains on warps, 2: all small chains on warps
+    int warp_mode = 0;   // 0: every chain on a CTA, 1: independent small chains on warps, 2: all small chains on warps
     int err = 0;
     std::string errmsg;
     std::mutex mu;
@@ -597,7 +597,9 @@ static int plan_build(Eav1cuCtx *ctx, FramePlan &pl, bool staged, const Eav1Fram
                 const int x0 = (int)((it >> 24) & 3) * 32, y0 = (int)((it >> 26) & 3) * 32;
                 pl.mc_px += (c.op == EAV1_OP_MC && !c.u.mc.dx) ? (long long)std::min(32, c.w - x0) * std::min(32, c.h - y0) : (long long)c.w * c.h;
             }
-            for (uint32_t ci : g.unit_cmd) pl.unit_px += (long long)cmds[ci].w * cmds[ci].h;
+            for (size_t u = 0; u < g.unit_cmd.size(); u++)
+                for (uint32_t k = 0; k < g.unit_cnt[u]; k++)
+                    pl.unit_px += (long long)cmds[g.unit_cmd[u] + k].w * cmds[g.unit_cmd[u] + k].h;
         }
         if (pl.n_items) {
             if ((r = up.put(ctx->items, g.mc_items.data(), g.mc_items.size() * 4, &d))) return r;
@@ -627,7 +629,7 @@ static int plan_build(Eav1cuCtx *ctx, FramePlan &pl, bool staged, const Eav1Fram
                     else if (ctx->warp_mode == 1) big |= linked;
                     if (big != (pass == 0)) continue;
                     ChainRec &rc = rt[pos++];
-                    rc.first = g.unit_cmd[u]; rc.count = 1;
+                    rc.first = g.unit_cmd[u]; rc.count = g.unit_cnt[u];
                     rc.dep_off = g.dep_start[u]; rc.n_deps = g.dep_start[u + 1] - g.dep_start[u];
                     rc.id = (uint32_t)u; rc.pad[0] = fed[u]; rc.pad[1] = rc.pad[2] = 0;
                     if (big) px_big += (double)c.w * c.h; else px_small += (double)c.w * c.h;

@@ -34,7 +34,8 @@ struct DepGraph {
 // writers of the scratch regions it reads). Scratch regions are single-assignment (recorder).
 struct UnitGraph {
     std::vector<uint32_t> mc_items;    // cmd index | tile_x << 24 | tile_y << 26
-    std::vector<uint32_t> unit_cmd;    // phase-2 units in decode order
+    std::vector<uint32_t> unit_cmd;    // phase-2 units in decode order: first command ...
+    std::vector<uint32_t> unit_cnt;    // ... and how many consecutive commands the unit runs
     std::vector<uint32_t> dep_start;   // unit_cmd.size() + 1
     std::vector<uint32_t> deps;        // producer unit ids (smaller than the consumer)
 };
@@ -83,9 +84,10 @@ public:
     }
 
     void build_units(const Eav1Cmd *cmds, size_t n, UnitGraph &g) {
-        g.mc_items.clear(); g.unit_cmd.clear(); g.dep_start.clear(); g.deps.clear();
+        g.mc_items.clear(); g.unit_cmd.clear(); g.unit_cnt.clear(); g.dep_start.clear(); g.deps.clear();
         mark_.clear();
         prod_.clear();
+        last_big_ = false;
         for (size_t i = 0; i < n; i++) {
             const Eav1Cmd &c = cmds[i];
             if (c.flags & EAV1_F_BLOCK_HEAD) prod_.clear();
@@ -102,19 +104,40 @@ public:
                     continue;
                 }
             }
-            const uint32_t id = (uint32_t)g.unit_cmd.size();
+            // A command that consumes what the previous unit produced, and directly follows it in
+            // the command list, joins that unit: the pair runs back to back on one work group
+            // with no flag hop (prediction -> residual -> next transform block's prediction ...).
+            uint32_t id = (uint32_t)g.unit_cmd.size();
+            bool fuse = false;
+            if (id > 0 && g.unit_cmd[id - 1] + g.unit_cnt[id - 1] == i && g.unit_cnt[id - 1] < 64 &&
+                (c.w > 32 || c.h > 32) == last_big_) {
+                cur_ = id;                      // probe with the previous unit's identity
+                probe_hit_ = false;
+                probe_ = true;
+                touch(c, false);
+                arena_reads(c);
+                probe_ = false;
+                fuse = probe_hit_;
+            }
+            if (fuse) {
+                id -= 1;
+                g.unit_cnt[id]++;
+            } else {
+                mark_.push_back(0);
+                g.dep_start.push_back((uint32_t)g.deps.size());
+                g.unit_cmd.push_back((uint32_t)i);
+                g.unit_cnt.push_back(1);
+                last_big_ = c.w > 32 || c.h > 32;
+            }
             cur_ = id + 1;
-            mark_.push_back(0);
-            g.dep_start.push_back((uint32_t)g.deps.size());
             out_ = &g.deps;
             touch(c, false);
             arena_reads(c);
             touch(c, true);
             if (c.flags & EAV1_F_DST_ARENA)
-                prod_.push_back({c.dst_off, c.dst_off + (uint32_t)c.w * c.h * ((c.flags & EAV1_F_PREP) ? 2u : 2u), id});
+                prod_.push_back({c.dst_off, c.dst_off + (uint32_t)c.w * c.h * 2u, id});
             if (c.op == EAV1_OP_W_MASK)
                 prod_.push_back({c.u.comp.mask_off, c.u.comp.mask_off + (uint32_t)c.w * c.h, id});
-            g.unit_cmd.push_back((uint32_t)i);
         }
         g.dep_start.push_back((uint32_t)g.deps.size());
     }
@@ -165,6 +188,7 @@ private:
     uint32_t cur_ = 0;
     struct Prod { uint32_t lo, hi, unit; };
     std::vector<Prod> prod_;          // phase-2 writers of scratch regions of the current block
+    bool probe_ = false, probe_hit_ = false, last_big_ = false;
 
     bool stamped(int p, int x0, int y0, int x1, int y1) const {
         int cx0 = std::max(x0, 0) >> 2, cy0 = std::max(y0, 0) >> 2;
@@ -176,8 +200,11 @@ private:
     }
 
     void arena_dep(uint32_t off) {
-        for (const Prod &p : prod_)
-            if (off >= p.lo && off < p.hi && mark_[p.unit] != cur_) { mark_[p.unit] = cur_; out_->push_back(p.unit); }
+        for (const Prod &p : prod_) {
+            if (off < p.lo || off >= p.hi) continue;
+            if (probe_) { probe_hit_ |= p.unit + 1 == cur_; continue; }
+            if (p.unit + 1 != cur_ && mark_[p.unit] != cur_) { mark_[p.unit] = cur_; out_->push_back(p.unit); }
+        }
     }
 
     void arena_reads(const Eav1Cmd &c) {
@@ -203,6 +230,7 @@ private:
             for (int cx = cx0; cx < cx1; cx++) {
                 if (write) { row[cx] = cur_; continue; }
                 const uint32_t w = row[cx];
+                if (probe_) { probe_hit_ |= w == cur_; continue; }
                 if (w && w != cur_ && mark_[w - 1] != cur_) { mark_[w - 1] = cur_; out_->push_back(w - 1); }
             }
         }

@@ -225,6 +225,14 @@ struct FramePlan {
     long long launches = 0;
 };
 
+// Per-frame upload buffers exist twice: while the kernels of frame k still read slot k&1, the
+// host already fills the other slot for frame k+1 (the `done` event guards reuse two frames later).
+struct Slot {
+    DevBuf cmds, payload, lfrec, lflvl, lrrec, lfmask, deps, recs, items;
+    cudaEvent_t done = nullptr;
+    bool used = false;
+};
+
 struct Eav1cuCtx {
     int device = 0;
     cudaStream_t stream = nullptr;
@@ -232,13 +240,20 @@ struct Eav1cuCtx {
     bool have_tab = false;
     uint8_t *d_masks = nullptr; size_t masks_bytes = 0;
     std::vector<Picture> pics;
-    DevBuf cmds, chains, payload, arena, lfrec, lflvl, lrrec, lfmask;
+    DevBuf arena;
+    Slot slot[2];
+    int cur_slot = 0;
+    Slot &S() { return slot[cur_slot]; }
+    // fences: events the host side can wait on (frame finished, picture downloaded)
+    static const int N_FENCE = 64;
+    cudaEvent_t fence_ev[N_FENCE] = {};
+    unsigned long long fence_next = 1;
+    std::mutex fence_mu;
     Picture work[2];           // post-filter ping-pong pictures
     std::vector<Eav1LfRec> lf_sorted;
     Scheduler sched;
     DepGraph graph;
     Schedule plan;
-    DevBuf deps, recs, items;
     UnitGraph units;
     std::vector<ChainRec> rec_tmp;
     std::vector<uint8_t> fed_tmp;
@@ -348,6 +363,7 @@ int eav1cu_ctx_create(Eav1cuCtx **out, int device)
     if (cudaGetDeviceCount(&n) != cudaSuccess || n <= 0 || device >= n) return EAV1CU_ERR_NO_DEVICE;
     Eav1cuCtx *ctx = new Eav1cuCtx();
     ctx->device = device;
+    ctx->pics.reserve(512);   // never reallocates: other threads index it while frames are in flight
     if (cudaSetDevice(device) != cudaSuccess ||
         cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess ||
         cudaMalloc(&ctx->d_tab, sizeof(Eav1Tables)) != cudaSuccess ||
@@ -375,9 +391,13 @@ void eav1cu_ctx_destroy(Eav1cuCtx *ctx)
     cudaStreamSynchronize(ctx->stream);
     for (auto &p : ctx->pics) if (p.base) cudaFree(p.base);
     for (auto &p : ctx->work) if (p.base) cudaFree(p.base);
-    free_buf(ctx->cmds); free_buf(ctx->chains); free_buf(ctx->payload); free_buf(ctx->arena);
-    free_buf(ctx->lfrec); free_buf(ctx->lflvl); free_buf(ctx->lrrec); free_buf(ctx->lfmask);
-    free_buf(ctx->deps); free_buf(ctx->recs); free_buf(ctx->items);
+    free_buf(ctx->arena);
+    for (Slot &sl : ctx->slot) {
+        free_buf(sl.cmds); free_buf(sl.payload); free_buf(sl.lfrec); free_buf(sl.lflvl); free_buf(sl.lrrec);
+        free_buf(sl.lfmask); free_buf(sl.deps); free_buf(sl.recs); free_buf(sl.items);
+        if (sl.done) cudaEventDestroy(sl.done);
+    }
+    for (cudaEvent_t e : ctx->fence_ev) if (e) cudaEventDestroy(e);
     if (ctx->d_done) cudaFree(ctx->d_done);
     if (ctx->d_ctrl) cudaFree(ctx->d_ctrl);
     if (ctx->d_tab) cudaFree(ctx->d_tab);
@@ -442,7 +462,10 @@ int eav1cu_pic_alloc(Eav1cuCtx *ctx, int w, int h, int layout, int bpc)
     int id = -1;
     for (size_t i = 0; i < ctx->pics.size(); i++)
         if (!ctx->pics[i].used) { id = (int)i; break; }
-    if (id < 0) { ctx->pics.emplace_back(); id = (int)ctx->pics.size() - 1; }
+    if (id < 0) {
+        if (ctx->pics.size() >= 512) return fail(ctx, EAV1CU_ERR_NOMEM, "device picture pool exhausted");
+        ctx->pics.emplace_back(); id = (int)ctx->pics.size() - 1;
+    }
     Picture &p = ctx->pics[id];
     int r = pic_setup(ctx, p, w, h, layout, bpc);
     if (r) return r;
@@ -458,7 +481,7 @@ int eav1cu_pic_release(Eav1cuCtx *ctx, int id)
     return 0;
 }
 
-static int pic_copy(Eav1cuCtx *ctx, int id, void *const data[3], const ptrdiff_t stride[2], bool to_device)
+static int pic_copy(Eav1cuCtx *ctx, int id, void *const data[3], const ptrdiff_t stride[2], bool to_device, bool wait = true)
 {
     if (!ctx || id < 0 || id >= (int)ctx->pics.size() || !ctx->pics[id].base) return EAV1CU_ERR_INVAL;
     CK(cudaSetDevice(ctx->device));
@@ -476,7 +499,41 @@ static int pic_copy(Eav1cuCtx *ctx, int id, void *const data[3], const ptrdiff_t
             CK(cudaMemcpy2DAsync(data[pl], stride[!!pl], p.pl[pl].p, p.pl[pl].stride, (size_t)w << hbd, h,
                                  cudaMemcpyDeviceToHost, ctx->stream));
     }
-    CK(cudaStreamSynchronize(ctx->stream));
+    if (wait) CK(cudaStreamSynchronize(ctx->stream));
+    return ctx->err;
+}
+
+int eav1cu_pic_download_async(Eav1cuCtx *ctx, int id, void *const data[3], const ptrdiff_t stride[2])
+{
+    return pic_copy(ctx, id, data, stride, false, false);
+}
+
+int eav1cu_fence(Eav1cuCtx *ctx, unsigned long long *ticket)
+{
+    if (!ctx || !ticket) return EAV1CU_ERR_INVAL;
+    CK(cudaSetDevice(ctx->device));
+    std::lock_guard<std::mutex> g(ctx->fence_mu);
+    const unsigned long long t = ctx->fence_next++;
+    cudaEvent_t &e = ctx->fence_ev[t % Eav1cuCtx::N_FENCE];
+    if (!e) CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    else CK(cudaEventSynchronize(e));   // the ticket issued N_FENCE fences ago
+    CK(cudaEventRecord(e, ctx->stream));
+    *ticket = t;
+    return 0;
+}
+
+int eav1cu_fence_wait(Eav1cuCtx *ctx, unsigned long long ticket)
+{
+    if (!ctx || !ticket) return EAV1CU_ERR_INVAL;
+    CK(cudaSetDevice(ctx->device));
+    cudaEvent_t e = nullptr;
+    {
+        std::lock_guard<std::mutex> g(ctx->fence_mu);
+        if (ticket >= ctx->fence_next) return EAV1CU_ERR_INVAL;
+        if (ticket + Eav1cuCtx::N_FENCE <= ctx->fence_next) return ctx->err;   // recycled: it completed long ago
+        e = ctx->fence_ev[ticket % Eav1cuCtx::N_FENCE];
+    }
+    CK(cudaEventSynchronize(e));
     return ctx->err;
 }
 
@@ -583,11 +640,11 @@ static int plan_build(Eav1cuCtx *ctx, FramePlan &pl, bool staged, const Eav1Fram
         ctx->sched.reset(pw, ph);
         ctx->sched.build_units(cmds, n_cmds, ctx->units);
         const UnitGraph &g = ctx->units;
-        if ((r = up.put(ctx->cmds, cmds, n_cmds * sizeof(Eav1Cmd), &d))) return r;
+        if ((r = up.put(ctx->S().cmds, cmds, n_cmds * sizeof(Eav1Cmd), &d))) return r;
         pl.d_cmds = reinterpret_cast<const Eav1Cmd *>(d);
         // never hand the kernel a null list, even when nothing has a producer
         static const uint32_t zero = 0;
-        if ((r = up.put(ctx->deps, g.deps.empty() ? &zero : g.deps.data(), std::max<size_t>(g.deps.size(), 1) * 4, &d))) return r;
+        if ((r = up.put(ctx->S().deps, g.deps.empty() ? &zero : g.deps.data(), std::max<size_t>(g.deps.size(), 1) * 4, &d))) return r;
         pl.d_deps = reinterpret_cast<const uint32_t *>(d);
         pl.n_items = (uint32_t)g.mc_items.size();
         if (staged) {
@@ -602,7 +659,7 @@ static int plan_build(Eav1cuCtx *ctx, FramePlan &pl, bool staged, const Eav1Fram
                     pl.unit_px += (long long)cmds[g.unit_cmd[u] + k].w * cmds[g.unit_cmd[u] + k].h;
         }
         if (pl.n_items) {
-            if ((r = up.put(ctx->items, g.mc_items.data(), g.mc_items.size() * 4, &d))) return r;
+            if ((r = up.put(ctx->S().items, g.mc_items.data(), g.mc_items.size() * 4, &d))) return r;
             pl.d_items = reinterpret_cast<const uint32_t *>(d);
         }
         pl.n_chains = (uint32_t)g.unit_cmd.size(); pl.n_deps = (uint32_t)g.deps.size();
@@ -638,10 +695,10 @@ static int plan_build(Eav1cuCtx *ctx, FramePlan &pl, bool staged, const Eav1Fram
             }
             pl.n_big = (uint32_t)nb; pl.n_small = (uint32_t)(nc - nb);
             pl.big_share = px_big + px_small > 0 ? px_big / (px_big + px_small) : 0;
-            if ((r = up.put(ctx->recs, rt.data(), rt.size() * sizeof(ChainRec), &d))) return r;
+            if ((r = up.put(ctx->S().recs, rt.data(), rt.size() * sizeof(ChainRec), &d))) return r;
             pl.d_recs = reinterpret_cast<const ChainRec *>(d);
         } else { pl.n_big = pl.n_small = 0; }
-        if ((r = up.put(ctx->payload, payload, payload_bytes, &pl.d_payload))) return r;
+        if ((r = up.put(ctx->S().payload, payload, payload_bytes, &pl.d_payload))) return r;
         if ((r = ensure(ctx, ctx->arena, arena_bytes + 16, false))) return r;
         if (g.unit_cmd.size() > ctx->done_cap) {
             if (ctx->d_done) { CK(cudaStreamSynchronize(ctx->stream)); cudaFree(ctx->d_done); ctx->d_done = nullptr; }
@@ -659,16 +716,16 @@ static int plan_build(Eav1cuCtx *ctx, FramePlan &pl, bool staged, const Eav1Fram
         for (size_t i = 0; i < fd->n_lf_recs; i++) if (fd->lf_recs[i].dir == 0) v[n0++] = fd->lf_recs[i];
         size_t n1 = n0;
         for (size_t i = 0; i < fd->n_lf_recs; i++) if (fd->lf_recs[i].dir != 0) v[n1++] = fd->lf_recs[i];
-        if ((r = up.put(ctx->lfrec, v.data(), v.size() * sizeof(Eav1LfRec), &d))) return r;
+        if ((r = up.put(ctx->S().lfrec, v.data(), v.size() * sizeof(Eav1LfRec), &d))) return r;
         pl.d_lf = reinterpret_cast<const Eav1LfRec *>(d);
         pl.n_lf0 = n0; pl.n_lf1 = n1 - n0;
-        if ((r = up.put(ctx->lflvl, fd->lf_level, fd->lf_level_bytes, &pl.d_lflvl))) return r;
+        if ((r = up.put(ctx->S().lflvl, fd->lf_level, fd->lf_level_bytes, &pl.d_lflvl))) return r;
     } else { pl.n_lf0 = pl.n_lf1 = 0; }
     if (has_cdef)
-        if ((r = up.put(ctx->lfmask, fd->lf_mask, (size_t)fd->sb128w * fd->sb128h * 1348, &pl.d_lfmask))) return r;
+        if ((r = up.put(ctx->S().lfmask, fd->lf_mask, (size_t)fd->sb128w * fd->sb128h * 1348, &pl.d_lfmask))) return r;
     pl.n_lr = fd->n_lr_recs;
     if (has_lr) {
-        if ((r = up.put(ctx->lrrec, fd->lr_recs, fd->n_lr_recs * sizeof(Eav1LrRec), &d))) return r;
+        if ((r = up.put(ctx->S().lrrec, fd->lr_recs, fd->n_lr_recs * sizeof(Eav1LrRec), &d))) return r;
         pl.d_lr = reinterpret_cast<const Eav1LrRec *>(d);
     }
     return 0;
@@ -787,9 +844,15 @@ int eav1cu_frame_submit(Eav1cuCtx *ctx, const Eav1FrameDesc *fd,
     if (ctx->err) return ctx->err;
     if (!ctx->have_tab) return fail(ctx, EAV1CU_ERR_NOTABLES, "eav1cu_set_tables not called");
     CK(cudaSetDevice(ctx->device));
+    ctx->cur_slot ^= 1;
+    Slot &sl = ctx->S();
+    if (!sl.done) CK(cudaEventCreateWithFlags(&sl.done, cudaEventDisableTiming));
+    if (sl.used) CK(cudaEventSynchronize(sl.done));   // the frame two submits ago has finished with this slot
     int r = plan_build(ctx, ctx->live, false, fd, cmds, n_cmds, payload, payload_bytes, arena_bytes);
     if (r) return r;
     if ((r = plan_launch(ctx, ctx->live))) return r;
+    CK(cudaEventRecord(sl.done, ctx->stream));
+    sl.used = true;
     ctx->n_frames++;
     if (ctx->capture) {
         // keep a replayable copy of this frame (bench.py's device-resident leg)

@@ -1,7 +1,7 @@
 /*
  * rec_common.c — bit-depth independent part of the recorder: decoder open/close wrappers,
- * pinned picture allocator tied to the device picture pool, constant-table upload, list
- * management and the per-frame submit. See rec.h.
+ * pinned picture allocator tied to the device picture pool, constant-table upload, per-frame
+ * list management, the hooks into dav1d's frame life cycle and the submit thread. See rec.h.
  */
 #include <errno.h>
 #include <pthread.h>
@@ -13,16 +13,21 @@
 #include "common/frame.h"
 #include "src/tables.h"
 #include "src/wedge.h"
+#include "src/decode.h"
+#include "src/thread_task.h"
 
 /* the reference's own entry points, renamed at compile time (host/Makefile) */
 int  eav1ref_dav1d_open(Dav1dContext **c_out, const Dav1dSettings *s);
 void eav1ref_dav1d_close(Dav1dContext **c_out);
+int  eav1ref_dav1d_get_picture(Dav1dContext *c, Dav1dPicture *out);
 
 /* pinned host memory comes from the engine so this library needs no CUDA headers */
 int  eav1cu_host_alloc(void **p, size_t bytes);
 void eav1cu_host_free(void *p);
 
-__thread Eav1Rec *eav1_tls_rec;
+#define FENCE_PENDING (~0ULL)
+
+__thread Eav1Walk eav1_walk;
 
 #define MAX_RECS 256
 static pthread_mutex_t g_mu = PTHREAD_MUTEX_INITIALIZER;
@@ -30,14 +35,14 @@ static Eav1Rec *g_recs[MAX_RECS];
 
 Eav1Rec *eav1rec_for_ctx(const Dav1dContext *c)
 {
-    Eav1Rec *r = eav1_tls_rec;
+    Eav1Rec *r = eav1_walk.r;
     if (r && r->c == c) return r;
     pthread_mutex_lock(&g_mu);
     r = NULL;
     for (int i = 0; i < MAX_RECS; i++)
         if (g_recs[i] && g_recs[i]->c == c) { r = g_recs[i]; break; }
     pthread_mutex_unlock(&g_mu);
-    eav1_tls_rec = r;
+    eav1_walk.r = r;
     return r;
 }
 
@@ -54,73 +59,132 @@ static void *grow(void *p, size_t *cap, size_t need, size_t elem)
     return p;
 }
 
-Eav1Cmd *eav1rec_push(Eav1Rec *r)
+Eav1Cmd *eav1rec_push(Eav1Walk *w)
 {
-    r->cmds = grow(r->cmds, &r->cap_cmds, r->n_cmds + 1, sizeof(Eav1Cmd));
-    Eav1Cmd *c = &r->cmds[r->n_cmds++];
+    Eav1List *l = w->list;
+    l->cmds = grow(l->cmds, &l->cap, l->n + 1, sizeof(Eav1Cmd));
+    Eav1Cmd *c = &l->cmds[l->n++];
     memset(c, 0, sizeof(*c));
-    if (r->block_head) { c->flags |= EAV1_F_BLOCK_HEAD; r->block_head = 0; }
+    if (w->block_head) { c->flags |= EAV1_F_BLOCK_HEAD; w->block_head = 0; }
     return c;
 }
 
-uint32_t eav1rec_payload(Eav1Rec *r, const void *src, size_t bytes, size_t align)
+/* The payload buffer is sized for the worst case when the frame opens (one coefficient per
+ * sample plus palette data), so concurrent tiles only need an atomic bump. */
+uint32_t eav1rec_payload(Eav1Walk *w, const void *src, size_t bytes, size_t align)
 {
-    size_t off = (r->n_payload + align - 1) & ~(align - 1);
-    r->payload = grow(r->payload, &r->cap_payload, off + bytes, 1);
-    memcpy(r->payload + off, src, bytes);
-    r->n_payload = off + bytes;
+    Eav1Frame *fr = w->fr;
+    const size_t take = (bytes + align - 1) & ~(align - 1);
+    const size_t off = atomic_fetch_add(&fr->n_payload, take);
+    if (off + bytes > fr->cap_payload) { atomic_store(&w->r->unsupported, 1); return 0; }
+    memcpy(fr->payload + off, src, bytes);
     return (uint32_t)off;
-}
-
-uint32_t eav1rec_region(Eav1Rec *r, int reg, size_t elem_bytes)
-{
-    if (!r->region_live[reg]) {
-        size_t off = (r->arena_used + 15) & ~(size_t)15;
-        r->region_off[reg] = (uint32_t)off;
-        r->arena_used = off + (size_t)r->blk_w * r->blk_h * elem_bytes;
-        r->region_live[reg] = 1;
-    }
-    return r->region_off[reg];
 }
 
 /* A producer starts a fresh region every time (single assignment): no command ever overwrites
  * scratch that an earlier command of the frame still has to read, so the engine is free to run
  * all motion compensation of a frame before anything else. */
-uint32_t eav1rec_region_new(Eav1Rec *r, int reg, size_t bytes)
+uint32_t eav1rec_region_new(Eav1Walk *w, int reg, size_t bytes)
 {
-    size_t off = (r->arena_used + 15) & ~(size_t)15;
-    r->region_off[reg] = (uint32_t)off;
-    r->arena_used = off + bytes;
-    r->region_live[reg] = 1;
+    const size_t take = (bytes + 15) & ~(size_t)15;
+    const size_t off = atomic_fetch_add(&w->fr->arena_used, take);
+    w->region_off[reg] = (uint32_t)off;
+    w->region_live[reg] = 1;
     return (uint32_t)off;
 }
 
-Eav1LfRec *eav1rec_push_lf(Eav1Rec *r)
+uint32_t eav1rec_region(Eav1Walk *w, int reg, size_t elem_bytes)
 {
-    r->lf = grow(r->lf, &r->cap_lf, r->n_lf + 1, sizeof(Eav1LfRec));
-    return &r->lf[r->n_lf++];
+    if (!w->region_live[reg]) eav1rec_region_new(w, reg, (size_t)w->blk_w * w->blk_h * elem_bytes);
+    return w->region_off[reg];
 }
 
-Eav1LrRec *eav1rec_push_lr(Eav1Rec *r)
+Eav1LfRec *eav1rec_push_lf(Eav1Walk *w, const Eav1LfRec *v)
 {
-    r->lr = grow(r->lr, &r->cap_lr, r->n_lr + 1, sizeof(Eav1LrRec));
-    Eav1LrRec *x = &r->lr[r->n_lr++];
-    memset(x, 0, sizeof(*x));
+    Eav1Frame *fr = w->fr;
+    pthread_mutex_lock(&fr->mu);
+    fr->lf = grow(fr->lf, &fr->cap_lf, fr->n_lf + 1, sizeof(Eav1LfRec));
+    Eav1LfRec *x = &fr->lf[fr->n_lf++];
+    *x = *v;
+    pthread_mutex_unlock(&fr->mu);
     return x;
 }
 
-void eav1rec_block_begin(Eav1Rec *r, const Dav1dTaskContext *t, int bs)
+Eav1LrRec *eav1rec_push_lr(Eav1Walk *w, const Eav1LrRec *v)
 {
-    r->f = t->f;
-    r->t = t;
-    r->frame_open = 1;
-    r->block_head = 1;
-    r->blk_w = dav1d_block_dimensions[bs][0] * 4;
-    r->blk_h = dav1d_block_dimensions[bs][1] * 4;
-    memset(r->region_live, 0, sizeof(r->region_live));
-    r->emu.valid = 0;
-    r->edge.valid = 0;
-    r->ac.valid = 0;
+    Eav1Frame *fr = w->fr;
+    pthread_mutex_lock(&fr->mu);
+    fr->lr = grow(fr->lr, &fr->cap_lr, fr->n_lr + 1, sizeof(Eav1LrRec));
+    Eav1LrRec *x = &fr->lr[fr->n_lr++];
+    *x = *v;
+    pthread_mutex_unlock(&fr->mu);
+    return x;
+}
+
+/* ------------------------------------------------------------------ frame open */
+
+static size_t payload_worst_case(const Dav1dFrameContext *f)
+{
+    const size_t luma = (size_t)f->bw * 4 * f->bh * 4;
+    const int layout = f->cur.p.layout;
+    const size_t samples = layout == DAV1D_PIXEL_LAYOUT_I400 ? luma :
+                           layout == DAV1D_PIXEL_LAYOUT_I420 ? luma * 3 / 2 :
+                           layout == DAV1D_PIXEL_LAYOUT_I422 ? luma * 2 : luma * 3;
+    const size_t coef = f->cur.p.bpc > 8 ? 4 : 2;
+    /* one coefficient per sample + palette indices (<= 1 byte/sample incl. the 16-byte rounding) */
+    return samples * (coef + 1) + (1 << 16);
+}
+
+static void frame_begin(Eav1Frame *fr, const Dav1dFrameContext *f)
+{
+    pthread_mutex_lock(&fr->mu);
+    if (!fr->open) {
+        const size_t need = payload_worst_case(f);
+        if (need > fr->cap_payload) {
+            free(fr->payload);
+            fr->payload = malloc(need);
+            if (!fr->payload) abort();
+            fr->cap_payload = need;
+        }
+        for (int i = 0; i < fr->n_tiles; i++) fr->tiles[i].n = 0;
+        fr->n_tiles = f->frame_hdr->tiling.cols * f->frame_hdr->tiling.rows;
+        if (fr->n_tiles > EAV1_MAX_TILES) fr->n_tiles = EAV1_MAX_TILES;
+        for (int i = 0; i < fr->n_tiles; i++) fr->tiles[i].n = 0;
+        atomic_store(&fr->n_payload, 0);
+        atomic_store(&fr->arena_used, 0);
+        fr->n_lf = fr->n_lr = 0;
+        atomic_store(&fr->unsupported, 0);
+        fr->open = 1;
+    }
+    pthread_mutex_unlock(&fr->mu);
+}
+
+Eav1Walk *eav1rec_enter(const Dav1dFrameContext *f, const Dav1dTaskContext *t)
+{
+    Eav1Walk *w = &eav1_walk;
+    Eav1Rec *r = eav1rec_for_ctx(f->c);
+    w->r = r;
+    w->f = f;
+    w->t = t;
+    w->fr = &r->frames[f - f->c->fc];
+    if (!w->fr->open) frame_begin(w->fr, f);
+    w->list = NULL;
+    if (t && t->ts) {
+        const ptrdiff_t ti = t->ts - f->ts;
+        w->list = &w->fr->tiles[ti >= 0 && ti < w->fr->n_tiles ? ti : 0];
+    }
+    return w;
+}
+
+void eav1rec_block_begin(Eav1Walk *w, int bs)
+{
+    w->block_head = 1;
+    w->blk_w = dav1d_block_dimensions[bs][0] * 4;
+    w->blk_h = dav1d_block_dimensions[bs][1] * 4;
+    memset(w->region_live, 0, sizeof(w->region_live));
+    w->emu.valid = 0;
+    w->edge.valid = 0;
+    w->ac.valid = 0;
 }
 
 /* ------------------------------------------------------------------ pointer provenance */
@@ -145,16 +209,16 @@ static int locate(const Dav1dPicture *p, const void *ptr, int *plane, int *x, in
     return 0;
 }
 
-int eav1rec_locate_cur(const Eav1Rec *r, const void *p, int *x, int *y)
+int eav1rec_locate_cur(const Eav1Walk *w, const void *p, int *x, int *y)
 {
     int pl;
-    if (r->f && locate(&r->f->cur, p, &pl, x, y)) return pl;
+    if (w->f && locate(&w->f->cur, p, &pl, x, y)) return pl;
     return -1;
 }
 
-int eav1rec_locate_ref(const Eav1Rec *r, const void *p, int *plane, int *x, int *y)
+int eav1rec_locate_ref(const Eav1Walk *w, const void *p, int *plane, int *x, int *y)
 {
-    const Dav1dFrameContext *f = r->f;
+    const Dav1dFrameContext *f = w->f;
     if (!f) return -1;
     for (int i = 0; i < 7; i++)
         if (f->refp[i].p.data[0] && locate(&f->refp[i].p, p, plane, x, y)) return i;
@@ -165,7 +229,8 @@ int eav1rec_locate_ref(const Eav1Rec *r, const void *p, int *plane, int *x, int 
 /* ------------------------------------------------------------------ picture allocator
  * Replaces dav1d_default_picture_alloc (ext/dav1d/src/picture.c:46-80): same geometry
  * (128-aligned, planes contiguous Y,U,V, strides never a multiple of 1024), but the host
- * buffer is pinned and paired with a device-resident picture of the engine's pool. */
+ * buffer is pinned and paired with a device-resident picture of the engine's pool. A picture
+ * stays alive (host buffer and device slot) while a queued job still reads or writes it. */
 
 typedef struct HostBuf { void *p; size_t bytes; } HostBuf;
 typedef struct AllocState {
@@ -215,6 +280,10 @@ static int pic_alloc_cb(Dav1dPicture *pic, void *cookie)
     pd->dev_id = eav1cu_pic_alloc(r->cu, pic->p.w, pic->p.h, pic->p.layout, pic->p.bpc);
     if (pd->dev_id < 0) { eav1cu_host_free(pd->host_base); free(pd); return DAV1D_ERR(ENOMEM); }
     pd->rec = r;
+    pd->alloc_state = as;
+    atomic_init(&pd->refs, 1);
+    atomic_init(&pd->fence, 0);
+    atomic_init(&pd->failed, 0);
     uint8_t *d = pd->host_base;
     pic->data[0] = d;
     pic->data[1] = has_chroma ? d + y_sz : NULL;
@@ -226,11 +295,10 @@ static int pic_alloc_cb(Dav1dPicture *pic, void *cookie)
     return 0;
 }
 
-static void pic_release_cb(Dav1dPicture *pic, void *cookie)
+static void pd_unref(Eav1PicData *pd)
 {
-    AllocState *as = cookie;
-    Eav1PicData *pd = pic->allocator_data;
-    if (!pd) return;
+    if (atomic_fetch_sub(&pd->refs, 1) != 1) return;
+    AllocState *as = pd->alloc_state;
     eav1cu_pic_release(pd->rec->cu, pd->dev_id);
     int kept = 0;
     pthread_mutex_lock(&as->mu);
@@ -247,6 +315,12 @@ static void pic_release_cb(Dav1dPicture *pic, void *cookie)
     Eav1Rec *r = pd->rec;
     free(pd);
     if (last) destroy_rec(r, as);
+}
+
+static void pic_release_cb(Dav1dPicture *pic, void *cookie)
+{
+    (void)cookie;
+    if (pic->allocator_data) pd_unref(pic->allocator_data);
 }
 
 /* ------------------------------------------------------------------ tables */
@@ -277,6 +351,294 @@ static void fill_tables(Eav1Tables *t)
         }
 }
 
+/* ------------------------------------------------------------------ jobs */
+
+struct Eav1Job {
+    struct Eav1Job *next;
+    unsigned long long seq;
+    int skip;                           /* failed / aborted frame: only keeps the order going */
+    Eav1FrameDesc fd;
+    Eav1Cmd *cmds; size_t n_cmds, cap_cmds;
+    uint8_t *payload; size_t n_payload, cap_payload;
+    size_t arena_bytes;
+    Eav1LfRec *lf; size_t n_lf, cap_lf;
+    Eav1LrRec *lr; size_t n_lr, cap_lr;
+    uint8_t *lf_level; size_t cap_level;
+    uint8_t *lf_mask; size_t cap_mask;
+    Eav1PicData *cur, *ref[7];
+    void *cur_data[3]; ptrdiff_t cur_stride[2];
+};
+
+static Eav1Job *job_get(Eav1Rec *r)
+{
+    pthread_mutex_lock(&r->q_mu);
+    Eav1Job *j = r->job_free;
+    if (j) r->job_free = j->next;
+    pthread_mutex_unlock(&r->q_mu);
+    if (!j) { j = calloc(1, sizeof(*j)); if (!j) abort(); }
+    j->next = NULL; j->skip = 0; j->cur = NULL;
+    memset(j->ref, 0, sizeof(j->ref));
+    j->n_cmds = j->n_payload = j->n_lf = j->n_lr = 0;
+    return j;
+}
+
+static void job_free_all(Eav1Job *j)
+{
+    while (j) {
+        Eav1Job *n = j->next;
+        free(j->cmds); free(j->payload); free(j->lf); free(j->lr); free(j->lf_level); free(j->lf_mask);
+        free(j);
+        j = n;
+    }
+}
+
+static void enqueue(Eav1Rec *r, Eav1Job *j)
+{
+    pthread_mutex_lock(&r->q_mu);
+    Eav1Job **pp = &r->q_head;
+    while (*pp && (*pp)->seq < j->seq) pp = &(*pp)->next;
+    j->next = *pp;
+    *pp = j;
+    pthread_cond_broadcast(&r->q_cv);
+    pthread_mutex_unlock(&r->q_mu);
+}
+
+static Eav1PicData *pd_of(const Dav1dPicture *p)
+{
+    return p->data[0] ? p->allocator_data : NULL;
+}
+
+/* Detach everything recorded for the frame in slot f into a job. Runs on whichever thread
+ * finished the frame (under dav1d's task lock in threaded mode), so it only moves pointers and
+ * copies the two side tables dav1d is about to reuse (lf.level, lf.mask). */
+void eav1rec_frame_end(Eav1Rec *r, const Dav1dFrameContext *f, int retval)
+{
+    Eav1Frame *fr = &r->frames[f - f->c->fc];
+    unsigned long long seq = 0;
+    int have_seq = 0;
+    pthread_mutex_lock(&r->q_mu);
+    if (fr->seq_n > 0) {
+        seq = fr->seq_q[0];
+        memmove(&fr->seq_q[0], &fr->seq_q[1], sizeof(fr->seq_q[0]) * (size_t)(fr->seq_n - 1));
+        fr->seq_n--;
+        have_seq = 1;
+    }
+    pthread_mutex_unlock(&r->q_mu);
+    if (!have_seq) { fr->open = 0; return; }
+
+    Eav1Job *j = job_get(r);
+    j->seq = seq;
+    const Dav1dFrameHeader *const hdr = f->frame_hdr;
+    Eav1PicData *cur = pd_of(&f->cur);
+    int unsupported = atomic_load(&r->unsupported) || atomic_load(&fr->unsupported);
+    if (!retval && hdr && hdr->width[0] != hdr->width[1]) unsupported = 1;   /* super-res: not yet */
+    j->skip = retval != 0 || !cur || !hdr || unsupported;
+    if (!retval && unsupported && cur) {
+        fprintf(stderr, "easyav1_b200: unsupported coding tool in stream (no CPU fallback)\n");
+        atomic_store(&cur->failed, 1);
+        atomic_store(&r->error, EAV1CU_ERR_INVAL);
+    }
+    if (!j->skip) {
+        if (!fr->open) frame_begin(fr, f);
+        Eav1FrameDesc *fd = &j->fd;
+        memset(fd, 0, sizeof(*fd));
+        fd->w = f->cur.p.w; fd->h = f->cur.p.h;
+        fd->bpc = f->cur.p.bpc;
+        fd->layout = f->cur.p.layout;
+        fd->bw4 = f->bw; fd->bh4 = f->bh;
+        fd->sb128 = f->seq_hdr->sb128;
+        fd->cur = cur->dev_id;
+        j->cur = cur;
+        atomic_fetch_add(&cur->refs, 1);
+        atomic_store(&cur->fence, FENCE_PENDING);
+        for (int i = 0; i < 7; i++) {
+            Eav1PicData *rp = IS_INTER_OR_SWITCH(hdr) ? pd_of(&f->refp[i].p) : NULL;
+            fd->ref[i] = rp ? rp->dev_id : -1;
+            j->ref[i] = rp;
+            if (rp) atomic_fetch_add(&rp->refs, 1);
+        }
+        for (int i = 0; i < 3; i++) j->cur_data[i] = f->cur.data[i];
+        j->cur_stride[0] = f->cur.stride[0]; j->cur_stride[1] = f->cur.stride[1];
+        /* command lists: tiles are independent in reconstruction, so any tile order is legal */
+        size_t total = 0;
+        for (int i = 0; i < fr->n_tiles; i++) total += fr->tiles[i].n;
+        j->cmds = grow(j->cmds, &j->cap_cmds, total + 1, sizeof(Eav1Cmd));
+        size_t pos = 0;
+        for (int i = 0; i < fr->n_tiles; i++) {
+            memcpy(j->cmds + pos, fr->tiles[i].cmds, fr->tiles[i].n * sizeof(Eav1Cmd));
+            pos += fr->tiles[i].n;
+        }
+        j->n_cmds = total;
+        /* payload / lf / lr: swap buffers with the frame slot */
+        { uint8_t *p = j->payload; size_t c = j->cap_payload;
+          j->payload = fr->payload; j->cap_payload = fr->cap_payload; j->n_payload = atomic_load(&fr->n_payload);
+          fr->payload = p; fr->cap_payload = c; }
+        { Eav1LfRec *p = j->lf; size_t c = j->cap_lf;
+          j->lf = fr->lf; j->cap_lf = fr->cap_lf; j->n_lf = fr->n_lf; fr->lf = p; fr->cap_lf = c; }
+        { Eav1LrRec *p = j->lr; size_t c = j->cap_lr;
+          j->lr = fr->lr; j->cap_lr = fr->cap_lr; j->n_lr = fr->n_lr; fr->lr = p; fr->cap_lr = c; }
+        j->arena_bytes = atomic_load(&fr->arena_used);
+        fd->lf_recs = j->lf; fd->n_lf_recs = j->n_lf;
+        fd->lr_recs = j->lr; fd->n_lr_recs = j->n_lr;
+        fd->b4_stride = (int)f->b4_stride;
+        fd->lf_level_bytes = (size_t)f->b4_stride * 32 * f->sb128h * 4;
+        if (j->n_lf) {
+            j->lf_level = grow(j->lf_level, &j->cap_level, fd->lf_level_bytes, 1);
+            memcpy(j->lf_level, f->lf.level, fd->lf_level_bytes);
+        }
+        fd->lf_level = j->lf_level;
+        memcpy(fd->lut_e, f->lf.lim_lut.e, 64);
+        memcpy(fd->lut_i, f->lf.lim_lut.i, 64);
+        fd->cdef_enable = f->seq_hdr->cdef && (f->c->inloop_filters & DAV1D_INLOOPFILTER_CDEF);
+        fd->cdef_damping = hdr->cdef.damping;
+        for (int i = 0; i < 8; i++) {
+            fd->cdef_y_strength[i] = (uint8_t)hdr->cdef.y_strength[i];
+            fd->cdef_uv_strength[i] = (uint8_t)hdr->cdef.uv_strength[i];
+        }
+        fd->sb128w = f->sb128w; fd->sb128h = f->sb128h;
+        if (fd->cdef_enable) {
+            const size_t mb = (size_t)f->sb128w * f->sb128h * sizeof(Av1Filter);
+            j->lf_mask = grow(j->lf_mask, &j->cap_mask, mb, 1);
+            memcpy(j->lf_mask, f->lf.mask, mb);
+        }
+        fd->lf_mask = j->lf_mask;
+    }
+    fr->open = 0;
+    enqueue(r, j);
+}
+
+/* The submit thread: takes jobs strictly in decode order, hands them to the engine, queues the
+ * device->host copy of the finished planes and publishes the fence get_picture waits on. */
+static void *submit_main(void *arg)
+{
+    Eav1Rec *r = arg;
+    pthread_mutex_lock(&r->q_mu);
+    for (;;) {
+        while (!r->q_stop && !(r->q_head && r->q_head->seq == r->seq_submit))
+            pthread_cond_wait(&r->q_cv, &r->q_mu);
+        if (!(r->q_head && r->q_head->seq == r->seq_submit)) break;   /* stop, nothing runnable */
+        Eav1Job *j = r->q_head;
+        r->q_head = j->next;
+        r->q_busy = 1;
+        pthread_mutex_unlock(&r->q_mu);
+
+        if (!j->skip) {
+            int res = atomic_load(&r->error);
+            if (!res)
+                res = eav1cu_frame_submit(r->cu, &j->fd, j->cmds, j->n_cmds, j->payload, j->n_payload, j->arena_bytes);
+            unsigned long long ticket = 0;
+            if (!res) res = eav1cu_pic_download_async(r->cu, j->fd.cur, j->cur_data, j->cur_stride);
+            if (!res) res = eav1cu_fence(r->cu, &ticket);
+            if (res) {
+                char msg[256] = "";
+                eav1cu_last_error(r->cu, msg, sizeof(msg));
+                fprintf(stderr, "easyav1_b200: frame reconstruction failed (%d) %s\n", res, msg);
+                atomic_store(&r->error, res);
+                atomic_store(&j->cur->failed, 1);
+            }
+            atomic_store(&j->cur->fence, ticket);
+            atomic_fetch_add(&r->frames_submitted, 1);
+        }
+        pthread_mutex_lock(&r->q_mu);
+        r->seq_submit++;
+        r->q_busy = 0;
+        pthread_cond_broadcast(&r->q_idle);
+        pthread_mutex_unlock(&r->q_mu);
+        /* the pictures may go once the engine has the launches queued: device slots are reused
+         * in stream order, and the host buffer of `cur` stays referenced by its Dav1dPicture or,
+         * for a frame nobody keeps, is only recycled after the fence below */
+        if (!j->skip) {
+            Eav1PicData *cur = j->cur;
+            const unsigned long long t = atomic_load(&cur->fence);
+            if (atomic_load(&cur->refs) == 1 && t) eav1cu_fence_wait(r->cu, t);
+            pd_unref(cur);
+            for (int i = 0; i < 7; i++) if (j->ref[i]) pd_unref(j->ref[i]);
+        }
+        pthread_mutex_lock(&r->q_mu);
+        j->next = r->job_free;
+        r->job_free = j;
+    }
+    pthread_mutex_unlock(&r->q_mu);
+    return NULL;
+}
+
+/* block until the picture's planes are in host memory; returns 0 or DAV1D_ERR(EIO) */
+static int pd_wait(Eav1Rec *r, Eav1PicData *pd)
+{
+    if (!pd) return 0;
+    if (atomic_load(&pd->fence) == FENCE_PENDING) {
+        pthread_mutex_lock(&r->q_mu);
+        while (atomic_load(&pd->fence) == FENCE_PENDING && !r->q_stop)
+            pthread_cond_wait(&r->q_idle, &r->q_mu);
+        pthread_mutex_unlock(&r->q_mu);
+    }
+    const unsigned long long t = atomic_load(&pd->fence);
+    if (t && t != FENCE_PENDING && eav1cu_fence_wait(r->cu, t)) return DAV1D_ERR(EIO);
+    return atomic_load(&pd->failed) ? DAV1D_ERR(EIO) : 0;
+}
+
+/* ------------------------------------------------------------------ hooks into the frame life cycle
+ * host/Makefile renames the CALLS (not the definitions) of three reference functions:
+ *   obu.c:          dav1d_submit_frame       -> eav1hook_submit_frame        (decode.c:3321)
+ *   thread_task.c:  dav1d_decode_frame_init  -> eav1hook_decode_frame_init   (decode.c:2750)
+ *   thread_task.c,
+ *   lib.c:          dav1d_decode_frame_exit  -> eav1hook_decode_frame_exit   (decode.c:3242)
+ */
+
+/* Frames enter the decoder here one at a time, in decode order: hand out the order ticket. */
+int eav1hook_submit_frame(Dav1dContext *const c)
+{
+    Eav1Rec *r = eav1rec_for_ctx(c);
+    if (!r) return dav1d_submit_frame(c);
+    const unsigned idx = c->n_fc > 1 ? c->frame_thread.next : 0;
+    Eav1Frame *fr = &r->frames[idx];
+    pthread_mutex_lock(&r->q_mu);
+    const unsigned long long seq = r->seq_assign++;
+    if (fr->seq_n < 4) fr->seq_q[fr->seq_n++] = seq;
+    pthread_mutex_unlock(&r->q_mu);
+    const int res = dav1d_submit_frame(c);
+    /* Single-threaded decoding has finished the frame by now; if it failed before reaching the
+     * last filter row (or the threaded path refused the frame) the ticket is still queued. */
+    int orphan = 0;
+    pthread_mutex_lock(&r->q_mu);
+    if (c->n_fc == 1 || res < 0)
+        for (int i = 0; i < fr->seq_n; i++)
+            if (fr->seq_q[i] == seq) {
+                memmove(&fr->seq_q[i], &fr->seq_q[i + 1], sizeof(fr->seq_q[0]) * (size_t)(fr->seq_n - 1 - i));
+                fr->seq_n--;
+                orphan = 1;
+                break;
+            }
+    pthread_mutex_unlock(&r->q_mu);
+    if (orphan) {
+        fr->open = 0;
+        Eav1Job *j = job_get(r);
+        j->seq = seq;
+        j->skip = 1;
+        enqueue(r, j);
+    }
+    return res;
+}
+
+int eav1hook_decode_frame_init(Dav1dFrameContext *const f)
+{
+    const int res = dav1d_decode_frame_init(f);
+    Eav1Rec *r = eav1rec_for_ctx(f->c);
+    if (r && !res) {
+        Eav1Frame *fr = &r->frames[f - f->c->fc];
+        fr->open = 0;
+        frame_begin(fr, f);
+    }
+    return res;
+}
+
+void eav1hook_decode_frame_exit(Dav1dFrameContext *const f, const int retval)
+{
+    Eav1Rec *r = eav1rec_for_ctx(f->c);
+    if (r) eav1rec_frame_end(r, f, retval);
+    dav1d_decode_frame_exit(f, retval);
+}
+
 /* ------------------------------------------------------------------ open / close */
 
 static void destroy_rec(Eav1Rec *r, AllocState *as)
@@ -285,19 +647,44 @@ static void destroy_rec(Eav1Rec *r, AllocState *as)
     pthread_mutex_lock(&g_mu);
     for (int i = 0; i < MAX_RECS; i++) if (g_recs[i] == r) g_recs[i] = NULL;
     pthread_mutex_unlock(&g_mu);
-    if (eav1_tls_rec == r) eav1_tls_rec = NULL;
+    if (eav1_walk.r == r) eav1_walk.r = NULL;
     if (as) {
         for (int i = 0; i < 32; i++) if (as->free_list[i].p) eav1cu_host_free(as->free_list[i].p);
         pthread_mutex_destroy(&as->mu);
         free(as);
     }
     if (r->cu) eav1cu_ctx_destroy(r->cu);
-    free(r->cmds); free(r->payload); free(r->lf); free(r->lr);
+    for (int i = 0; i < r->n_frames; i++) {
+        Eav1Frame *fr = &r->frames[i];
+        if (fr->tiles) for (int t = 0; t < EAV1_MAX_TILES; t++) free(fr->tiles[t].cmds);
+        free(fr->tiles); free(fr->payload); free(fr->lf); free(fr->lr);
+        pthread_mutex_destroy(&fr->mu);
+    }
+    free(r->frames);
+    job_free_all(r->q_head);
+    job_free_all(r->job_free);
+    pthread_mutex_destroy(&r->q_mu);
+    pthread_cond_destroy(&r->q_cv);
+    pthread_cond_destroy(&r->q_idle);
     free(r);
 }
 
+static void stop_submit_thread(Eav1Rec *r)
+{
+    if (!r->have_thread) return;
+    pthread_mutex_lock(&r->q_mu);
+    r->q_stop = 1;
+    pthread_cond_broadcast(&r->q_cv);
+    pthread_cond_broadcast(&r->q_idle);
+    pthread_mutex_unlock(&r->q_mu);
+    pthread_join(r->submit_thread, NULL);
+    r->have_thread = 0;
+}
+
 /* Drop-in for dav1d_open (ext/dav1d/src/lib.c:144): same signature and error codes. The GPU
- * ordinal comes from EASYAV1_CUDA_DEVICE (default 0) so easyav1.h stays unchanged. */
+ * ordinal comes from EASYAV1_CUDA_DEVICE (default 0) so easyav1.h stays unchanged. Threading is
+ * dav1d's own: n_threads / max_frame_delay keep their meaning (lib.c:100-142), the workers walk
+ * frames and tiles concurrently and only record; EASYAV1_THREADS overrides n_threads. */
 int dav1d_open(Dav1dContext **c_out, const Dav1dSettings *s)
 {
     if (!c_out || !s) return DAV1D_ERR(EINVAL);
@@ -305,6 +692,9 @@ int dav1d_open(Dav1dContext **c_out, const Dav1dSettings *s)
     AllocState *as = calloc(1, sizeof(*as));
     if (!r || !as) { free(r); free(as); return DAV1D_ERR(ENOMEM); }
     pthread_mutex_init(&as->mu, NULL);
+    pthread_mutex_init(&r->q_mu, NULL);
+    pthread_cond_init(&r->q_cv, NULL);
+    pthread_cond_init(&r->q_idle, NULL);
     as->rec = r;
     const char *dev = getenv("EASYAV1_CUDA_DEVICE");
     if (eav1cu_ctx_create(&r->cu, dev ? atoi(dev) : 0)) {
@@ -313,14 +703,33 @@ int dav1d_open(Dav1dContext **c_out, const Dav1dSettings *s)
         return DAV1D_ERR(ENODEV);
     }
     Dav1dSettings ss = *s;
-    ss.n_threads = 1;       /* host walk is serial per stream; streams scale across threads/GPUs */
-    ss.max_frame_delay = 1;
+    const char *thr = getenv("EASYAV1_THREADS");
+    if (thr) ss.n_threads = atoi(thr);
+    /* tile threads without frame threads would end frames inside decode.c where no hook
+     * reaches; a frame delay of 1 therefore means the plain single-threaded walk */
+    if (ss.max_frame_delay == 1) ss.n_threads = 1;
     ss.allocator.cookie = as;
     ss.allocator.alloc_picture_callback = pic_alloc_cb;
     ss.allocator.release_picture_callback = pic_release_cb;
+    /* the recorder must exist before the workers start: register under a placeholder first */
     const int res = eav1ref_dav1d_open(c_out, &ss);
     if (res < 0) { destroy_rec(r, as); return res; }
-    r->c = *c_out;
+    Dav1dContext *c = *c_out;
+    if (c->n_fc == 1 && c->n_tc > 1) {   /* cannot happen with dav1d's n_fc rule; be safe */
+        eav1ref_dav1d_close(c_out);
+        destroy_rec(r, as);
+        return DAV1D_ERR(EINVAL);
+    }
+    r->c = c;
+    r->threaded = c->n_fc > 1;
+    r->n_frames = (int)c->n_fc;
+    r->frames = calloc((size_t)r->n_frames, sizeof(Eav1Frame));
+    if (!r->frames) { eav1ref_dav1d_close(c_out); destroy_rec(r, as); return DAV1D_ERR(ENOMEM); }
+    for (int i = 0; i < r->n_frames; i++) {
+        pthread_mutex_init(&r->frames[i].mu, NULL);
+        r->frames[i].tiles = calloc(EAV1_MAX_TILES, sizeof(Eav1List));
+        if (!r->frames[i].tiles) { eav1ref_dav1d_close(c_out); destroy_rec(r, as); return DAV1D_ERR(ENOMEM); }
+    }
     Eav1Tables tab;
     fill_tables(&tab);
     if (eav1cu_set_tables(r->cu, &tab) ||
@@ -333,7 +742,8 @@ int dav1d_open(Dav1dContext **c_out, const Dav1dSettings *s)
     int ok = 0;
     for (int i = 0; i < MAX_RECS; i++) if (!g_recs[i]) { g_recs[i] = r; ok = 1; break; }
     pthread_mutex_unlock(&g_mu);
-    if (!ok) { eav1ref_dav1d_close(c_out); destroy_rec(r, as); return DAV1D_ERR(ENOMEM); }
+    if (ok && pthread_create(&r->submit_thread, NULL, submit_main, r) == 0) r->have_thread = 1;
+    if (!ok || !r->have_thread) { eav1ref_dav1d_close(c_out); destroy_rec(r, as); return DAV1D_ERR(ENOMEM); }
     /* remember the allocator state for close */
     r->alloc_state = as;
     return 0;
@@ -345,8 +755,9 @@ void dav1d_close(Dav1dContext **c_out)
 {
     if (!c_out || !*c_out) return;
     Eav1Rec *r = eav1rec_for_ctx(*c_out);
-    eav1ref_dav1d_close(c_out);
+    eav1ref_dav1d_close(c_out);     /* flushes: frames in flight end through the exit hook */
     if (!r) return;
+    stop_submit_thread(r);
     AllocState *as = r->alloc_state;
     pthread_mutex_lock(&as->mu);
     as->closing = 1;
@@ -355,87 +766,36 @@ void dav1d_close(Dav1dContext **c_out)
     if (!busy) destroy_rec(r, as);
 }
 
-/* ------------------------------------------------------------------ frame submit */
-
-static int dev_id_of(const Dav1dPicture *p)
-{
-    const Eav1PicData *pd = p->allocator_data;
-    return pd && p->data[0] ? pd->dev_id : -1;
-}
-
-/* Called after the host walk and the lf/lr sbrow drivers of the last superblock row ran.
- * Ships the frame's lists to the engine and brings the finished planes back into the
- * Dav1dPicture the application will see (ext/dav1d/include/dav1d/picture.h). */
-int eav1rec_frame_end(Eav1Rec *r, const Dav1dFrameContext *f)
-{
-    const Dav1dFrameHeader *const hdr = f->frame_hdr;
-    Eav1FrameDesc fd;
-    memset(&fd, 0, sizeof(fd));
-    fd.w = f->cur.p.w; fd.h = f->cur.p.h;
-    fd.bpc = f->cur.p.bpc;
-    fd.layout = f->cur.p.layout;
-    fd.bw4 = f->bw; fd.bh4 = f->bh;
-    fd.sb128 = f->seq_hdr->sb128;
-    fd.cur = dev_id_of(&f->cur);
-    for (int i = 0; i < 7; i++)
-        fd.ref[i] = IS_INTER_OR_SWITCH(hdr) ? dev_id_of(&f->refp[i].p) : -1;
-    fd.lf_recs = r->lf; fd.n_lf_recs = r->n_lf;
-    fd.lf_level = (const uint8_t *)f->lf.level;
-    fd.b4_stride = (int)f->b4_stride;
-    fd.lf_level_bytes = (size_t)f->b4_stride * 32 * f->sb128h * 4;
-    memcpy(fd.lut_e, f->lf.lim_lut.e, 64);
-    memcpy(fd.lut_i, f->lf.lim_lut.i, 64);
-    fd.cdef_enable = f->seq_hdr->cdef && (f->c->inloop_filters & DAV1D_INLOOPFILTER_CDEF);
-    fd.cdef_damping = hdr->cdef.damping;
-    for (int i = 0; i < 8; i++) {
-        fd.cdef_y_strength[i] = (uint8_t)hdr->cdef.y_strength[i];
-        fd.cdef_uv_strength[i] = (uint8_t)hdr->cdef.uv_strength[i];
-    }
-    fd.lf_mask = f->lf.mask;
-    fd.sb128w = f->sb128w; fd.sb128h = f->sb128h;
-    fd.lr_recs = r->lr; fd.n_lr_recs = r->n_lr;
-
-    int res = 0;
-    if (hdr->width[0] != hdr->width[1]) { r->unsupported = 1; res = EAV1CU_ERR_INVAL; } /* super-res: not yet */
-    if (!res && r->unsupported) res = EAV1CU_ERR_INVAL;
-    if (!res)
-        res = eav1cu_frame_submit(r->cu, &fd, r->cmds, r->n_cmds, r->payload, r->n_payload, r->arena_used);
-    if (!res) {
-        void *data[3] = { f->cur.data[0], f->cur.data[1], f->cur.data[2] };
-        res = eav1cu_pic_download(r->cu, fd.cur, data, f->cur.stride);
-    }
-    if (res) {
-        char msg[256] = "";
-        eav1cu_last_error(r->cu, msg, sizeof(msg));
-        fprintf(stderr, "easyav1_b200: frame reconstruction failed (%d) %s%s\n", res, msg,
-                r->unsupported ? " [unsupported coding tool in stream]" : "");
-        r->error = res;
-    }
-    r->n_cmds = r->n_payload = r->n_lf = r->n_lr = 0;
-    r->arena_used = 0;
-    r->frame_open = 0;
-    r->frames_submitted++;
-    return res;
-}
-
 /* for tools / tests: how many frames went through the engine and whether it failed */
-long long eav1rec_frames_submitted(const Dav1dContext *c) { Eav1Rec *r = eav1rec_for_ctx(c); return r ? r->frames_submitted : -1; }
-int eav1rec_error(const Dav1dContext *c) { Eav1Rec *r = eav1rec_for_ctx(c); return r ? r->error : -1; }
+long long eav1rec_frames_submitted(const Dav1dContext *c) { Eav1Rec *r = eav1rec_for_ctx(c); return r ? atomic_load(&r->frames_submitted) : -1; }
+int eav1rec_error(const Dav1dContext *c) { Eav1Rec *r = eav1rec_for_ctx(c); return r ? atomic_load(&r->error) : -1; }
 /* the engine context behind a Dav1dContext, for measurement (bench.py) */
 Eav1cuCtx *eav1rec_engine(const Dav1dContext *c) { Eav1Rec *r = eav1rec_for_ctx(c); return r ? r->cu : NULL; }
 long long eav1rec_launches(const Dav1dContext *c) { Eav1Rec *r = eav1rec_for_ctx(c); return r ? eav1cu_launch_count(r->cu) : -1; }
+/* wait until every frame handed over so far has been given to the engine */
+void eav1rec_drain(const Dav1dContext *c)
+{
+    Eav1Rec *r = eav1rec_for_ctx(c);
+    if (!r) return;
+    pthread_mutex_lock(&r->q_mu);
+    while ((r->q_head || r->q_busy) && !r->q_stop) pthread_cond_wait(&r->q_idle, &r->q_mu);
+    pthread_mutex_unlock(&r->q_mu);
+    eav1cu_sync(r->cu);
+}
 
-/* Drop-in for dav1d_get_picture (ext/dav1d/src/lib.c:458): the DSP surface we replace is void,
- * so engine failures are latched by the recorder and surfaced here as DAV1D_ERR(EIO); easyAV1
- * maps that to EASYAV1_STATUS_DECODER_ERROR (src/easyav1.c:2399-2412). No CPU fallback. */
-int eav1ref_dav1d_get_picture(Dav1dContext *c, Dav1dPicture *out);
+/* Drop-in for dav1d_get_picture (ext/dav1d/src/lib.c:458): the picture dav1d hands out was
+ * reconstructed asynchronously; wait for its planes to arrive in (pinned) host memory. The DSP
+ * surface we replace is void, so engine failures are latched and surface here as DAV1D_ERR(EIO);
+ * easyAV1 maps that to EASYAV1_STATUS_DECODER_ERROR (src/easyav1.c:2399-2412). No CPU fallback. */
 int dav1d_get_picture(Dav1dContext *c, Dav1dPicture *out)
 {
     const int res = eav1ref_dav1d_get_picture(c, out);
     Eav1Rec *r = eav1rec_for_ctx(c);
-    if (r && r->error) {
-        if (res == 0) dav1d_picture_unref(out);
-        return DAV1D_ERR(EIO);
+    if (!r) return res;
+    if (res == 0 && out->data[0]) {
+        const int w = pd_wait(r, out->allocator_data);
+        if (w) { dav1d_picture_unref(out); return w; }
     }
+    if (res == 0 && atomic_load(&r->error)) { dav1d_picture_unref(out); return DAV1D_ERR(EIO); }
     return res;
 }

@@ -20,7 +20,8 @@
 #include "src/wedge.h"
 #include "src/ipred_prepare.h"
 
-#define REC() Eav1Rec *const r = eav1_tls_rec
+#define REC() Eav1Walk *const r = &eav1_walk
+#define UNSUPPORTED(r) atomic_store(&(r)->r->unsupported, 1)
 
 #if BITDEPTH == 8
 #define BDMAX_ARG
@@ -31,10 +32,13 @@
 /* the reference's walk, renamed at compile time */
 void bitfn(eav1ref_recon_b_intra)(Dav1dTaskContext *t, enum BlockSize bs, enum EdgeFlags flags, const Av1Block *b);
 int  bitfn(eav1ref_recon_b_inter)(Dav1dTaskContext *t, enum BlockSize bs, const Av1Block *b);
+void bitfn(eav1ref_filter_sbrow_deblock_cols)(Dav1dFrameContext *f, int sby);
+void bitfn(eav1ref_filter_sbrow_deblock_rows)(Dav1dFrameContext *f, int sby);
+void bitfn(eav1ref_filter_sbrow_lr)(Dav1dFrameContext *f, int sby);
 
 /* ---------------------------------------------------------------- helpers */
 
-static void set_dst(Eav1Rec *r, Eav1Cmd *c, const void *dst, int w, int h, int reg, size_t elem)
+static void set_dst(Eav1Walk *r, Eav1Cmd *c, const void *dst, int w, int h, int reg, size_t elem)
 {
     int x, y;
     const int pl = eav1rec_locate_cur(r, dst, &x, &y);
@@ -90,7 +94,7 @@ static const uint8_t filt_v_of[N_2D_FILTERS] = { 0, 1, 2, 0, 1, 2, 0, 1, 2, 3 };
 
 /* Resolve a source pointer handed to an mc function: either inside a reference plane or
  * inside the emu_edge scratch patch announced by the preceding emu_edge call. */
-static int resolve_src(Eav1Rec *r, const pixel *src, int *ref, int *plane, int *sx, int *sy, int *iw, int *ih)
+static int resolve_src(Eav1Walk *r, const pixel *src, int *ref, int *plane, int *sx, int *sy, int *iw, int *ih)
 {
     if (r->emu.valid) {
         const ptrdiff_t off = (const uint8_t *)src - (const uint8_t *)r->emu.dst;
@@ -103,7 +107,7 @@ static int resolve_src(Eav1Rec *r, const pixel *src, int *ref, int *plane, int *
         }
     }
     const int i = eav1rec_locate_ref(r, src, plane, sx, sy);
-    if (i < 0) { r->unsupported = 1; return -1; }
+    if (i < 0) { UNSUPPORTED(r); return -1; }
     *ref = i;
     *iw = *ih = 1 << 24; /* in-bounds by construction: clamping is the identity */
     return 0;
@@ -111,7 +115,7 @@ static int resolve_src(Eav1Rec *r, const pixel *src, int *ref, int *plane, int *
 
 /* produce != 0: the caller writes the prep block; a write at the start of the scratch buffer
  * opens a fresh region (warp8x8t fills one region tile by tile at inner offsets) */
-static uint32_t tmp_region(Eav1Rec *r, const int16_t *tmp, int produce)
+static uint32_t tmp_region(Eav1Walk *r, const int16_t *tmp, int produce)
 {
     const int16_t *base = r->t->scratch.compinter[0];
     const ptrdiff_t off = tmp - base;
@@ -164,7 +168,7 @@ static void rec_emu_edge(intptr_t bw, intptr_t bh, intptr_t iw, intptr_t ih, int
     (void)src_stride;
     int pl, sx, sy;
     const int ref = eav1rec_locate_ref(r, src, &pl, &sx, &sy);
-    if (ref < 0) { r->unsupported = 1; r->emu.valid = 0; return; }
+    if (ref < 0) { UNSUPPORTED(r); r->emu.valid = 0; return; }
     r->emu.dst = dst; r->emu.dst_stride = dst_stride;
     r->emu.bw = (int)bw; r->emu.bh = (int)bh;
     r->emu.x = (int)x; r->emu.y = (int)y; r->emu.iw = (int)iw; r->emu.ih = (int)ih;
@@ -264,7 +268,7 @@ static void rec_resize(pixel *dst, ptrdiff_t ds, const pixel *src, ptrdiff_t ss,
 {
     REC();
     (void)dst; (void)ds; (void)src; (void)ss; (void)dst_w; (void)h; (void)src_w; (void)dx; (void)mx;
-    r->unsupported = 1; /* super-resolution: not yet on the device */
+    UNSUPPORTED(r); /* super-resolution: not yet on the device */
 }
 
 void bitfn(eav1rec_mc_dsp_init)(Dav1dMCDSPContext *const c)
@@ -316,7 +320,7 @@ bitfn(eav1rec_prepare_intra_edges)(const int x, const int have_left, const int y
     int ex, ey;
     const int pl = eav1rec_locate_cur(r, dst, &ex, &ey);
     r->edge.valid = pl >= 0;
-    if (pl < 0) { r->unsupported = 1; return mode; }
+    if (pl < 0) { UNSUPPORTED(r); return mode; }
     r->edge.topleft = topleft_out;
     r->edge.plane = pl; r->edge.ex = ex; r->edge.ey = ey;
     r->edge.mode = mode; r->edge.tw = tw; r->edge.th = th;
@@ -343,7 +347,7 @@ bitfn(eav1rec_prepare_intra_edges)(const int x, const int have_left, const int y
     return mode;
 }
 
-static void fill_edge(Eav1Rec *r, Eav1Cmd *c)
+static void fill_edge(Eav1Walk *r, Eav1Cmd *c)
 {
     c->u.ipred.ex = (int16_t)r->edge.ex; c->u.ipred.ey = (int16_t)r->edge.ey;
     c->u.ipred.mode = (uint8_t)r->edge.mode; c->u.ipred.have = (uint8_t)r->edge.have;
@@ -357,7 +361,7 @@ static void rec_ipred(const int m, pixel *dst, const pixel *topleft, int w, int 
     REC();
     Eav1Cmd *c = eav1rec_push(r);
     c->op = EAV1_OP_IPRED;
-    if (!r->edge.valid || r->edge.topleft != topleft || r->edge.mode != m) { r->unsupported = 1; c->op = EAV1_OP_NOP; return; }
+    if (!r->edge.valid || r->edge.topleft != topleft || r->edge.mode != m) { UNSUPPORTED(r); c->op = EAV1_OP_NOP; return; }
     set_dst(r, c, dst, w, h, REG_II, sizeof(pixel));
     if (c->flags & EAV1_F_DST_ARENA) c->plane = (uint8_t)r->edge.plane;
     fill_edge(r, c);
@@ -377,7 +381,7 @@ static void rec_cfl_ac(int16_t *ac, const pixel *ypx, ptrdiff_t stride, int w_pa
     int lx, ly;
     const int pl = eav1rec_locate_cur(r, ypx, &lx, &ly);
     r->ac.valid = pl == 0;
-    if (pl != 0) { r->unsupported = 1; return; }
+    if (pl != 0) { UNSUPPORTED(r); return; }
     r->ac.lx = lx; r->ac.ly = ly; r->ac.w_pad = w_pad; r->ac.h_pad = h_pad; r->ac.cw = cw; r->ac.ch = ch;
 }
 static void rec_cfl_pred(const int m, pixel *dst, const pixel *topleft, int w, int h, int alpha)
@@ -386,7 +390,7 @@ static void rec_cfl_pred(const int m, pixel *dst, const pixel *topleft, int w, i
     Eav1Cmd *c = eav1rec_push(r);
     c->op = EAV1_OP_CFL;
     if (!r->ac.valid || !r->edge.valid || r->edge.topleft != topleft || r->edge.mode != m ||
-        r->ac.cw != w || r->ac.ch != h) { r->unsupported = 1; c->op = EAV1_OP_NOP; return; }
+        r->ac.cw != w || r->ac.ch != h) { UNSUPPORTED(r); c->op = EAV1_OP_NOP; return; }
     set_dst(r, c, dst, w, h, REG_II, sizeof(pixel));
     fill_edge(r, c);
     c->u.ipred.lx = (int16_t)r->ac.lx; c->u.ipred.ly = (int16_t)r->ac.ly;
@@ -427,13 +431,14 @@ static void rec_lf_any(const int dir, pixel *dst, const uint32_t *mask, const ui
     REC();
     int x, y;
     const int pl = eav1rec_locate_cur(r, dst, &x, &y);
-    if (pl < 0) { r->unsupported = 1; return; }
+    if (pl < 0) { UNSUPPORTED(r); return; }
     const uint32_t any = mask[0] | mask[1] | (n_masks > 2 ? mask[2] : 0);
     if (!any) return;
-    Eav1LfRec *lr = eav1rec_push_lf(r);
+    Eav1LfRec v, *lr = &v;
     lr->x = (uint16_t)x; lr->y = (uint16_t)y; lr->plane = (uint8_t)pl; lr->dir = (uint8_t)dir; lr->pad = 0;
     lr->vmask[0] = mask[0]; lr->vmask[1] = mask[1]; lr->vmask[2] = n_masks > 2 ? mask[2] : 0;
     lr->lvl_off = (uint32_t)((const uint8_t *)lvl - (const uint8_t *)r->f->lf.level);
+    eav1rec_push_lf(r, &v);
 }
 #define LF_FN(name, dir, n) \
 static void name(pixel *dst, ptrdiff_t stride, const uint32_t *mask, const uint8_t (*lvl)[4], ptrdiff_t lvl_stride, \
@@ -452,12 +457,14 @@ static void rec_lr_any(const int kind, pixel *dst, int w, int h, const Loopresto
     REC();
     int x, y;
     const int pl = eav1rec_locate_cur(r, dst, &x, &y);
-    if (pl < 0) { r->unsupported = 1; return; }
-    Eav1LrRec *lr = eav1rec_push_lr(r);
+    if (pl < 0) { UNSUPPORTED(r); return; }
+    Eav1LrRec v, *lr = &v;
+    memset(&v, 0, sizeof(v));
     lr->x = (uint16_t)x; lr->y = (uint16_t)y; lr->w = (uint16_t)w; lr->h = (uint16_t)h;
     lr->plane = (uint8_t)pl; lr->edges = (uint8_t)edges; lr->kind = (uint8_t)kind;
     if (kind <= EAV1_LR_WIENER5) memcpy(lr->p.filter, params->filter, sizeof(lr->p.filter));
     else { lr->p.sgr.s0 = params->sgr.s0; lr->p.sgr.s1 = params->sgr.s1; lr->p.sgr.w0 = params->sgr.w0; lr->p.sgr.w1 = params->sgr.w1; }
+    eav1rec_push_lr(r, &v);
 }
 #define LR_FN(name, kind) \
 static void name(pixel *dst, ptrdiff_t stride, const_left_pixel_row left, const pixel *lpf, int w, int h, \
@@ -476,11 +483,11 @@ void bitfn(eav1rec_loop_restoration_dsp_init)(Dav1dLoopRestorationDSPContext *co
 /* CDEF is driven on the device (needs pixel-derived direction/variance): the host table
  * must never be reached because filter_sbrow below skips dav1d_filter_sbrow_cdef. */
 static int rec_cdef_dir(const pixel *dst, ptrdiff_t s, unsigned *var HIGHBD_DECL_SUFFIX)
-{ (void)dst; (void)s; *var = 0; if (eav1_tls_rec) eav1_tls_rec->unsupported = 1; return 0; }
+{ (void)dst; (void)s; *var = 0; if (eav1_walk.r) atomic_store(&eav1_walk.r->unsupported, 1); return 0; }
 static void rec_cdef_fb(pixel *dst, ptrdiff_t stride, const_left_pixel_row_2px left, const pixel *top, const pixel *bottom,
                         int pri, int sec, int dir, int damping, enum CdefEdgeFlags edges HIGHBD_DECL_SUFFIX)
 { (void)dst; (void)stride; (void)left; (void)top; (void)bottom; (void)pri; (void)sec; (void)dir; (void)damping; (void)edges;
-  if (eav1_tls_rec) eav1_tls_rec->unsupported = 1; }
+  if (eav1_walk.r) atomic_store(&eav1_walk.r->unsupported, 1); }
 void bitfn(eav1rec_cdef_dsp_init)(Dav1dCdefDSPContext *const c)
 {
     c->dir = rec_cdef_dir; c->fb[0] = c->fb[1] = c->fb[2] = rec_cdef_fb;
@@ -498,31 +505,53 @@ void bitfn(eav1rec_film_grain_dsp_init)(Dav1dFilmGrainDSPContext *const c)
 void bitfn(eav1rec_recon_b_intra)(Dav1dTaskContext *const t, const enum BlockSize bs,
                                   const enum EdgeFlags intra_edge_flags, const Av1Block *const b)
 {
-    Eav1Rec *r = eav1rec_for_ctx(t->c);
-    eav1rec_block_begin(r, t, bs);
+    eav1rec_block_begin(eav1rec_enter(t->f, t), bs);
     bitfn(eav1ref_recon_b_intra)(t, bs, intra_edge_flags, b);
 }
 
 int bitfn(eav1rec_recon_b_inter)(Dav1dTaskContext *const t, const enum BlockSize bs, const Av1Block *const b)
 {
-    Eav1Rec *r = eav1rec_for_ctx(t->c);
-    eav1rec_block_begin(r, t, bs);
+    eav1rec_block_begin(eav1rec_enter(t->f, t), bs);
     return bitfn(eav1ref_recon_b_inter)(t, bs, b);
 }
 
 void bitfn(eav1rec_backup_ipred_edge)(Dav1dTaskContext *const t) { (void)t; }
 void bitfn(eav1rec_copy_lpf)(Dav1dFrameContext *const f, pixel *const src[3], const int sby) { (void)f; (void)src; (void)sby; }
 
-/* Replaces dav1d_filter_sbrow (recon_tmpl.c:2100-2109). Deblocking and loop-restoration
- * drivers of the reference run against the recording tables; CDEF is skipped here (device
- * driven). After the last superblock row the whole frame is submitted. */
+/* The post-filter stages as dav1d's task scheduler calls them one by one (thread_task.c:809-864).
+ * Deblocking and loop-restoration drivers of the reference run against the recording tables;
+ * CDEF is driven on the device from the frame's Av1Filter array; super-res is not run yet. */
+void bitfn(eav1rec_filter_sbrow_deblock_cols)(Dav1dFrameContext *const f, const int sby)
+{
+    eav1rec_enter(f, NULL);
+    bitfn(eav1ref_filter_sbrow_deblock_cols)(f, sby);
+}
+void bitfn(eav1rec_filter_sbrow_deblock_rows)(Dav1dFrameContext *const f, const int sby)
+{
+    eav1rec_enter(f, NULL);
+    bitfn(eav1ref_filter_sbrow_deblock_rows)(f, sby);
+}
+void bitfn(eav1rec_filter_sbrow_cdef)(Dav1dTaskContext *const tc, const int sby) { (void)tc; (void)sby; }
+void bitfn(eav1rec_filter_sbrow_resize)(Dav1dFrameContext *const f, const int sby)
+{
+    (void)sby;
+    Eav1Walk *w = eav1rec_enter(f, NULL);
+    atomic_store(&w->fr->unsupported, 1);
+}
+void bitfn(eav1rec_filter_sbrow_lr)(Dav1dFrameContext *const f, const int sby)
+{
+    eav1rec_enter(f, NULL);
+    bitfn(eav1ref_filter_sbrow_lr)(f, sby);
+}
+
+/* Replaces dav1d_filter_sbrow (recon_tmpl.c:2100-2109), the single-threaded path: all stages
+ * of one superblock row; after the last row the frame is handed over. */
 void bitfn(eav1rec_filter_sbrow)(Dav1dFrameContext *const f, const int sby)
 {
-    Eav1Rec *r = eav1rec_for_ctx(f->c);
-    r->f = f;
-    bitfn(dav1d_filter_sbrow_deblock_cols)(f, sby);
-    bitfn(dav1d_filter_sbrow_deblock_rows)(f, sby);
-    if (f->frame_hdr->width[0] != f->frame_hdr->width[1]) r->unsupported = 1;
-    if (f->lf.restore_planes) bitfn(dav1d_filter_sbrow_lr)(f, sby);
-    if (sby == f->sbh - 1) eav1rec_frame_end(r, f);
+    Eav1Walk *w = eav1rec_enter(f, NULL);
+    bitfn(eav1ref_filter_sbrow_deblock_cols)(f, sby);
+    bitfn(eav1ref_filter_sbrow_deblock_rows)(f, sby);
+    if (f->frame_hdr->width[0] != f->frame_hdr->width[1]) atomic_store(&w->fr->unsupported, 1);
+    if (f->lf.restore_planes) bitfn(eav1ref_filter_sbrow_lr)(f, sby);
+    if (sby == f->sbh - 1) eav1rec_frame_end(w->r, f, 0);
 }

@@ -214,6 +214,14 @@ int  eav1cu_host_alloc(void **p, size_t bytes);
 void eav1cu_host_free(void *p);
 
 /* ---- frame reconstruction --------------------------------------------------------------- */
+/* Asynchronous variant of eav1cu_pic_download: queues the copies on the context's stream and
+ * returns; pair it with a fence. `data` must be pinned (eav1cu_host_alloc) to really overlap. */
+int  eav1cu_pic_download_async(Eav1cuCtx *ctx, int id, void *const data[3], const ptrdiff_t stride[2]);
+/* A fence marks everything queued so far on the context's stream; eav1cu_fence_wait blocks the
+ * calling host thread until that work has finished (callable from any thread). */
+int  eav1cu_fence(Eav1cuCtx *ctx, unsigned long long *ticket);
+int  eav1cu_fence_wait(Eav1cuCtx *ctx, unsigned long long ticket);
+
 /* Reconstruct one frame from its recorded commands (in host walk order) and run the in-loop
  * post filters; the result stays resident as picture fd->cur. Asynchronous on the context's
  * stream; eav1cu_pic_download / eav1cu_sync order after it. */

@@ -59,7 +59,7 @@ static void pic_setup(Picture &p, int w, int h, int layout, int bpc)
 extern "C" {
 
 int eav1cu_device_count(void) { return 1; }
-int eav1cu_ctx_create(Eav1cuCtx **out, int) { *out = new Eav1cuCtx(); return 0; }
+int eav1cu_ctx_create(Eav1cuCtx **out, int) { *out = new Eav1cuCtx(); (*out)->pics.reserve(512); return 0; }
 void eav1cu_ctx_destroy(Eav1cuCtx *c) { delete c; }
 int eav1cu_last_error(Eav1cuCtx *c, char *msg, size_t cap) { if (msg && cap) msg[0] = 0; return c->err; }
 int eav1cu_set_tables(Eav1cuCtx *c, const Eav1Tables *t) { c->tab = *t; c->have_tab = true; return 0; }
@@ -98,6 +98,11 @@ int eav1cu_pic_upload(Eav1cuCtx *c, int id, const void *const data[3], const ptr
 int eav1cu_pic_download(Eav1cuCtx *c, int id, void *const data[3], const ptrdiff_t stride[2]) { return pic_copy(c, id, data, stride, false); }
 int eav1cu_arena_upload(Eav1cuCtx *c, size_t off, const void *src, size_t n) { if (c->arena.size() < off + n) c->arena.resize(off + n); memcpy(c->arena.data() + off, src, n); return 0; }
 int eav1cu_arena_download(Eav1cuCtx *c, size_t off, void *dst, size_t n) { if (c->arena.size() < off + n) return EAV1CU_ERR_INVAL; memcpy(dst, c->arena.data() + off, n); return 0; }
+
+int eav1cu_pic_download_async(Eav1cuCtx *c, int id, void *const data[3], const ptrdiff_t stride[2])
+{ return eav1cu_pic_download(c, id, data, stride); }
+int eav1cu_fence(Eav1cuCtx *, unsigned long long *ticket) { static unsigned long long n; *ticket = ++n; return 0; }
+int eav1cu_fence_wait(Eav1cuCtx *, unsigned long long) { return 0; }
 
 int eav1cu_frame_submit(Eav1cuCtx *c, const Eav1FrameDesc *fd, const Eav1Cmd *cmds, size_t n,
                         const void *payload, size_t, size_t arena_bytes)

@@ -5,6 +5,7 @@
 #include <stdio.h>
 #include <string.h>
 #include <stdlib.h>
+#include <atomic>
 #include <mutex>
 #include <string>
 #include <vector>
@@ -16,6 +17,10 @@
 #include "sched.h"
 
 using namespace eav1;
+
+// Launch epochs are unique across every context of the process: a done-flag array that lands on
+// memory a destroyed context used can then never hold a value that looks current.
+static std::atomic<uint32_t> g_epoch{0};
 
 // ------------------------------------------------------------------ kernels
 
@@ -43,6 +48,7 @@ struct ReconArgs {
     uint32_t n_big, n_small;
     uint32_t n_big_ctas, n_workers;
     uint32_t epoch;
+    uint32_t debug;               // count executed units in ctrl[4] (EAV1_DEBUG_CHECK)
 };
 
 __device__ __forceinline__ uint32_t ld_acquire(const uint32_t *p)
@@ -99,6 +105,7 @@ __device__ __forceinline__ void recon_worker(const FrameCtx &fc, const ReconArgs
                 CTA_SYNC();
             }
         }
+        if (ra.debug && tid == 0) atomicAdd(&ra.ctrl[4], 1u);
         if (fed && tid == 0) {   // nobody polls the flag of a unit without consumers
             __threadfence();
             st_release(&ra.done[id], ra.epoch);
@@ -154,6 +161,14 @@ mc_kernel(FrameCtx fc, const Eav1Cmd *__restrict__ cmds, const uint32_t *__restr
     } else if (c.op == EAV1_OP_WARP) {
         exec_warp<BD>(fc, c, sm, lane, 32);
     }
+}
+
+// debugging aid (EAV1_DEBUG_CHECK=2): stream-ordered checksum of an uploaded buffer
+__global__ void checksum_kernel(const uint32_t *p, size_t n_words, unsigned long long *out)
+{
+    unsigned long long s = 0;
+    for (size_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_words; i += (size_t)gridDim.x * blockDim.x) s += p[i];
+    atomicAdd(out, s);
 }
 
 template <typename pixel>
@@ -261,6 +276,10 @@ struct Eav1cuCtx {
     uint32_t *d_ctrl = nullptr;
     uint32_t epoch = 0;
     int recon_grid = 148 * 4;
+    int debug_check = 0;
+    unsigned long long *d_sums = nullptr;   // [frame & 63][2]: device checksums of payload / cmds
+    unsigned long long h_sums[64][2] = {};  // host checksums of the same uploads
+    long long sum_frame[64] = {};
     int warp_mode = 0;   // 0: every chain on a CTA, 1: independent small chains on warps, 2: all small chains on warps
     int err = 0;
     std::string errmsg;
@@ -367,7 +386,9 @@ int eav1cu_ctx_create(Eav1cuCtx **out, int device)
     if (cudaSetDevice(device) != cudaSuccess ||
         cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess ||
         cudaMalloc(&ctx->d_tab, sizeof(Eav1Tables)) != cudaSuccess ||
-        cudaMalloc(&ctx->d_ctrl, 64) != cudaSuccess || cudaMemset(ctx->d_ctrl, 0, 64) != cudaSuccess) {
+        cudaMalloc(&ctx->d_ctrl, 64) != cudaSuccess ||
+        cudaMemsetAsync(ctx->d_ctrl, 0, 64, ctx->stream) != cudaSuccess ||
+        cudaStreamSynchronize(ctx->stream) != cudaSuccess) {
         delete ctx;
         return EAV1CU_ERR_CUDA;
     }
@@ -380,6 +401,8 @@ int eav1cu_ctx_create(Eav1cuCtx **out, int device)
         ctx->recon_grid = sms * std::max(1, std::min(per8, per16));
     }
     if (const char *e = getenv("EAV1_WARP_MODE")) ctx->warp_mode = atoi(e);
+    if (const char *e = getenv("EAV1_DEBUG_CHECK")) ctx->debug_check = atoi(e) ? atoi(e) : 1;
+    if (ctx->debug_check == 2) { cudaMalloc(&ctx->d_sums, 64 * 2 * 8); cudaMemset(ctx->d_sums, 0, 64 * 2 * 8); cudaDeviceSynchronize(); }
     *out = ctx;
     return 0;
 }
@@ -770,7 +793,7 @@ static int plan_launch(Eav1cuCtx *ctx, FramePlan &pl)
         if (pl.n_chains > ctx->done_cap) return fail(ctx, EAV1CU_ERR_INVAL, "done-flag array smaller than the staged frame");
         ReconArgs ra;
         ra.cmds = pl.d_cmds; ra.deps = pl.d_deps;
-        ra.done = ctx->d_done; ra.ctrl = ctx->d_ctrl; ra.epoch = ++ctx->epoch;
+        ra.done = ctx->d_done; ra.ctrl = ctx->d_ctrl; ra.epoch = ctx->epoch = ++g_epoch;
         ra.big = pl.d_recs; ra.small = pl.d_recs + pl.n_big;
         ra.n_big = pl.n_big; ra.n_small = pl.n_small;
         // CTAs are split between the two kinds in proportion to their pixel work
@@ -781,9 +804,48 @@ static int plan_launch(Eav1cuCtx *ctx, FramePlan &pl)
         if (!pl.n_small) big_ctas = std::min<unsigned>(pl.n_big, grid);
         grid = big_ctas + small_ctas;
         ra.n_big_ctas = big_ctas; ra.n_workers = big_ctas + 4 * small_ctas;
+        ra.debug = ctx->debug_check == 1;
+        if (ctx->debug_check == 2) {
+            // verify what the kernels will read: checksum payload and commands on the device, in stream order
+            const int slot = (int)(ctx->n_frames & 63);
+            unsigned long long old[2];
+            if (ctx->sum_frame[slot]) {   // the entry written 64 frames ago has long completed: compare it
+                cudaMemcpy(old, ctx->d_sums + slot * 2, 16, cudaMemcpyDeviceToHost);
+                if (old[0] != ctx->h_sums[slot][0] || old[1] != ctx->h_sums[slot][1])
+                    fprintf(stderr, "EAV1 DEBUG: frame %lld upload mismatch payload %llx/%llx cmds %llx/%llx\n", ctx->sum_frame[slot] - 1, old[0], ctx->h_sums[slot][0], old[1], ctx->h_sums[slot][1]);
+            }
+            cudaMemsetAsync(ctx->d_sums + slot * 2, 0, 16, st);
+            unsigned long long hs = 0;
+            const uint32_t *hp = reinterpret_cast<const uint32_t *>(ctx->S().payload.h);
+            for (size_t i = 0; i < pl.payload_bytes / 4; i++) hs += hp[i];
+            ctx->h_sums[slot][0] = hs;
+            hs = 0;
+            hp = reinterpret_cast<const uint32_t *>(ctx->S().cmds.h);
+            for (size_t i = 0; i < pl.n_cmds * sizeof(Eav1Cmd) / 4; i++) hs += hp[i];
+            ctx->h_sums[slot][1] = hs;
+            ctx->sum_frame[slot] = ctx->n_frames + 1;
+            if (pl.payload_bytes) checksum_kernel<<<64, 256, 0, st>>>(reinterpret_cast<const uint32_t *>(pl.d_payload), pl.payload_bytes / 4, ctx->d_sums + slot * 2);
+            checksum_kernel<<<64, 256, 0, st>>>(reinterpret_cast<const uint32_t *>(pl.d_cmds), pl.n_cmds * sizeof(Eav1Cmd) / 4, ctx->d_sums + slot * 2 + 1);
+        }
+        if (ctx->debug_check == 1) {
+            uint32_t c[8];
+            CK(cudaStreamSynchronize(st));
+            CK(cudaMemcpy(c, ctx->d_ctrl, sizeof(c), cudaMemcpyDeviceToHost));
+            if (c[0] | c[1] | c[2]) fprintf(stderr, "EAV1 DEBUG: ctrl not armed before launch: %u %u %u (frame %lld)\n", c[0], c[1], c[2], ctx->n_frames);
+            CK(cudaMemset(ctx->d_ctrl + 4, 0, 4));
+            CK(cudaDeviceSynchronize());
+        }
         if (hbd) recon_frame_kernel<BD16><<<grid, 128, 0, st>>>(fc, ra);
         else     recon_frame_kernel<BD8><<<grid, 128, 0, st>>>(fc, ra);
         ctx->n_launches++;
+        if (ctx->debug_check == 1) {
+            uint32_t c[8];
+            CK(cudaStreamSynchronize(st));
+            CK(cudaMemcpy(c, ctx->d_ctrl, sizeof(c), cudaMemcpyDeviceToHost));
+            if (c[4] != pl.n_chains || (c[0] | c[1] | c[2]))
+                fprintf(stderr, "EAV1 DEBUG: frame %lld executed %u of %u units, ctrl after = %u %u %u, grid %u workers %u\n",
+                        ctx->n_frames, c[4], pl.n_chains, c[0], c[1], c[2], grid, ra.n_workers);
+        }
     }
 
     PfParams pp;

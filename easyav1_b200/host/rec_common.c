@@ -509,9 +509,39 @@ void eav1rec_frame_end(Eav1Rec *r, const Dav1dFrameContext *f, int retval)
 
 /* The submit thread: takes jobs strictly in decode order, hands them to the engine, queues the
  * device->host copy of the finished planes and publishes the fence get_picture waits on. */
+static uint64_t fnv(const void *p, size_t n, uint64_t h)
+{
+    const uint8_t *b = p;
+    for (size_t i = 0; i < n; i++) { h ^= b[i]; h *= 1099511628211ULL; }
+    return h;
+}
+
+/* EAV1_JOB_HASH=1: print a digest of every job (debugging aid for nondeterminism; the filter
+ * records are summed because their order legitimately depends on thread timing) */
+static void job_digest(const Eav1Job *j)
+{
+    if (atoi(getenv("EAV1_JOB_HASH")) == 2) {
+        if (j->seq < 3) fprintf(stderr, "JOB %llu cmds %zu payload %zu lf %zu lr %zu arena %zu cur %d w %d h %d bw4 %d first-coef-bytes %02x%02x%02x%02x\n", j->seq, j->n_cmds, j->n_payload, j->n_lf, j->n_lr, j->arena_bytes, j->fd.cur, j->fd.w, j->fd.h, j->fd.bw4, j->payload[0], j->payload[1], j->payload[2], j->payload[3]);
+        return;
+    }
+    uint64_t hc = fnv(j->cmds, j->n_cmds * sizeof(Eav1Cmd), 14695981039346656037ULL);
+    uint64_t hp = fnv(j->payload, j->n_payload, 14695981039346656037ULL);
+    uint64_t hl = 0, hr = 0;
+    for (size_t i = 0; i < j->n_lf; i++) hl += fnv(&j->lf[i], sizeof(Eav1LfRec), 14695981039346656037ULL);
+    for (size_t i = 0; i < j->n_lr; i++) hr += fnv(&j->lr[i], sizeof(Eav1LrRec), 14695981039346656037ULL);
+    uint64_t hv = j->n_lf ? fnv(j->lf_level, j->fd.lf_level_bytes, 1) : 0;
+    uint64_t hm = j->fd.cdef_enable ? fnv(j->lf_mask, (size_t)j->fd.sb128w * j->fd.sb128h * 1348, 1) : 0;
+    fprintf(stderr, "JOB %llu cmds %zu %016llx payload %zu %016llx lf %zu %016llx lr %zu %016llx lvl %016llx mask %016llx cur %d refs %d %d %d %d %d %d %d arena %zu\n",
+            j->seq, j->n_cmds, (unsigned long long)hc, j->n_payload, (unsigned long long)hp, j->n_lf, (unsigned long long)hl,
+            j->n_lr, (unsigned long long)hr, (unsigned long long)hv, (unsigned long long)hm, j->fd.cur,
+            j->fd.ref[0], j->fd.ref[1], j->fd.ref[2], j->fd.ref[3], j->fd.ref[4], j->fd.ref[5], j->fd.ref[6], j->arena_bytes);
+}
+
 static void *submit_main(void *arg)
 {
     Eav1Rec *r = arg;
+    const int digest = getenv("EAV1_JOB_HASH") != NULL;
+    const int sync_each = getenv("EAV1_SYNC_EACH") != NULL;
     pthread_mutex_lock(&r->q_mu);
     for (;;) {
         while (!r->q_stop && !(r->q_head && r->q_head->seq == r->seq_submit))
@@ -523,12 +553,14 @@ static void *submit_main(void *arg)
         pthread_mutex_unlock(&r->q_mu);
 
         if (!j->skip) {
+            if (digest) job_digest(j);
             int res = atomic_load(&r->error);
             if (!res)
                 res = eav1cu_frame_submit(r->cu, &j->fd, j->cmds, j->n_cmds, j->payload, j->n_payload, j->arena_bytes);
             unsigned long long ticket = 0;
             if (!res) res = eav1cu_pic_download_async(r->cu, j->fd.cur, j->cur_data, j->cur_stride);
             if (!res) res = eav1cu_fence(r->cu, &ticket);
+            if (!res && sync_each) res = eav1cu_sync(r->cu);
             if (res) {
                 char msg[256] = "";
                 eav1cu_last_error(r->cu, msg, sizeof(msg));
@@ -705,6 +737,8 @@ int dav1d_open(Dav1dContext **c_out, const Dav1dSettings *s)
     Dav1dSettings ss = *s;
     const char *thr = getenv("EASYAV1_THREADS");
     if (thr) ss.n_threads = atoi(thr);
+    const char *fdl = getenv("EASYAV1_FRAME_DELAY");
+    if (fdl) ss.max_frame_delay = atoi(fdl);
     /* tile threads without frame threads would end frames inside decode.c where no hook
      * reaches; a frame delay of 1 therefore means the plain single-threaded walk */
     if (ss.max_frame_delay == 1) ss.n_threads = 1;

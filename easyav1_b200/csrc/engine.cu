@@ -6,6 +6,7 @@
 #include <string.h>
 #include <stdlib.h>
 #include <atomic>
+#include <chrono>
 #include <mutex>
 #include <string>
 #include <vector>
@@ -277,6 +278,7 @@ struct Eav1cuCtx {
     uint32_t epoch = 0;
     int recon_grid = 148 * 4;
     int debug_check = 0;
+    double t_build = 0, t_launch = 0, t_wait = 0;   // host seconds spent in frame_submit (EAV1_TIMING)
     unsigned long long *d_sums = nullptr;   // [frame & 63][2]: device checksums of payload / cmds
     unsigned long long h_sums[64][2] = {};  // host checksums of the same uploads
     long long sum_frame[64] = {};
@@ -374,12 +376,28 @@ int eav1cu_device_count(void)
     return n;
 }
 
+// Contexts are recycled within the process: opening a decoder right after another one was
+// closed (the usual pattern of a player or a transcoder working through a playlist) finds its
+// stream, staging buffers and device pictures already allocated.
+static std::mutex g_cache_mu;
+static std::vector<Eav1cuCtx *> g_cache;
+static const size_t MAX_CACHED_CTX = 4;
+
 int eav1cu_ctx_create(Eav1cuCtx **out, int device)
 {
     if (!out) return EAV1CU_ERR_INVAL;
     *out = nullptr;
     int n = 0;
     if (cudaGetDeviceCount(&n) != cudaSuccess || n <= 0 || device >= n) return EAV1CU_ERR_NO_DEVICE;
+    {
+        std::lock_guard<std::mutex> g(g_cache_mu);
+        for (size_t i = 0; i < g_cache.size(); i++)
+            if (g_cache[i]->device == device) {
+                *out = g_cache[i];
+                g_cache.erase(g_cache.begin() + i);
+                return 0;
+            }
+    }
     Eav1cuCtx *ctx = new Eav1cuCtx();
     ctx->device = device;
     ctx->pics.reserve(512);   // never reallocates: other threads index it while frames are in flight
@@ -407,9 +425,12 @@ int eav1cu_ctx_create(Eav1cuCtx **out, int device)
     return 0;
 }
 
-void eav1cu_ctx_destroy(Eav1cuCtx *ctx)
+static void ctx_free(Eav1cuCtx *ctx)
 {
     if (!ctx) return;
+    if (getenv("EAV1_TIMING") && ctx->n_frames)
+        fprintf(stderr, "EAV1 TIMING: %lld frames; per frame on the submitting thread: slot wait %.3f ms, plan build + uploads %.3f ms, launches %.3f ms\n",
+                ctx->n_frames, 1e3 * ctx->t_wait / ctx->n_frames, 1e3 * ctx->t_build / ctx->n_frames, 1e3 * ctx->t_launch / ctx->n_frames);
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
     for (auto &p : ctx->pics) if (p.base) cudaFree(p.base);
@@ -430,6 +451,31 @@ void eav1cu_ctx_destroy(Eav1cuCtx *ctx)
     for (FramePlan *sp : ctx->staged) { for (void *d : sp->owned) cudaFree(d); delete sp; }
     if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
+}
+
+void eav1cu_ctx_destroy(Eav1cuCtx *ctx)
+{
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    bool keep = ctx->own_stream && !ctx->err && !getenv("EAV1_NO_CTX_CACHE");
+    if (keep) {
+        // back to a just-created state, keeping every allocation
+        if (getenv("EAV1_TIMING")) { ctx_free(ctx); return; }
+        for (FramePlan *sp : ctx->staged) { for (void *d : sp->owned) cudaFree(d); delete sp; }
+        ctx->staged.clear();
+        for (auto &p : ctx->pics) p.used = false;
+        ctx->have_tab = false;
+        ctx->capture = false; ctx->stage_timing = false;
+        for (auto &sp : ctx->spans) { ctx->ev_pool.push_back(sp.a); ctx->ev_pool.push_back(sp.b); }
+        ctx->spans.clear();
+        for (int i = 0; i < EAV1CU_N_STAGES; i++) { ctx->stage_ms[i] = 0; ctx->stage_launches[i] = 0; ctx->stage_calls[i] = 0; }
+        ctx->n_launches = ctx->h2d_bytes = ctx->d2h_bytes = ctx->n_frames = 0;
+        ctx->t_build = ctx->t_launch = ctx->t_wait = 0;
+        std::lock_guard<std::mutex> g(g_cache_mu);
+        if (g_cache.size() < MAX_CACHED_CTX) { g_cache.push_back(ctx); return; }
+    }
+    ctx_free(ctx);
 }
 
 int eav1cu_last_error(Eav1cuCtx *ctx, char *msg, size_t cap)
@@ -463,8 +509,8 @@ int eav1cu_set_masks(Eav1cuCtx *ctx, const uint8_t *blob, size_t bytes)
 {
     if (!ctx || !blob) return EAV1CU_ERR_INVAL;
     CK(cudaSetDevice(ctx->device));
-    if (ctx->d_masks) cudaFree(ctx->d_masks);
-    CK(cudaMalloc(&ctx->d_masks, bytes));
+    if (ctx->d_masks && ctx->masks_bytes != bytes) { cudaFree(ctx->d_masks); ctx->d_masks = nullptr; }
+    if (!ctx->d_masks) CK(cudaMalloc(&ctx->d_masks, bytes));
     CK(cudaMemcpy(ctx->d_masks, blob, bytes, cudaMemcpyHostToDevice));
     ctx->masks_bytes = bytes;
     return 0;
@@ -909,10 +955,17 @@ int eav1cu_frame_submit(Eav1cuCtx *ctx, const Eav1FrameDesc *fd,
     ctx->cur_slot ^= 1;
     Slot &sl = ctx->S();
     if (!sl.done) CK(cudaEventCreateWithFlags(&sl.done, cudaEventDisableTiming));
+    auto t0 = std::chrono::steady_clock::now();
     if (sl.used) CK(cudaEventSynchronize(sl.done));   // the frame two submits ago has finished with this slot
+    auto t1 = std::chrono::steady_clock::now();
     int r = plan_build(ctx, ctx->live, false, fd, cmds, n_cmds, payload, payload_bytes, arena_bytes);
     if (r) return r;
+    auto t2 = std::chrono::steady_clock::now();
     if ((r = plan_launch(ctx, ctx->live))) return r;
+    auto t3 = std::chrono::steady_clock::now();
+    ctx->t_wait += std::chrono::duration<double>(t1 - t0).count();
+    ctx->t_build += std::chrono::duration<double>(t2 - t1).count();
+    ctx->t_launch += std::chrono::duration<double>(t3 - t2).count();
     CK(cudaEventRecord(sl.done, ctx->stream));
     sl.used = true;
     ctx->n_frames++;

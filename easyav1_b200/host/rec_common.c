@@ -242,6 +242,35 @@ typedef struct AllocState {
 
 static void destroy_rec(Eav1Rec *r, AllocState *as);
 
+/* pinned buffers outlive a decoder: the next one opened in this process takes them over */
+#define PIN_POOL 64
+static HostBuf g_pin_pool[PIN_POOL];
+
+static int pin_pool_get(size_t total, HostBuf *out)
+{
+    int ok = 0;
+    pthread_mutex_lock(&g_mu);
+    for (int i = 0; i < PIN_POOL; i++)
+        if (g_pin_pool[i].p && g_pin_pool[i].bytes >= total && g_pin_pool[i].bytes <= total * 2) {
+            *out = g_pin_pool[i];
+            g_pin_pool[i].p = NULL;
+            ok = 1;
+            break;
+        }
+    pthread_mutex_unlock(&g_mu);
+    return ok;
+}
+
+static int pin_pool_put(HostBuf b)
+{
+    int ok = 0;
+    pthread_mutex_lock(&g_mu);
+    for (int i = 0; i < PIN_POOL; i++)
+        if (!g_pin_pool[i].p) { g_pin_pool[i] = b; ok = 1; break; }
+    pthread_mutex_unlock(&g_mu);
+    return ok;
+}
+
 static int pic_alloc_cb(Dav1dPicture *pic, void *cookie)
 {
     AllocState *as = cookie;
@@ -273,6 +302,10 @@ static int pic_alloc_cb(Dav1dPicture *pic, void *cookie)
             break;
         }
     pthread_mutex_unlock(&as->mu);
+    if (!pd->host_base) {
+        HostBuf hb;
+        if (pin_pool_get(total, &hb)) { pd->host_base = hb.p; pd->host_bytes = hb.bytes; }
+    }
     if (!pd->host_base) {
         if (eav1cu_host_alloc(&pd->host_base, total)) { free(pd); return DAV1D_ERR(ENOMEM); }
         pd->host_bytes = total;
@@ -681,7 +714,8 @@ static void destroy_rec(Eav1Rec *r, AllocState *as)
     pthread_mutex_unlock(&g_mu);
     if (eav1_walk.r == r) eav1_walk.r = NULL;
     if (as) {
-        for (int i = 0; i < 32; i++) if (as->free_list[i].p) eav1cu_host_free(as->free_list[i].p);
+        for (int i = 0; i < 32; i++)
+            if (as->free_list[i].p && !pin_pool_put(as->free_list[i])) eav1cu_host_free(as->free_list[i].p);
         pthread_mutex_destroy(&as->mu);
         free(as);
     }

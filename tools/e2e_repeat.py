@@ -15,18 +15,25 @@ host = load_host(os.path.join(ROOT, "tests/emu/libdav1d_b200_emu.so")) if os.env
 cap = man["w"] * man["h"] * 4
 buf = C.create_string_buffer(cap)
 for rep in range(int(sys.argv[2]) if len(sys.argv) > 2 else 5):
+    import time
     keep = C.create_string_buffer(obu, len(obu))
+    t0 = time.perf_counter()
     h = host.eav1_stream_open(keep, len(obu), 1, 7, 1)
+    t1 = time.perf_counter(); tfirst = None
     info, used, n, bad = StreamFrame(), C.c_size_t(0), 0, []
     keepf = []
     fast = bool(os.environ.get("E2E_FAST"))
     while True:
         r = host.eav1_stream_next(h, C.byref(info), buf, cap, C.byref(used))
         if r: break
+        if tfirst is None: tfirst = time.perf_counter()
         if fast: keepf.append(buf.raw[:used.value] if (os.environ["E2E_FAST"] == "2" or n % 8 == 7 or n >= len(man["frames"]) - 3) else None)
         elif n < len(man["frames"]) and hashlib.md5(buf.raw[:used.value]).hexdigest() != man["frames"][n]["md5"]: bad.append(n)
         n += 1
+    t2 = time.perf_counter()
     host.eav1_stream_close(h)
+    t3 = time.perf_counter()
+    print("  open %.1f ms, first frame after %.1f ms, decode loop %.1f ms (%.1f fps), close %.1f ms" % (1e3*(t1-t0), 1e3*(tfirst-t1), 1e3*(t2-t1), n/(t2-t1), 1e3*(t3-t2)))
     for i, fb in enumerate(keepf):
         if fb is not None and hashlib.md5(fb).hexdigest() != man["frames"][i]["md5"]: bad.append(i)
     print("pass", rep, "frames", n, "r", r, "bad", bad[:10])

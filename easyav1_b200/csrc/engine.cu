@@ -1009,6 +1009,27 @@ int eav1cu_plan_levels(const Eav1Cmd *cmds, size_t n_cmds, const int plane_w[3],
     return (int)plan.chains.size();
 }
 
+int eav1cu_plan_units(const Eav1Cmd *cmds, size_t n_cmds, const int plane_w[3], const int plane_h[3],
+                      uint32_t *unit_first, uint32_t *unit_count, uint32_t *unit_level, size_t cap_units,
+                      uint32_t *mc_items, size_t cap_items, size_t *n_items)
+{
+    if (!cmds || !plane_w || !plane_h) return EAV1CU_ERR_INVAL;
+    Scheduler sc;
+    UnitGraph g;
+    sc.reset(plane_w, plane_h);
+    sc.build_units(cmds, n_cmds, g);
+    std::vector<uint32_t> lvl;
+    Scheduler::unit_levels(g, &lvl);
+    for (size_t u = 0; u < g.unit_cmd.size() && u < cap_units; u++) {
+        if (unit_first) unit_first[u] = g.unit_cmd[u];
+        if (unit_count) unit_count[u] = g.unit_cnt[u];
+        if (unit_level) unit_level[u] = lvl[u];
+    }
+    for (size_t i = 0; i < g.mc_items.size() && i < cap_items; i++) if (mc_items) mc_items[i] = g.mc_items[i];
+    if (n_items) *n_items = g.mc_items.size();
+    return (int)g.unit_cmd.size();
+}
+
 int eav1cu_counters(Eav1cuCtx *ctx, long long out[4])
 {
     if (!ctx || !out) return EAV1CU_ERR_INVAL;

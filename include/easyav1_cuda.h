@@ -256,6 +256,12 @@ size_t eav1cu_abi_sizeof(int which);
  * (coding blocks) come back sorted by level; returns the number of chains. Needs no device. */
 int  eav1cu_plan_levels(const Eav1Cmd *cmds, size_t n_cmds, const int plane_w[3], const int plane_h[3],
                         uint32_t *chain_first, uint32_t *chain_level, size_t cap);
+/* Host-only: the two-phase plan eav1cu_frame_submit makes. Phase-1 motion-compensation items
+ * (command index | tile_x << 24 | tile_y << 26) and the dataflow units (first command, number of
+ * fused commands, dependency level) in decode order. Returns the number of units. */
+int  eav1cu_plan_units(const Eav1Cmd *cmds, size_t n_cmds, const int plane_w[3], const int plane_h[3],
+                       uint32_t *unit_first, uint32_t *unit_count, uint32_t *unit_level, size_t cap_units,
+                       uint32_t *mc_items, size_t cap_items, size_t *n_items);
 /* out[0] kernel launches, out[1] host->device bytes, out[2] device->host bytes, out[3] frames */
 int  eav1cu_counters(Eav1cuCtx *ctx, long long out[4]);
 int  eav1cu_set_capture(Eav1cuCtx *ctx, int on);

@@ -140,6 +140,27 @@ def encode(frames, advanced, quality=55, speed=6):
     return bio.getvalue()
 
 
+def encode_cv2(frames, depth, quality, speed):
+    """High-bit-depth clips: OpenCV's animated-AVIF writer (libavif/aom) takes 16-bit input."""
+    import cv2
+    arrs = []
+    for i, f in enumerate(frames):
+        a = np.asarray(f).astype(np.uint16)
+        # use the extra precision: a low-amplitude ramp below the 8-bit LSB
+        a = (a << (depth - 8)) + ((np.arange(a.shape[1])[None, :, None] + i) % (1 << (depth - 8))).astype(np.uint16)
+        arrs.append(cv2.cvtColor((a << (16 - depth)).astype(np.uint16), cv2.COLOR_RGB2BGR))
+    anim = cv2.Animation()
+    anim.frames = arrs
+    anim.durations = [33] * len(arrs)
+    path = "/tmp/_eav1_fixture.avif"
+    ok = cv2.imwriteanimation(path, anim, [cv2.IMWRITE_AVIF_DEPTH, depth, cv2.IMWRITE_AVIF_QUALITY, quality,
+                                          cv2.IMWRITE_AVIF_SPEED, speed])
+    assert ok
+    buf = open(path, "rb").read()
+    os.remove(path)
+    return buf
+
+
 def golden_md5(obu):
     from tests.refdec import decode_all_big as _dec
     decode_all = lambda o: _dec(o, 3840 * 2160 * 4)
@@ -163,6 +184,9 @@ CLIPS = {
     # (Wiener + SGR), OBMC (blend_v/blend_h), wedge / inter-intra / diff-weighted masks
     "cif_tools_s4": (352, 288, 7, 21, {"enable-cdef": "1", "enable-restoration": "1"}, 60, 4, 8.0),
     "cif_tools_s2": (352, 288, 7, 22, {"enable-cdef": "1", "enable-restoration": "1"}, 50, 2, 10.0),
+    # 10-bit 4:2:0 (the BITDEPTH=16 template of every kernel); encoded through OpenCV (depth key)
+    "cif_10bit": (352, 288, 6, 31, {"depth": 10}, 60, 4, 8.0),
+    "c4_720p_10bit": (1280, 720, 4, 32, {"depth": 10}, 60, 6, 6.0),
     # the bench workload (BASELINE.json configs[1]): same recipe, 120 frames. Speed 4 because
     # speed 6 never signals loop restoration on this content (checked from the recorded frames)
     "c2_1080p_bench": (1920, 1080, 120, 7, {"enable-cdef": "1", "enable-restoration": "1"}, 60, 4, 6.0),
@@ -179,14 +203,14 @@ def main():
         if only and name not in only:
             continue
         frames = synth_frames(w, h, n, seed, noise=noise)
-        avif = encode(frames, adv, q, spd)
+        avif = encode_cv2(frames, adv["depth"], q, spd) if "depth" in adv else encode(frames, adv, q, spd)
         samples = avif_samples(avif)
         ivf = os.path.join(HERE, name + ".ivf")
         write_ivf(ivf, samples, w, h)
         obu = b"".join(samples)
         g = golden_md5(obu)
         manifest[name] = {"file": name + ".ivf", "w": w, "h": h, "frames": g, "bytes": len(obu),
-                          "encoder": "Pillow AVIF/aom", "advanced": adv, "quality": q, "speed": spd,
+                          "encoder": "OpenCV AVIF/aom" if "depth" in adv else "Pillow AVIF/aom", "advanced": adv, "quality": q, "speed": spd,
                           "seed": seed, "noise": noise}
         print(name, len(samples), "samples", len(obu), "bytes ->", len(g), "decoded frames",
               [x["frame_type"] for x in g])

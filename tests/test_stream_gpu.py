@@ -7,7 +7,8 @@ import pytest
 
 from tests.conftest import fixture_obu
 
-CLIPS = ["intra_64x64_nofilt", "cif_intra", "cif_inter", "c1_360p", "c2_1080p"]
+CLIPS = ["intra_64x64_nofilt", "cif_intra", "cif_inter", "cif_tools_s4", "cif_tools_s2", "c1_360p", "c2_1080p",
+         "cif_10bit", "c4_720p_10bit"]
 
 
 @pytest.mark.gpu

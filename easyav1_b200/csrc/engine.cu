@@ -15,6 +15,7 @@
 #include "dev_common.cuh"
 #include "exec.cuh"
 #include "postfilter.cuh"
+#include "filmgrain.cuh"
 #include "sched.h"
 
 using namespace eav1;
@@ -204,6 +205,20 @@ lr_kernel(PfParams pp, const Eav1LrRec *__restrict__ recs)
     lr_tile<pixel>(pp, r, blockIdx.x, sm, threadIdx.x, blockDim.x);
 }
 
+__global__ void __launch_bounds__(256)
+fg_prepare_kernel(FgParams P)
+{
+    __shared__ FgSmem sm;
+    fg_prepare(P, sm, threadIdx.x, blockDim.x);
+}
+
+template <typename pixel>
+__global__ void __launch_bounds__(256)
+fg_apply_kernel(FgParams P)
+{
+    fg_strip<pixel>(P, blockIdx.x, blockIdx.y, threadIdx.x, blockDim.x);
+}
+
 // ------------------------------------------------------------------ context
 
 struct Picture {
@@ -275,6 +290,7 @@ struct Eav1cuCtx {
     std::vector<uint8_t> fed_tmp;
     uint32_t *d_done = nullptr; size_t done_cap = 0;
     uint32_t *d_ctrl = nullptr;
+    uint8_t *d_fg = nullptr;   // film grain: templates, scaling LUTs, block offsets
     uint32_t epoch = 0;
     int recon_grid = 148 * 4;
     int debug_check = 0;
@@ -444,6 +460,7 @@ static void ctx_free(Eav1cuCtx *ctx)
     for (cudaEvent_t e : ctx->fence_ev) if (e) cudaEventDestroy(e);
     if (ctx->d_done) cudaFree(ctx->d_done);
     if (ctx->d_ctrl) cudaFree(ctx->d_ctrl);
+    if (ctx->d_fg) cudaFree(ctx->d_fg);
     if (ctx->d_tab) cudaFree(ctx->d_tab);
     if (ctx->d_masks) cudaFree(ctx->d_masks);
     for (auto &sp : ctx->spans) { cudaEventDestroy(sp.a); cudaEventDestroy(sp.b); }
@@ -1099,6 +1116,48 @@ int eav1cu_staged_info(Eav1cuCtx *ctx, int idx, Eav1StagedInfo *out)
     out->cdef = p.fd.cdef_enable;
     out->n_cmds = (long long)p.n_cmds; out->payload_bytes = (long long)p.payload_bytes;
     for (int i = 0; i < 7; i++) if (p.fd.ref[i] >= 0) out->inter = 1;
+    return 0;
+}
+
+enum { FG_GRAIN_BYTES = 36864, FG_SCALE_BYTES = 3 * 4096, FG_OFFSET_BYTES = 65536 };
+
+int eav1cu_apply_grain(Eav1cuCtx *ctx, int src_pic, int dst_pic, const Eav1GrainParams *g)
+{
+    if (!ctx || !g) return EAV1CU_ERR_INVAL;
+    if (ctx->err) return ctx->err;
+    const int np = (int)ctx->pics.size();
+    if (src_pic < 0 || src_pic >= np || dst_pic < 0 || dst_pic >= np || src_pic == dst_pic ||
+        !ctx->pics[src_pic].base || !ctx->pics[dst_pic].base)
+        return fail(ctx, EAV1CU_ERR_INVAL, "apply_grain: bad picture id");
+    const Picture &src = ctx->pics[src_pic], &dst = ctx->pics[dst_pic];
+    if (src.w != dst.w || src.h != dst.h || src.layout != dst.layout || src.bpc != dst.bpc)
+        return fail(ctx, EAV1CU_ERR_INVAL, "apply_grain: geometry mismatch");
+    if (!ctx->have_tab) return fail(ctx, EAV1CU_ERR_INVAL, "apply_grain: tables not set");
+    if (g->ar_coeff_lag < 0 || g->ar_coeff_lag > 3 || g->num_y_points > 14 || g->num_uv_points[0] > 10 ||
+        g->num_uv_points[1] > 10)
+        return fail(ctx, EAV1CU_ERR_INVAL, "apply_grain: bad parameters");
+    CK(cudaSetDevice(ctx->device));
+    if (!ctx->d_fg) CK(cudaMalloc(&ctx->d_fg, FG_GRAIN_BYTES + FG_SCALE_BYTES + FG_OFFSET_BYTES));
+    FgParams P;
+    memset(&P, 0, sizeof(P));
+    P.g = *g;
+    for (int i = 0; i < 3; i++) { P.src[i] = src.pl[i]; P.dst[i] = dst.pl[i]; }
+    P.w = src.w; P.h = src.h; P.layout = src.layout;
+    P.ss_hor = src.layout != 3; P.ss_ver = src.layout == 1;
+    P.bitdepth_max = (1 << src.bpc) - 1;
+    P.rows = (src.h + 31) / 32; P.cols = (src.w + 31) / 32;
+    if ((size_t)P.rows * P.cols > FG_OFFSET_BYTES) return fail(ctx, EAV1CU_ERR_INVAL, "apply_grain: picture too large");
+    P.tab = ctx->d_tab;
+    P.grain = (int16_t *)ctx->d_fg;
+    P.scaling = ctx->d_fg + FG_GRAIN_BYTES;
+    P.offsets = ctx->d_fg + FG_GRAIN_BYTES + FG_SCALE_BYTES;
+    StageTimer tm(ctx, 5);
+    fg_prepare_kernel<<<1, 256, 0, ctx->stream>>>(P);
+    const dim3 grid((P.cols + FG_STRIP - 1) / FG_STRIP, P.rows);
+    if (src.bpc > 8) fg_apply_kernel<uint16_t><<<grid, 256, 0, ctx->stream>>>(P);
+    else fg_apply_kernel<uint8_t><<<grid, 256, 0, ctx->stream>>>(P);
+    ctx->n_launches += 2;
+    CK(cudaGetLastError());
     return 0;
 }
 

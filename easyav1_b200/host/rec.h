@@ -75,6 +75,7 @@ typedef struct Eav1Rec {
     int threaded;                       /* dav1d runs frame threads: frames end in the exit hook */
     /* job queue (decode order) */
     pthread_mutex_t q_mu; pthread_cond_t q_cv, q_idle;
+    pthread_mutex_t cu_mu;              /* engine calls: the submit thread vs. film grain at output time */
     Eav1Job *q_head, *job_free;
     unsigned long long seq_assign, seq_submit;
     int q_stop, q_busy;

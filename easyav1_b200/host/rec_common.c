@@ -384,12 +384,17 @@ static void fill_tables(Eav1Tables *t)
         }
 }
 
+/* the tables exactly as the product uploads them (operator-level tests drive the engine directly) */
+void eav1rec_fill_tables(Eav1Tables *t) { fill_tables(t); }
+size_t eav1rec_masks(const void **blob) { *blob = &dav1d_masks; return sizeof(dav1d_masks); }
+
 /* ------------------------------------------------------------------ jobs */
 
 struct Eav1Job {
     struct Eav1Job *next;
     unsigned long long seq;
     int skip;                           /* failed / aborted frame: only keeps the order going */
+    int no_download;                    /* never shown as is (film grain makes a new picture) */
     Eav1FrameDesc fd;
     Eav1Cmd *cmds; size_t n_cmds, cap_cmds;
     uint8_t *payload; size_t n_payload, cap_payload;
@@ -439,6 +444,14 @@ static void enqueue(Eav1Rec *r, Eav1Job *j)
 static Eav1PicData *pd_of(const Dav1dPicture *p)
 {
     return p->data[0] ? p->allocator_data : NULL;
+}
+
+/* ext/dav1d/src/lib.c:303-309 */
+static int has_grain(const Dav1dFrameHeader *hdr)
+{
+    const Dav1dFilmGrainData *fg = &hdr->film_grain.data;
+    return fg->num_y_points || fg->num_uv_points[0] || fg->num_uv_points[1] ||
+           (fg->clip_to_restricted_range && fg->chroma_scaling_from_luma);
 }
 
 /* Detach everything recorded for the frame in slot f into a job. Runs on whichever thread
@@ -492,6 +505,8 @@ void eav1rec_frame_end(Eav1Rec *r, const Dav1dFrameContext *f, int retval)
         }
         for (int i = 0; i < 3; i++) j->cur_data[i] = f->cur.data[i];
         j->cur_stride[0] = f->cur.stride[0]; j->cur_stride[1] = f->cur.stride[1];
+        /* output_image (lib.c:311-330) hands out a grain-synthesised copy, never this picture */
+        j->no_download = f->c->apply_grain && has_grain(hdr);
         /* command lists: tiles are independent in reconstruction, so any tile order is legal */
         size_t total = 0;
         for (int i = 0; i < fr->n_tiles; i++) total += fr->tiles[i].n;
@@ -588,12 +603,14 @@ static void *submit_main(void *arg)
         if (!j->skip) {
             if (digest) job_digest(j);
             int res = atomic_load(&r->error);
+            pthread_mutex_lock(&r->cu_mu);
             if (!res)
                 res = eav1cu_frame_submit(r->cu, &j->fd, j->cmds, j->n_cmds, j->payload, j->n_payload, j->arena_bytes);
             unsigned long long ticket = 0;
-            if (!res) res = eav1cu_pic_download_async(r->cu, j->fd.cur, j->cur_data, j->cur_stride);
+            if (!res && !j->no_download) res = eav1cu_pic_download_async(r->cu, j->fd.cur, j->cur_data, j->cur_stride);
             if (!res) res = eav1cu_fence(r->cu, &ticket);
             if (!res && sync_each) res = eav1cu_sync(r->cu);
+            pthread_mutex_unlock(&r->cu_mu);
             if (res) {
                 char msg[256] = "";
                 eav1cu_last_error(r->cu, msg, sizeof(msg));
@@ -641,6 +658,71 @@ static int pd_wait(Eav1Rec *r, Eav1PicData *pd)
     if (t && t != FENCE_PENDING && eav1cu_fence_wait(r->cu, t)) return DAV1D_ERR(EIO);
     return atomic_load(&pd->failed) ? DAV1D_ERR(EIO) : 0;
 }
+
+/* ------------------------------------------------------------------ film grain
+ * host/Makefile renames, in lib.c, the calls dav1d_apply_grain() makes once it has allocated the
+ * output picture (lib.c:485-524): dav1d_apply_grain_{8,16}bpc (single-threaded) and
+ * dav1d_task_delayed_fg (worker pool) both arrive here. `in` is device-resident once its frame
+ * has been handed to the engine; the grain kernels run behind it on the same stream and the new
+ * picture comes back like any other (fence on `out`, waited for in dav1d_get_picture). */
+static void apply_grain_gpu(Dav1dPicture *const out, const Dav1dPicture *const in)
+{
+    Eav1PicData *po = pd_of(out), *pi = pd_of(in);
+    if (!po || !pi) return;
+    Eav1Rec *r = po->rec;
+    /* wait until the frame that reconstructs `in` has been queued on the stream */
+    if (atomic_load(&pi->fence) == FENCE_PENDING) {
+        pthread_mutex_lock(&r->q_mu);
+        while (atomic_load(&pi->fence) == FENCE_PENDING && !r->q_stop)
+            pthread_cond_wait(&r->q_idle, &r->q_mu);
+        pthread_mutex_unlock(&r->q_mu);
+    }
+    if (atomic_load(&pi->failed) || atomic_load(&r->error)) { atomic_store(&po->failed, 1); return; }
+    const Dav1dFilmGrainData *d = &out->frame_hdr->film_grain.data;
+    Eav1GrainParams g;
+    memset(&g, 0, sizeof(g));
+    g.seed = d->seed;
+    g.num_y_points = d->num_y_points;
+    memcpy(g.y_points, d->y_points, sizeof(g.y_points));
+    g.chroma_scaling_from_luma = d->chroma_scaling_from_luma;
+    for (int i = 0; i < 2; i++) {
+        g.num_uv_points[i] = d->num_uv_points[i];
+        g.uv_mult[i] = d->uv_mult[i];
+        g.uv_luma_mult[i] = d->uv_luma_mult[i];
+        g.uv_offset[i] = d->uv_offset[i];
+    }
+    memcpy(g.uv_points, d->uv_points, sizeof(g.uv_points));
+    g.scaling_shift = d->scaling_shift;
+    g.ar_coeff_lag = d->ar_coeff_lag;
+    memcpy(g.ar_coeffs_y, d->ar_coeffs_y, sizeof(g.ar_coeffs_y));
+    memcpy(g.ar_coeffs_uv, d->ar_coeffs_uv, sizeof(g.ar_coeffs_uv));
+    g.ar_coeff_shift = (int32_t)d->ar_coeff_shift;
+    g.grain_scale_shift = d->grain_scale_shift;
+    g.overlap_flag = d->overlap_flag;
+    g.clip_to_restricted_range = d->clip_to_restricted_range;
+    g.mtrx_identity = out->seq_hdr->mtrx == DAV1D_MC_IDENTITY;
+    unsigned long long ticket = 0;
+    pthread_mutex_lock(&r->cu_mu);
+    int res = eav1cu_apply_grain(r->cu, pi->dev_id, po->dev_id, &g);
+    if (!res) res = eav1cu_pic_download_async(r->cu, po->dev_id, out->data, out->stride);
+    if (!res) res = eav1cu_fence(r->cu, &ticket);
+    pthread_mutex_unlock(&r->cu_mu);
+    if (res) {
+        fprintf(stderr, "easyav1_b200: film grain synthesis failed (%d)\n", res);
+        atomic_store(&r->error, res);
+        atomic_store(&po->failed, 1);
+    }
+    atomic_store(&po->fence, ticket);
+}
+
+void eav1hook_apply_grain_8bpc(const Dav1dFilmGrainDSPContext *const dsp, Dav1dPicture *const out,
+                               const Dav1dPicture *const in)
+{ (void)dsp; apply_grain_gpu(out, in); }
+void eav1hook_apply_grain_16bpc(const Dav1dFilmGrainDSPContext *const dsp, Dav1dPicture *const out,
+                                const Dav1dPicture *const in)
+{ (void)dsp; apply_grain_gpu(out, in); }
+void eav1hook_task_delayed_fg(Dav1dContext *const c, Dav1dPicture *const out, const Dav1dPicture *const in)
+{ (void)c; apply_grain_gpu(out, in); }
 
 /* ------------------------------------------------------------------ hooks into the frame life cycle
  * host/Makefile renames the CALLS (not the definitions) of three reference functions:
@@ -759,6 +841,7 @@ int dav1d_open(Dav1dContext **c_out, const Dav1dSettings *s)
     if (!r || !as) { free(r); free(as); return DAV1D_ERR(ENOMEM); }
     pthread_mutex_init(&as->mu, NULL);
     pthread_mutex_init(&r->q_mu, NULL);
+    pthread_mutex_init(&r->cu_mu, NULL);
     pthread_cond_init(&r->q_cv, NULL);
     pthread_cond_init(&r->q_idle, NULL);
     as->rec = r;

@@ -267,7 +267,7 @@ int  eav1cu_counters(Eav1cuCtx *ctx, long long out[4]);
 int  eav1cu_set_capture(Eav1cuCtx *ctx, int on);
 /* Per-stage device time (CUDA events on the context's stream around each stage of every
  * frame): index 0 dataflow reconstruction (intra, residual, compound/blend), 1 deblock, 2 CDEF,
- * 3 loop restoration, 4 motion compensation. Each array has EAV1CU_N_STAGES entries: accumulated
+ * 3 loop restoration, 4 motion compensation, 5 film grain. Each array has EAV1CU_N_STAGES entries: accumulated
  * milliseconds, kernel launches and stage invocations since the last reset. */
 #define EAV1CU_N_STAGES 6
 int  eav1cu_set_stage_timing(Eav1cuCtx *ctx, int on);
@@ -278,6 +278,31 @@ int  eav1cu_staged_info(Eav1cuCtx *ctx, int idx, Eav1StagedInfo *out);
 /* Run on a caller-owned cudaStream_t (passed as void*) so the caller can record its own
  * events around the launches; the context never destroys a stream it did not create. */
 int  eav1cu_set_stream(Eav1cuCtx *ctx, void *cuda_stream);
+
+/* ---- film grain synthesis ----------------------------------------------
+ * Replaces dav1d_apply_grain_{8,16}bpc (ext/dav1d/src/fg_apply_tmpl.c:225-241: prep_grain :100,
+ * apply_grain_row :161) and the Dav1dFilmGrainDSPContext entries behind it (filmgrain_tmpl.c:
+ * generate_grain_y :50, generate_grain_uv :88, fgy_32x32xn :169, fguv_32x32xn :278).
+ * Eav1GrainParams is Dav1dFilmGrainData (include/dav1d/headers.h:315-333) with fixed-width
+ * members plus the one sequence-header bit the chroma clip depends on. */
+typedef struct Eav1GrainParams {
+    uint32_t seed;
+    int32_t  num_y_points;
+    uint8_t  y_points[14][2];
+    int32_t  chroma_scaling_from_luma;
+    int32_t  num_uv_points[2];
+    uint8_t  uv_points[2][10][2];
+    int32_t  scaling_shift, ar_coeff_lag;
+    int8_t   ar_coeffs_y[24];
+    int8_t   ar_coeffs_uv[2][28];
+    int32_t  ar_coeff_shift, grain_scale_shift;
+    int32_t  uv_mult[2], uv_luma_mult[2], uv_offset[2];
+    int32_t  overlap_flag, clip_to_restricted_range;
+    int32_t  mtrx_identity;             /* seq_hdr->mtrx == DAV1D_MC_IDENTITY (fg_apply_tmpl.c:172) */
+} Eav1GrainParams;
+/* dst = src + grain, both device pictures of the same geometry; stream-ordered after every frame
+ * submitted so far. Three launches: grain templates + scaling LUTs + block offsets, then all planes. */
+int  eav1cu_apply_grain(Eav1cuCtx *ctx, int src_pic, int dst_pic, const Eav1GrainParams *g);
 
 #ifdef __cplusplus
 }

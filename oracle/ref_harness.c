@@ -361,14 +361,17 @@ void ref_lr_sgr(int bpc, int idx /*0=5x5,1=3x3,2=mix*/, void *dst, ptrdiff_t str
 
 /* Film grain applied to a whole picture through the reference driver
  * (ext/dav1d/src/fg_apply_tmpl.c:225-241). Planes are caller-owned. */
-void ref_apply_grain(int bpc, int w, int h, int layout, const Dav1dFilmGrainData *fg,
+void ref_apply_grain(int bpc, int w, int h, int layout, int mtrx_identity, const Dav1dFilmGrainData *fg,
                      void *const out_data[3], void *const in_data[3], const ptrdiff_t stride[2])
 {
     const Dav1dDSPContext *d = get_dsp(bpc);
     Dav1dPicture in, out;
     Dav1dFrameHeader fh;
-    memset(&in, 0, sizeof(in)); memset(&out, 0, sizeof(out)); memset(&fh, 0, sizeof(fh));
+    Dav1dSequenceHeader sh;
+    memset(&in, 0, sizeof(in)); memset(&out, 0, sizeof(out)); memset(&fh, 0, sizeof(fh)); memset(&sh, 0, sizeof(sh));
     fh.film_grain.data = *fg;
+    sh.mtrx = mtrx_identity ? DAV1D_MC_IDENTITY : DAV1D_MC_BT709;
+    in.seq_hdr = out.seq_hdr = &sh;
     in.frame_hdr = out.frame_hdr = &fh;
     in.p.w = out.p.w = w; in.p.h = out.p.h = h;
     in.p.layout = out.p.layout = layout; in.p.bpc = out.p.bpc = bpc;

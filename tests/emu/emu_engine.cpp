@@ -17,6 +17,7 @@
 #include "../../easyav1_b200/csrc/dev_common.cuh"
 #include "../../easyav1_b200/csrc/exec.cuh"
 #include "../../easyav1_b200/csrc/postfilter.cuh"
+#include "../../easyav1_b200/csrc/filmgrain.cuh"
 
 using namespace eav1;
 
@@ -56,10 +57,30 @@ static void pic_setup(Picture &p, int w, int h, int layout, int bpc)
 
 #include "emu_postfilter.inc"
 
+#include <execinfo.h>
+#include <signal.h>
+#include <unistd.h>
+// EAV1_EMU_BT=1: print a native backtrace on SIGSEGV (there is no debugger in the build container)
+#include <ucontext.h>
+static void segv_bt(int, siginfo_t *si, void *uc_)
+{
+    ucontext_t *uc = (ucontext_t *)uc_;
+    void *fr[48];
+    int n = backtrace(fr, 48);
+    backtrace_symbols_fd(fr, n, 2);
+    // a call through a bad pointer leaves no frame: the caller is on top of the stack
+    void **sp = (void **)uc->uc_mcontext.gregs[REG_RSP];
+    void *cand[8];
+    for (int i = 0; i < 8; i++) cand[i] = sp[i];
+    fprintf(stderr, "fault addr %p rip %p; stack words:\n", si->si_addr, (void *)uc->uc_mcontext.gregs[REG_RIP]);
+    backtrace_symbols_fd(cand, 8, 2);
+    _exit(139);
+}
+
 extern "C" {
 
 int eav1cu_device_count(void) { return 1; }
-int eav1cu_ctx_create(Eav1cuCtx **out, int) { *out = new Eav1cuCtx(); (*out)->pics.reserve(512); return 0; }
+int eav1cu_ctx_create(Eav1cuCtx **out, int) { if (getenv("EAV1_EMU_BT")) { struct sigaction sa; memset(&sa, 0, sizeof(sa)); sa.sa_sigaction = segv_bt; sa.sa_flags = SA_SIGINFO; sigaction(SIGSEGV, &sa, NULL); } *out = new Eav1cuCtx(); (*out)->pics.reserve(512); return 0; }
 void eav1cu_ctx_destroy(Eav1cuCtx *c) { delete c; }
 int eav1cu_last_error(Eav1cuCtx *c, char *msg, size_t cap) { if (msg && cap) msg[0] = 0; return c->err; }
 int eav1cu_set_tables(Eav1cuCtx *c, const Eav1Tables *t) { c->tab = *t; c->have_tab = true; return 0; }
@@ -151,6 +172,37 @@ int eav1cu_frame_submit(Eav1cuCtx *c, const Eav1FrameDesc *fd, const Eav1Cmd *cm
     }
     c->launches++;
     return emu_postfilter(c, fd, *A, cur);
+}
+
+int eav1cu_apply_grain(Eav1cuCtx *c, int src_pic, int dst_pic, const Eav1GrainParams *g)
+{
+    const Picture &src = c->pics[src_pic], &dst = c->pics[dst_pic];
+    static std::vector<uint8_t> buf(36864 + 3 * 4096 + 65536);
+    static FgSmem sm;
+    FgParams P;
+    memset(&P, 0, sizeof(P));
+    P.g = *g;
+    for (int i = 0; i < 3; i++) { P.src[i] = src.pl[i]; P.dst[i] = dst.pl[i]; }
+    P.w = src.w; P.h = src.h; P.layout = src.layout;
+    P.ss_hor = src.layout != 3; P.ss_ver = src.layout == 1;
+    P.bitdepth_max = (1 << src.bpc) - 1;
+    P.rows = (src.h + 31) / 32; P.cols = (src.w + 31) / 32;
+    P.tab = &c->tab;
+    P.grain = (int16_t *)buf.data();
+    P.scaling = buf.data() + 36864;
+    P.offsets = buf.data() + 36864 + 3 * 4096;
+    if (getenv("EAV1_EMU_STATS"))
+        fprintf(stderr, "grain: seed %u y-points %d uv-points %d %d cfl %d lag %d overlap %d clip %d shift %d\n", g->seed, g->num_y_points,
+                g->num_uv_points[0], g->num_uv_points[1], g->chroma_scaling_from_luma, g->ar_coeff_lag, g->overlap_flag,
+                g->clip_to_restricted_range, g->scaling_shift);
+    fg_prepare(P, sm, 0, 1);
+    for (int row = 0; row < P.rows; row++)
+        for (int s = 0; s < (P.cols + FG_STRIP - 1) / FG_STRIP; s++) {
+            if (src.bpc > 8) fg_strip<uint16_t>(P, s, row, 0, 1);
+            else fg_strip<uint8_t>(P, s, row, 0, 1);
+        }
+    c->launches += 2;
+    return 0;
 }
 
 } // extern "C"

@@ -134,8 +134,10 @@ def read_ivf(path):
 
 def encode(frames, advanced, quality=55, speed=6):
     bio = io.BytesIO()
+    advanced = dict(advanced)
+    subsampling = advanced.pop("subsampling", "4:2:0")
     frames[0].save(bio, format="AVIF", save_all=True, append_images=frames[1:], codec="aom",
-                   quality=quality, speed=speed, subsampling="4:2:0", duration=33,
+                   quality=quality, speed=speed, subsampling=subsampling, duration=33,
                    advanced=advanced)
     return bio.getvalue()
 
@@ -187,6 +189,17 @@ CLIPS = {
     # 10-bit 4:2:0 (the BITDEPTH=16 template of every kernel); encoded through OpenCV (depth key)
     "cif_10bit": (352, 288, 6, 31, {"depth": 10}, 60, 4, 8.0),
     "c4_720p_10bit": (1280, 720, 4, 32, {"depth": 10}, 60, 6, 6.0),
+    # film grain (aom's built-in parameter sets 1 and 15 = many scaling points without block overlap /
+    # chroma scaled from luma; and a grain table the encoder estimated itself from the noisy source)
+    "cif_grain_t1": (352, 288, 4, 41, {"film-grain-test": "1"}, 60, 6, 6.0),
+    "cif_grain_t15": (352, 288, 4, 42, {"film-grain-test": "15"}, 60, 6, 6.0),
+    "cif_grain_est": (352, 288, 5, 43, {"denoise-noise-level": "20"}, 60, 6, 8.0),
+    # other chroma layouts, lossless (Walsh-Hadamard), screen content (palette, intra block copy)
+    "cif_444": (352, 288, 5, 44, {"subsampling": "4:4:4"}, 60, 4, 6.0),
+    "cif_422": (352, 288, 5, 45, {"subsampling": "4:2:2"}, 60, 4, 6.0),
+    "cif_400": (352, 288, 4, 46, {"subsampling": "4:0:0"}, 60, 6, 6.0),
+    "qcif_lossless": (176, 144, 3, 47, {"subsampling": "4:4:4"}, 100, 6, 3.0),
+    "cif_screen": (352, 288, 5, 48, {"subsampling": "4:4:4", "tune-content": "screen"}, 60, 4, 0.0),
     # the bench workload (BASELINE.json configs[1]): same recipe, 120 frames. Speed 4 because
     # speed 6 never signals loop restoration on this content (checked from the recorded frames)
     "c2_1080p_bench": (1920, 1080, 120, 7, {"enable-cdef": "1", "enable-restoration": "1"}, 60, 4, 6.0),

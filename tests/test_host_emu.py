@@ -30,7 +30,8 @@ def emu():
     return run
 
 
-@pytest.mark.parametrize("name", ["intra_64x64_nofilt", "cif_intra", "cif_inter", "cif_tools_s4", "cif_tools_s2", "cif_10bit"])
+@pytest.mark.parametrize("name", ["intra_64x64_nofilt", "cif_intra", "cif_inter", "cif_tools_s4", "cif_tools_s2", "cif_10bit",
+                                  "cif_grain_t1", "cif_grain_t15", "cif_grain_est", "cif_444", "cif_422", "cif_400", "qcif_lossless", "cif_screen"])
 @pytest.mark.parametrize("threads", [1, 4])
 def test_recorded_frames_match_golden(emu, manifest, name, threads):
     """single-threaded walk and dav1d's frame/tile threading both give the golden frames"""

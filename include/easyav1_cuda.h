@@ -17,7 +17,7 @@
  *     lr_apply_tmpl.c:168)                                  side data, whole frame)
  *   dav1d_apply_grain_{8,16}bpc (src/fg_apply.h)          eav1cu_apply_grain
  *   Dav1dPicAllocator (include/dav1d/picture.h:133-145)   eav1cu_pic_alloc / _release / _download
- *   mdct_backward + vorbis_synthesis_blockin              eav1cu_vorbis_imdct_ola
+ *   mdct_backward + vorbis_synthesis_blockin              eav1cu_vorbis_open / _imdct_ola
  *     (ext/minivorbis/minivorbis.h:7054, 9195)
  *
  * Every function returns 0 on success or a negative EAV1CU_ERR_* code; CUDA errors are
@@ -303,6 +303,40 @@ typedef struct Eav1GrainParams {
 /* dst = src + grain, both device pictures of the same geometry; stream-ordered after every frame
  * submitted so far. Three launches: grain templates + scaling LUTs + block offsets, then all planes. */
 int  eav1cu_apply_grain(Eav1cuCtx *ctx, int src_pic, int dst_pic, const Eav1GrainParams *g);
+
+/* ---- Vorbis float slice ----------------------------------------------------
+ * Replaces, for a batch of decoded packets, mdct_backward (ext/minivorbis/minivorbis.h:7054-7148,
+ * called from mapping0_inverse :17825), the window + overlap-add of vorbis_synthesis_blockin
+ * (:9195-9300) and the planar -> interleaved copy of src/easyav1.c:2471-2492. The bit-serial part of
+ * vorbis_synthesis (floor1, residue, codebooks) stays on the host and produces the spectra.
+ * One object per audio track; the overlap state carries over between calls like
+ * vorbis_dsp_state.pcm does, eav1cu_vorbis_restart() is vorbis_synthesis_restart (:9159).
+ *   flags[n_blocks]    0 short / 1 long block (vorbis_block.W)
+ *   spectra            block-major: [block][channel][blocksize/2] floats, as mapping0_inverse holds
+ *                      them in vb->pcm[channel] just before the transform
+ *   pcm                planar [channel][cap_samples] or interleaved [sample][channels]
+ *   *n_samples         samples per channel made final by this batch: sum over consecutive block
+ *                      pairs of blocksize[lW]/4 + blocksize[W]/4 (the very first block of a stream
+ *                      only primes the overlap, minivorbis.h:9300-9308)
+ * window0 / window1: the half windows (blocksize/2 floats) the host's decoder uses
+ * (_vorbis_window_get, minivorbis.h:11992), or NULL to have them generated from the Vorbis window
+ * formula. Results match the reference within 1e-5 of full scale (different butterfly order). */
+typedef struct Eav1Vorbis Eav1Vorbis;
+int  eav1cu_vorbis_open(Eav1Vorbis **out, int device, int channels, int blocksize0, int blocksize1,
+                        const float *window0, const float *window1);
+void eav1cu_vorbis_close(Eav1Vorbis *v);
+int  eav1cu_vorbis_last_error(Eav1Vorbis *v, char *msg, size_t cap);
+int  eav1cu_vorbis_restart(Eav1Vorbis *v);
+int  eav1cu_vorbis_imdct_ola(Eav1Vorbis *v, const uint8_t *flags, int n_blocks, const float *spectra,
+                             float *pcm, size_t cap_samples, int interleave, size_t *n_samples);
+/* measurement: keep one batch resident in device memory, replay the kernel on it, read it back */
+int  eav1cu_vorbis_stage(Eav1Vorbis *v, const uint8_t *flags, int n_blocks, const float *spectra,
+                         int interleave, size_t *n_samples);
+int  eav1cu_vorbis_run_staged(Eav1Vorbis *v);
+int  eav1cu_vorbis_fetch(Eav1Vorbis *v, float *pcm, size_t cap_floats);
+int  eav1cu_vorbis_sync(Eav1Vorbis *v);
+int  eav1cu_vorbis_set_stream(Eav1Vorbis *v, void *cuda_stream);
+long long eav1cu_vorbis_launch_count(Eav1Vorbis *v);
 
 #ifdef __cplusplus
 }

@@ -1,0 +1,74 @@
+"""ctypes view of the reference's public C99 API (src/easyav1.h) as exported by
+libeasyav1_b200.so = the UNMODIFIED src/easyav1.c + nestegg compiled where they lie and linked
+against libdav1d_b200.so (easyav1_b200/host/Makefile). TEST INFRASTRUCTURE."""
+import ctypes as C
+import hashlib
+
+
+class Settings(C.Structure):   # easyav1_settings, src/easyav1.h:405-428
+    _fields_ = [("enable_video", C.c_int), ("enable_audio", C.c_int), ("skip_unprocessed_frames", C.c_int),
+                ("interlace_audio", C.c_int), ("close_handle_on_destroy", C.c_int),
+                ("cb_video", C.c_void_p), ("cb_audio", C.c_void_p), ("cb_userdata", C.c_void_p),
+                ("video_track", C.c_uint), ("audio_track", C.c_uint), ("use_fast_seeking", C.c_int),
+                ("audio_offset_time", C.c_int64), ("log_level", C.c_int)]
+
+
+class VideoFrame(C.Structure):   # easyav1_video_frame, src/easyav1.h:288-303
+    _fields_ = [("pixel_layout", C.c_int), ("bits_per_color", C.c_int), ("color_space", C.c_int),
+                ("color_primaries", C.c_int), ("transfer_characteristics", C.c_int), ("matrix_coefficients", C.c_int),
+                ("chroma_sample_position", C.c_int), ("width", C.c_uint), ("height", C.c_uint),
+                ("timestamp", C.c_uint64), ("data", C.c_void_p * 3), ("stride", C.c_size_t * 3)]
+
+
+def bind(path):
+    L = C.CDLL(path)
+    L.easyav1_default_settings.restype = Settings
+    L.easyav1_init_from_memory.restype = C.c_void_p
+    L.easyav1_init_from_memory.argtypes = [C.c_void_p, C.c_size_t, C.POINTER(Settings)]
+    L.easyav1_init_from_filename.restype = C.c_void_p
+    L.easyav1_init_from_filename.argtypes = [C.c_char_p, C.POINTER(Settings)]
+    L.easyav1_decode_next.argtypes = [C.c_void_p]
+    L.easyav1_has_video_frame.argtypes = [C.c_void_p]
+    L.easyav1_get_video_frame.restype = C.POINTER(VideoFrame)
+    L.easyav1_get_video_frame.argtypes = [C.c_void_p]
+    L.easyav1_is_finished.argtypes = [C.c_void_p]
+    L.easyav1_destroy.argtypes = [C.POINTER(C.c_void_p)]
+    L.easyav1_get_total_video_frames_processed.restype = C.c_uint64
+    L.easyav1_get_total_video_frames_processed.argtypes = [C.c_void_p]
+    return L
+
+
+def frame_md5(fr, bpc, layout):
+    """MD5 of the visible Y|U|V samples (same packing as the golden manifest)"""
+    bps = 2 if bpc > 8 else 1
+    w, h = fr.width, fr.height
+    sx, sy = int(layout != 3), int(layout == 1)
+    dims = [(w, h)] if layout == 0 else [(w, h), ((w + sx) >> sx, (h + sy) >> sy), ((w + sx) >> sx, (h + sy) >> sy)]
+    md = hashlib.md5()
+    for pl, (pw, ph) in enumerate(dims):
+        base, stride = fr.data[pl], fr.stride[pl]
+        for y in range(ph):
+            md.update(C.string_at(base + y * stride, pw * bps))
+    return md.hexdigest()
+
+
+def decode_webm(L, webm, bpc=8, layout=1):
+    """easyav1_init_from_memory -> easyav1_decode_next loop (the loop of easyav1.h:35-53); returns MD5s"""
+    keep = C.create_string_buffer(webm, len(webm))
+    st = L.easyav1_default_settings()
+    st.enable_audio = 0
+    st.log_level = 1
+    h = L.easyav1_init_from_memory(keep, len(webm), C.byref(st))
+    if not h:
+        raise RuntimeError("easyav1_init_from_memory failed")
+    out = []
+    try:
+        while L.easyav1_decode_next(h) == 1:
+            if L.easyav1_has_video_frame(h) == 1:
+                fr = L.easyav1_get_video_frame(h)
+                out.append(frame_md5(fr.contents, bpc, layout))
+        finished = L.easyav1_is_finished(h) == 1
+    finally:
+        hp = C.c_void_p(h)
+        L.easyav1_destroy(C.byref(hp))
+    return out, finished

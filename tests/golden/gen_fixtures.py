@@ -135,6 +135,7 @@ def read_ivf(path):
 def encode(frames, advanced, quality=55, speed=6):
     bio = io.BytesIO()
     advanced = dict(advanced)
+    advanced.pop("container", None)
     subsampling = advanced.pop("subsampling", "4:2:0")
     frames[0].save(bio, format="AVIF", save_all=True, append_images=frames[1:], codec="aom",
                    quality=quality, speed=speed, subsampling=subsampling, duration=33,
@@ -200,6 +201,11 @@ CLIPS = {
     "cif_400": (352, 288, 4, 46, {"subsampling": "4:0:0"}, 60, 6, 6.0),
     "qcif_lossless": (176, 144, 3, 47, {"subsampling": "4:4:4"}, 100, 6, 3.0),
     "cif_screen": (352, 288, 5, 48, {"subsampling": "4:4:4", "tune-content": "screen"}, 60, 4, 0.0),
+    # config C1 (easyav1_benchmark's input): 640x360 in a WebM container for the unchanged easyAV1 API.
+    # chroma-sample-position is set because easyav1_get_video_frame refuses streams that leave it
+    # unknown (src/easyav1.c:3493-3503)
+    "c1_360p_webm": (640, 360, 48, 2, {"enable-cdef": "1", "enable-restoration": "1", "chroma-sample-position": "1",
+                                       "container": "webm"}, 55, 6),
     # the bench workload (BASELINE.json configs[1]): same recipe, 120 frames. Speed 4 because
     # speed 6 never signals loop restoration on this content (checked from the recorded frames)
     "c2_1080p_bench": (1920, 1080, 120, 7, {"enable-cdef": "1", "enable-restoration": "1"}, 60, 4, 6.0),
@@ -220,6 +226,9 @@ def main():
         samples = avif_samples(avif)
         ivf = os.path.join(HERE, name + ".ivf")
         write_ivf(ivf, samples, w, h)
+        if adv.get("container") == "webm":
+            from tests.webm import mux_av1
+            open(os.path.join(HERE, name + ".webm"), "wb").write(mux_av1(samples, w, h))
         obu = b"".join(samples)
         g = golden_md5(obu)
         manifest[name] = {"file": name + ".ivf", "w": w, "h": h, "frames": g, "bytes": len(obu),

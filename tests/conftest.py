@@ -13,6 +13,26 @@ def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box)")
 
 
+def _ensure_built():
+    """The .so files are git-ignored: build what is missing (only possible where nvcc / gcc and,
+    for the host recorder and the checker, /root/reference exist; the GPU box gets them prebuilt)."""
+    need = [os.path.join(ROOT, "easyav1_b200", "libeasyav1_cuda.so"),
+            os.path.join(ROOT, "easyav1_b200", "libdav1d_b200.so"),
+            os.path.join(ROOT, "oracle", "_ref", "libdav1d_ref.so"),
+            os.path.join(ROOT, "tests", "emu", "libeav1_emu.so")]
+    if all(os.path.exists(p) for p in need):
+        return
+    import __graft_entry__
+    try:
+        __graft_entry__.build()
+    except Exception as e:  # the tests that need the missing piece report it themselves
+        sys.stderr.write("conftest: build() failed: %s\n" % e)
+
+
+def pytest_sessionstart(session):
+    _ensure_built()
+
+
 @pytest.fixture(scope="session")
 def manifest():
     return json.load(open(os.path.join(ROOT, "tests", "golden", "manifest.json")))

@@ -51,7 +51,16 @@ struct ReconArgs {
     uint32_t n_big_ctas, n_workers;
     uint32_t epoch;
     uint32_t debug;               // count executed units in ctrl[4] (EAV1_DEBUG_CHECK)
+    unsigned long long *trace;    // development aid (eav1cu_staged_trace): 6 words per unit, else null
 };
+
+#define EAV1_TRACE_WORDS 12
+__device__ __forceinline__ unsigned long long global_ns()
+{
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
 
 __device__ __forceinline__ uint32_t ld_acquire(const uint32_t *p)
 {
@@ -90,24 +99,51 @@ __device__ __forceinline__ void recon_worker(const FrameCtx &fc, const ReconArgs
         // draw the following ticket now: the round trip hides behind this chain's work
         if (tid == 0) next = atomicAdd(counter, 1u);
         const uint32_t first = r0.x, count = r0.y, d0 = r0.z, nd = r0.w;
+        unsigned long long t_ticket = 0, t_ready = 0;
+        if (ra.trace && tid == 0) t_ticket = global_ns();
         for (uint32_t d = tid; d < nd; d += nthr) {
             const uint32_t *flag = &ra.done[ra.deps[d0 + d]];
             unsigned ns = 20;
             while (ld_acquire(flag) != ra.epoch) { __nanosleep(ns); if (ns < 320) ns <<= 1; }
         }
         if (nd) CTA_SYNC();
+        if (ra.trace && tid == 0) {
+            t_ready = global_ns();
+            unsigned long long last = 0, who = ~0ull;
+            for (uint32_t d = 0; d < nd; d++) {
+                const uint32_t p = ra.deps[d0 + d];
+                const unsigned long long t = *(volatile unsigned long long *)&ra.trace[EAV1_TRACE_WORDS * (size_t)p + 2];
+                if (t >= last) { last = t; who = p; }
+            }
+            ra.trace[EAV1_TRACE_WORDS * (size_t)id + 3] = who;
+        }
+        long long cyc_stage = 0, cyc_op[3] = { 0, 0, 0 }, n_op[3] = { 0, 0, 0 };
         for (uint32_t base = 0; base < count; base += EAV1_CMD_STAGE) {
             const uint32_t n = min(count - base, (uint32_t)EAV1_CMD_STAGE);
             const uint32_t *src = reinterpret_cast<const uint32_t *>(&ra.cmds[first + base]);
             uint32_t *dst = reinterpret_cast<uint32_t *>(ws.cmd);
+            long long c0 = ra.trace ? clock64() : 0;
             for (uint32_t i = tid; i < n * (sizeof(Eav1Cmd) / 4); i += nthr) dst[i] = src[i];
             CTA_SYNC();
+            if (ra.trace) { const long long c1 = clock64(); cyc_stage += c1 - c0; c0 = c1; }
             for (uint32_t c = 0; c < n; c++) {
                 exec_cmd<BD>(fc, ws.cmd[c], sm, tid, nthr);
                 CTA_SYNC();
+                if (ra.trace) {
+                    const long long c1 = clock64();
+                    const int op = ws.cmd[c].op, k = op == EAV1_OP_ITX ? 1 : (op == EAV1_OP_IPRED || op == EAV1_OP_CFL) ? 0 : 2;
+                    cyc_op[k] += c1 - c0; n_op[k]++; c0 = c1;
+                }
             }
         }
         if (ra.debug && tid == 0) atomicAdd(&ra.ctrl[4], 1u);
+        if (ra.trace && tid == 0) {
+            unsigned long long *t = &ra.trace[EAV1_TRACE_WORDS * (size_t)id];
+            t[0] = t_ticket; t[1] = t_ready; t[2] = global_ns();
+            t[6] = cyc_stage; t[7] = cyc_op[0]; t[8] = cyc_op[1]; t[9] = cyc_op[2];
+            t[10] = (unsigned long long)n_op[0] << 32 | (unsigned long long)n_op[1]; t[11] = n_op[2];
+            t[4] = ((unsigned long long)first << 32) | count; t[5] = ((unsigned long long)k << 32) | (blockIdx.x << 8) | (nthr == 32 ? (threadIdx.x >> 5) : 255u);
+        }
         if (fed && tid == 0) {   // nobody polls the flag of a unit without consumers
             __threadfence();
             st_release(&ra.done[id], ra.epoch);
@@ -119,8 +155,11 @@ __device__ __forceinline__ void recon_worker(const FrameCtx &fc, const ReconArgs
     }
 }
 
+#ifndef EAV1_RECON_MIN_CTAS
+#define EAV1_RECON_MIN_CTAS 1
+#endif
 template <typename BD>
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(128, EAV1_RECON_MIN_CTAS)
 recon_frame_kernel(FrameCtx fc, ReconArgs ra)
 {
     __shared__ alignas(16) unsigned char scratch[4 * EAV1_WARP_SCRATCH > sizeof(CtaScratch) ? 4 * EAV1_WARP_SCRATCH : sizeof(CtaScratch)];
@@ -298,6 +337,8 @@ struct Eav1cuCtx {
     unsigned long long *d_sums = nullptr;   // [frame & 63][2]: device checksums of payload / cmds
     unsigned long long h_sums[64][2] = {};  // host checksums of the same uploads
     long long sum_frame[64] = {};
+    std::vector<uint32_t> est_tmp, order_tmp, bucket_tmp;
+    unsigned long long *d_trace = nullptr;   // set only inside eav1cu_staged_trace
     int warp_mode = 0;   // 0: every chain on a CTA, 1: independent small chains on warps, 2: all small chains on warps
     int err = 0;
     std::string errmsg;
@@ -762,9 +803,27 @@ static int plan_build(Eav1cuCtx *ctx, FramePlan &pl, bool staged, const Eav1Fram
             rt.resize(nc);
             size_t nb = 0;
             double px_big = 0, px_small = 0;
+            // Ticket order = earliest possible start (longest producer path, weighted by command
+            // count), ties in decode order. Any order in which producers precede consumers keeps
+            // the progress argument of recon_frame_kernel; this one makes the tickets held at any
+            // moment the frame's current wavefront instead of one stretch of superblock rows.
+            std::vector<uint32_t> &est = ctx->est_tmp, &order = ctx->order_tmp, &bucket = ctx->bucket_tmp;
+            est.resize(nc); order.resize(nc);
+            uint32_t est_max = 0;
+            for (size_t u = 0; u < nc; u++) {
+                uint32_t e = 0;
+                for (uint32_t d = g.dep_start[u]; d < g.dep_start[u + 1]; d++)
+                    e = std::max(e, est[g.deps[d]] + g.unit_cnt[g.deps[d]]);
+                est[u] = e; est_max = std::max(est_max, e);
+            }
+            bucket.assign((size_t)est_max + 2, 0);
+            for (size_t u = 0; u < nc; u++) bucket[est[u] + 1]++;
+            for (size_t b = 1; b < bucket.size(); b++) bucket[b] += bucket[b - 1];
+            for (size_t u = 0; u < nc; u++) order[bucket[est[u]]++] = (uint32_t)u;
             for (int pass = 0; pass < 2; pass++) {
                 size_t pos = pass ? nb : 0;
-                for (size_t u = 0; u < nc; u++) {
+                for (size_t oi = 0; oi < nc; oi++) {
+                    const size_t u = order[oi];
                     const Eav1Cmd &c = cmds[g.unit_cmd[u]];
                     const bool linked = fed[u] || g.dep_start[u + 1] != g.dep_start[u];
                     bool big = c.w > 32 || c.h > 32;
@@ -868,6 +927,7 @@ static int plan_launch(Eav1cuCtx *ctx, FramePlan &pl)
         grid = big_ctas + small_ctas;
         ra.n_big_ctas = big_ctas; ra.n_workers = big_ctas + 4 * small_ctas;
         ra.debug = ctx->debug_check == 1;
+        ra.trace = ctx->d_trace;
         if (ctx->debug_check == 2) {
             // verify what the kernels will read: checksum payload and commands on the device, in stream order
             const int slot = (int)(ctx->n_frames & 63);
@@ -1099,6 +1159,31 @@ int eav1cu_staged_replay(Eav1cuCtx *ctx, int idx)
     if (!ctx || idx < 0 || idx >= (int)ctx->staged.size()) return EAV1CU_ERR_INVAL;
     if (ctx->err) return ctx->err;
     return plan_launch(ctx, *ctx->staged[idx]);
+}
+
+/* Development aid: replay staged frame idx once with per-unit timestamps. out receives 6 words per
+ * dataflow unit, indexed by unit id (decode order): ticket drawn, producers ready, done (global
+ * timer, ns), id of the producer that finished last (~0 = none), first command << 32 | count,
+ * ticket << 32 | CTA << 8 | warp (255 = whole CTA). Returns the number of units, < 0 on error. */
+int eav1cu_staged_trace(Eav1cuCtx *ctx, int idx, unsigned long long *out, size_t cap_units)
+{
+    if (!ctx || !out || idx < 0 || idx >= (int)ctx->staged.size()) return EAV1CU_ERR_INVAL;
+    if (ctx->err) return ctx->err;
+    CK(cudaSetDevice(ctx->device));
+    FramePlan &pl = *ctx->staged[idx];
+    const size_t n = pl.n_chains;
+    if (n > cap_units) return EAV1CU_ERR_INVAL;
+    if (!n) return 0;
+    CK(cudaMalloc(&ctx->d_trace, n * EAV1_TRACE_WORDS * sizeof(unsigned long long)));
+    CK(cudaMemsetAsync(ctx->d_trace, 0, n * EAV1_TRACE_WORDS * sizeof(unsigned long long), ctx->stream));
+    int r = plan_launch(ctx, pl);
+    cudaError_t e = cudaStreamSynchronize(ctx->stream);
+    if (!r && e == cudaSuccess) e = cudaMemcpy(out, ctx->d_trace, n * EAV1_TRACE_WORDS * sizeof(unsigned long long), cudaMemcpyDeviceToHost);
+    cudaFree(ctx->d_trace);
+    ctx->d_trace = nullptr;
+    if (r) return r;
+    if (e != cudaSuccess) return fail(ctx, EAV1CU_ERR_CUDA, "staged trace", e);
+    return (int)n;
 }
 
 int eav1cu_staged_info(Eav1cuCtx *ctx, int idx, Eav1StagedInfo *out)

@@ -66,8 +66,18 @@ EAV1_DEV void exec_warp(const FrameCtx &fc, const Eav1Cmd &c, CtaScratch &sm, in
                       dst8, dst16, dstride, fc.bitdepth_max, sm.mc_mid, tid, nthr);
 }
 
+// Not inlined: the CTA-sized and the warp-sized worker of recon_frame_kernel share one copy of
+// every routine (the kernel's instruction footprint is what bounds short commands).
+#ifndef EAV1_DEDUPE
+#define EAV1_DEDUPE 1
+#endif
+#if EAV1_DEDUPE
+#define EAV1_EXEC_LINK EAV1_DEVN
+#else
+#define EAV1_EXEC_LINK EAV1_DEV
+#endif
 template <typename BD>
-EAV1_DEV void exec_cmd(const FrameCtx &fc, const Eav1Cmd &c, CtaScratch &sm, int tid, int nthr)
+EAV1_EXEC_LINK void exec_cmd(const FrameCtx &fc, const Eav1Cmd &c, CtaScratch &sm, int tid, int nthr)
 {
     typedef typename BD::pixel pixel;
     const int bdmax = fc.bitdepth_max;

@@ -487,6 +487,126 @@ EAV1_DEV TxDim tx_dim(int tx) {
     return d;
 }
 
+// ---- register path (both dimensions <= 32) ---------------------------------------------
+// One lane owns one row (first pass) and then one column (second pass) entirely in registers:
+// the coefficients are read straight from the payload (column-major, so consecutive lanes read
+// consecutive addresses), the only shared-memory traffic is the transpose between the passes,
+// and the second pass adds into the destination directly. One group barrier per transform.
+
+// N-point 1-D transform of kind `type` (T1D_FLIPADST is computed as ADST; the caller mirrors
+// the output index), in place on a register array.
+template <typename W, int N>
+EAV1_DEV void itx_1d_reg(int type, int (&v)[N], int mn, int mx) {
+    if (type == T1D_IDENTITY) {
+#pragma unroll
+        for (int i = 0; i < N; i++) {
+            if (N == 4) v[i] = v[i] + (int)(((W)v[i] * 1697 + 2048) >> 12);
+            else if (N == 8) v[i] *= 2;
+            else if (N == 16) v[i] = 2 * v[i] + (int)(((W)v[i] * 1697 + 1024) >> 11);
+            else v[i] *= 4;
+        }
+        return;
+    }
+    int o[N];
+    if (type == T1D_DCT || N == 32) {
+        if constexpr (N == 4) idct4<W>(v, o, mn, mx);
+        else if constexpr (N == 8) idct8<W>(v, o, mn, mx);
+        else if constexpr (N == 16) idct16<W>(v, o, mn, mx);
+        else idct32<W>(v, o, mn, mx);
+    } else {
+        if constexpr (N == 4) iadst4<W>(v, o);
+        else if constexpr (N == 8) iadst8<W>(v, o, mn, mx);
+        else if constexpr (N == 16) iadst16<W>(v, o, mn, mx);
+    }
+#pragma unroll
+    for (int i = 0; i < N; i++) v[i] = o[i];
+}
+
+// first pass of row y: coefficients -> s[x*P + y] (already rounded/clipped for the second pass)
+template <typename BD, int N>
+EAV1_DEV void itx_row_reg(const typename BD::coef *coeff, int sh, int y, int type, int is_rect2, int shift,
+                          int row_min, int row_max, int col_min, int col_max, int32_t *s, int P)
+{
+    typedef typename BD::wide W;
+    int v[N];
+#pragma unroll
+    for (int x = 0; x < N; x++) {
+        int c = coeff[y + x * sh];
+        if (is_rect2) c = (int)(((W)c * 181 + 128) >> 8);
+        v[x] = c;
+    }
+    itx_1d_reg<W, N>(type, v, row_min, row_max);
+    const int rnd = (1 << shift) >> 1;
+    const int flip = type == T1D_FLIPADST;
+#pragma unroll
+    for (int x = 0; x < N; x++)
+        s[(flip ? N - 1 - x : x) * P + y] = iclip((v[x] + rnd) >> shift, col_min, col_max);
+}
+
+// second pass of column x, added into dst
+template <typename BD, int N>
+EAV1_DEV void itx_col_reg(const int32_t *s, int P, int x, int type, int col_min, int col_max,
+                          typename BD::pixel *dst, int dst_stride, int bitdepth_max)
+{
+    typedef typename BD::wide W;
+    typedef typename BD::pixel pixel;
+    int v[N];
+#pragma unroll
+    for (int y = 0; y < N; y++) v[y] = s[x * P + y];
+    const int flip = type == T1D_FLIPADST;
+    pixel *d = dst + x;
+    if (N <= 16) {
+        // issue the destination loads before the butterflies so their latency hides behind them
+        int px[N];
+#pragma unroll
+        for (int y = 0; y < N; y++) px[y] = d[(flip ? N - 1 - y : y) * dst_stride];
+        itx_1d_reg<W, N>(type, v, col_min, col_max);
+#pragma unroll
+        for (int y = 0; y < N; y++)
+            d[(flip ? N - 1 - y : y) * dst_stride] = (pixel)iclip(px[y] + ((v[y] + 8) >> 4), 0, bitdepth_max);
+    } else {
+        itx_1d_reg<W, N>(type, v, col_min, col_max);
+#pragma unroll
+        for (int y = 0; y < N; y++) {
+            pixel *q = d + (flip ? N - 1 - y : y) * dst_stride;
+            *q = (pixel)iclip(*q + ((v[y] + 8) >> 4), 0, bitdepth_max);
+        }
+    }
+}
+
+template <typename BD>
+EAV1_DEVN void itx_add_reg(typename BD::pixel *dst, int dst_stride, const typename BD::coef *coeff, int w, int h,
+                           int shift, int rt, int ct, int bitdepth_max, int32_t *s, int tid, int nthr)
+{
+    const int is_rect2 = (w * 2 == h) || (h * 2 == w);
+    const int P = h + 1;
+    int row_min, col_min;
+    if (!BD::hbd) { row_min = col_min = -32768; }
+    else {
+        row_min = (int)((unsigned)~bitdepth_max << 7);
+        col_min = (int)((unsigned)~bitdepth_max << 5);
+    }
+    const int row_max = ~row_min, col_max = ~col_min;
+    for (int y = tid; y < h; y += nthr) {
+        switch (w) {
+        case 4:  itx_row_reg<BD, 4>(coeff, h, y, rt, is_rect2, shift, row_min, row_max, col_min, col_max, s, P); break;
+        case 8:  itx_row_reg<BD, 8>(coeff, h, y, rt, is_rect2, shift, row_min, row_max, col_min, col_max, s, P); break;
+        case 16: itx_row_reg<BD, 16>(coeff, h, y, rt, is_rect2, shift, row_min, row_max, col_min, col_max, s, P); break;
+        default: itx_row_reg<BD, 32>(coeff, h, y, rt, is_rect2, shift, row_min, row_max, col_min, col_max, s, P); break;
+        }
+    }
+    CTA_SYNC();
+    for (int x = tid; x < w; x += nthr) {
+        switch (h) {
+        case 4:  itx_col_reg<BD, 4>(s, P, x, ct, col_min, col_max, dst, dst_stride, bitdepth_max); break;
+        case 8:  itx_col_reg<BD, 8>(s, P, x, ct, col_min, col_max, dst, dst_stride, bitdepth_max); break;
+        case 16: itx_col_reg<BD, 16>(s, P, x, ct, col_min, col_max, dst, dst_stride, bitdepth_max); break;
+        default: itx_col_reg<BD, 32>(s, P, x, ct, col_min, col_max, dst, dst_stride, bitdepth_max); break;
+        }
+    }
+    CTA_SYNC();
+}
+
 // dst += inverse_transform(coef). `s` is the CTA's shared tile (>= 64*65 int32).
 template <typename BD>
 EAV1_DEVN void itx_add(typename BD::pixel *dst, int dst_stride /*pixels*/, const typename BD::coef *coeff,
@@ -525,6 +645,13 @@ EAV1_DEVN void itx_add(typename BD::pixel *dst, int dst_stride /*pixels*/, const
     }
     int rt, ct;
     txtp_1d_types(txtp, rt, ct);
+#ifndef EAV1_ITX_REG
+#define EAV1_ITX_REG 1
+#endif
+    if (EAV1_ITX_REG && w <= 32 && h <= 32) {
+        itx_add_reg<BD>(dst, dst_stride, coeff, w, h, d.shift, rt, ct, bitdepth_max, s, tid, nthr);
+        return;
+    }
     const int sh = imin(h, 32), sw = imin(w, 32);
     const int P = h + 1;
     int row_min, col_min;

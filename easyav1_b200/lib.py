@@ -84,4 +84,6 @@ def _bind_host(L):
     L.eav1rec_error.argtypes = [C.c_void_p]
     L.eav1rec_engine.restype = C.c_void_p
     L.eav1rec_engine.argtypes = [C.c_void_p]
+    L.eav1rec_drain.restype = None
+    L.eav1rec_drain.argtypes = [C.c_void_p]
     return L

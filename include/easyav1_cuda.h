@@ -275,6 +275,10 @@ int  eav1cu_stage_times(Eav1cuCtx *ctx, double *ms, long long *launches, long lo
 int  eav1cu_staged_count(Eav1cuCtx *ctx);
 int  eav1cu_staged_replay(Eav1cuCtx *ctx, int idx);
 int  eav1cu_staged_info(Eav1cuCtx *ctx, int idx, Eav1StagedInfo *out);
+/* Development aid: replay staged frame idx once with per-unit device timestamps. out gets 6 words
+ * per dataflow unit (index = unit id): ticket drawn, producers ready, done (ns), id of the producer
+ * that finished last (~0: none), first command << 32 | count, ticket << 32 | CTA << 8 | warp. */
+int  eav1cu_staged_trace(Eav1cuCtx *ctx, int idx, unsigned long long *out, size_t cap_units);
 /* Run on a caller-owned cudaStream_t (passed as void*) so the caller can record its own
  * events around the launches; the context never destroys a stream it did not create. */
 int  eav1cu_set_stream(Eav1cuCtx *ctx, void *cuda_stream);

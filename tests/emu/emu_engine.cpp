@@ -16,6 +16,7 @@
 #include "../../include/easyav1_cuda.h"
 #include "../../easyav1_b200/csrc/dev_common.cuh"
 #include "../../easyav1_b200/csrc/exec.cuh"
+#include "../../easyav1_b200/csrc/sched.h"
 #include "../../easyav1_b200/csrc/postfilter.cuh"
 #include "../../easyav1_b200/csrc/filmgrain.cuh"
 
@@ -139,6 +140,36 @@ int eav1cu_frame_submit(Eav1cuCtx *c, const Eav1FrameDesc *fd, const Eav1Cmd *cm
             static const char *nm[] = {"nop","mc","warp","avg","wavg","mask","wmask","blend","blendv","blendh","ipred","cfl","pal","itx"};
             for (int o = 1; o < 14; o++) if (hist[o]) fprintf(stderr, " %s %zu/%zuk", nm[o], hist[o], px[o] >> 10);
             fprintf(stderr, "\n");
+        }
+        if (getenv("EAV1_EMU_PLAN")) {   // planner analysis: critical path of the dataflow graph in commands
+            static eav1::Scheduler sch; static eav1::UnitGraph g;
+            const Picture &cp = c->pics[fd->cur];
+            int pw[3] = { cp.pl[0].w, cp.pl[1].w, cp.pl[2].w }, ph[3] = { cp.pl[0].h, cp.pl[1].h, cp.pl[2].h };
+            sch.reset(pw, ph);
+            sch.build_units(cmds, n, g);
+            const size_t nu = g.unit_cmd.size();
+            std::vector<uint32_t> cp_cmds(nu, 0), cp_units(nu, 0), pred(nu, UINT32_MAX);
+            size_t best = 0; size_t tot = 0, hist[8] = {0};
+            for (size_t u = 0; u < nu; u++) {
+                uint32_t m = 0, mu = 0, pr = UINT32_MAX;
+                for (uint32_t d = g.dep_start[u]; d < g.dep_start[u + 1]; d++)
+                    if (cp_cmds[g.deps[d]] > m) { m = cp_cmds[g.deps[d]]; mu = cp_units[g.deps[d]]; pr = g.deps[d]; }
+                cp_cmds[u] = m + g.unit_cnt[u]; cp_units[u] = mu + 1; pred[u] = pr;
+                if (cp_cmds[u] > cp_cmds[best]) best = u;
+                tot += g.unit_cnt[u];
+                int b = 0; while ((1u << (b + 1)) <= g.unit_cnt[u] && b < 7) b++;
+                hist[b]++;
+            }
+            fprintf(stderr, "plan frame %zu: units %zu cmds-in-units %zu mc-items %zu | critical path %u cmds over %u units | unit size hist(log2):",
+                    frames, nu, tot, g.mc_items.size(), nu ? cp_cmds[best] : 0, nu ? cp_units[best] : 0);
+            for (int b = 0; b < 8; b++) fprintf(stderr, " %zu", hist[b]);
+            fprintf(stderr, "\n");
+            if (atoi(getenv("EAV1_EMU_PLAN")) > 1 && nu) {
+                for (uint32_t u = (uint32_t)best; u != UINT32_MAX; u = pred[u]) {
+                    const Eav1Cmd &k = cmds[g.unit_cmd[u]];
+                    fprintf(stderr, "   unit %u: %u cmds, first op %d plane %d %dx%d at (%d,%d)\n", u, g.unit_cnt[u], k.op, k.plane, k.w, k.h, k.x, k.y);
+                }
+            }
         }
         return 0;
     }

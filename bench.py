@@ -307,7 +307,7 @@ def run_ours(args, man, obu):
         barrier()
         clk = clocks.stop()
         cnt1 = (C.c_longlong * 4)(); E.eav1cu_counters(eng, cnt1)
-        ms = (C.c_double * 6)(); ln = (C.c_longlong * 6)(); calls = (C.c_longlong * 6)()
+        ms = (C.c_double * 7)(); ln = (C.c_longlong * 7)(); calls = (C.c_longlong * 7)()
         E.eav1cu_stage_times(eng, ms, ln, calls, 1)
         E.eav1cu_set_stage_timing(eng, 0)
         assert last_frame_md5() == man["frames"][-1]["md5"], "timed replay differs from the golden MD5"

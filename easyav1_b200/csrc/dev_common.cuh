@@ -27,6 +27,19 @@ struct alignas(8) uint2 { uint32_t x, y; };
 struct alignas(16) uint4 { uint32_t x, y, z, w; };
 #endif
 
+// Development aid (-DEAV1_PROF=1 builds only): cycle accounting between marks inside one command.
+#if defined(__CUDACC__) && defined(EAV1_PROF) && EAV1_PROF
+__device__ unsigned long long g_prof[64];
+__device__ __forceinline__ void prof_mark(long long &t, int slot, int tid) {
+    if (tid == 0) { const long long n = clock64(); atomicAdd(&g_prof[2 * slot], (unsigned long long)(n - t)); atomicAdd(&g_prof[2 * slot + 1], 1ull); t = n; }
+}
+#define PROF_BEGIN() long long prof_t = clock64()
+#define PROF_MARK(slot) prof_mark(prof_t, slot, tid)
+#else
+#define PROF_BEGIN() ((void)0)
+#define PROF_MARK(slot) ((void)0)
+#endif
+
 namespace eav1 {
 
 struct Plane {

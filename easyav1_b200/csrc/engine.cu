@@ -51,6 +51,7 @@ struct ReconArgs {
     uint32_t n_big_ctas, n_workers;
     uint32_t epoch;
     uint32_t debug;               // count executed units in ctrl[4] (EAV1_DEBUG_CHECK)
+    unsigned long long *hist;     // development aid: per (op, size) cycle histogram behind the trace words
     unsigned long long *trace;    // development aid (eav1cu_staged_trace): 6 words per unit, else null
 };
 
@@ -132,7 +133,13 @@ __device__ __forceinline__ void recon_worker(const FrameCtx &fc, const ReconArgs
                 if (ra.trace) {
                     const long long c1 = clock64();
                     const int op = ws.cmd[c].op, k = op == EAV1_OP_ITX ? 1 : (op == EAV1_OP_IPRED || op == EAV1_OP_CFL) ? 0 : 2;
-                    cyc_op[k] += c1 - c0; n_op[k]++; c0 = c1;
+                    cyc_op[k] += c1 - c0; n_op[k]++;
+                    if (tid == 0 && ra.hist) {   // [op][log2(w*h)] -> cycles, count
+                        const int lg = 31 - __clz((int)ws.cmd[c].w * (int)ws.cmd[c].h);
+                        unsigned long long *hh = ra.hist + ((op & 15) * 16 + (lg & 15)) * 2;
+                        atomicAdd(hh, (unsigned long long)(c1 - c0)); atomicAdd(hh + 1, 1ull);
+                    }
+                    c0 = c1;
                 }
             }
         }
@@ -201,6 +208,37 @@ mc_kernel(FrameCtx fc, const Eav1Cmd *__restrict__ cmds, const uint32_t *__restr
         }
     } else if (c.op == EAV1_OP_WARP) {
         exec_warp<BD>(fc, c, sm, lane, 32);
+    }
+}
+
+// Phase 1b: residuals. The inverse transform of a block depends on nothing but its coefficients, so
+// every two-step ITX command of the frame is an independent item: one warp per block up to 32x32
+// (register path), one CTA per block with a 64-point side. Items arrive sorted by (size, type) so
+// that neighbouring warps run the same code. The residual lands in the arena; phase 2 adds it.
+template <typename BD>
+__global__ void __launch_bounds__(128)
+resid_kernel(FrameCtx fc, const Eav1Cmd *__restrict__ cmds, const uint32_t *__restrict__ items,
+             uint32_t n_small, uint32_t n_small_ctas, uint32_t n_items)
+{
+    __shared__ alignas(16) unsigned char scratch[4 * EAV1_WARP_SCRATCH > sizeof(CtaScratch) ? 4 * EAV1_WARP_SCRATCH : sizeof(CtaScratch)];
+    __shared__ Eav1Cmd cmd[4];
+    if (blockIdx.x < n_small_ctas) {
+        const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+        const uint32_t it = blockIdx.x * 4 + w;
+        if (it >= n_small) return;
+        const uint32_t ci = items[it];
+        if (lane < (int)(sizeof(Eav1Cmd) / 4))
+            reinterpret_cast<uint32_t *>(&cmd[w])[lane] = reinterpret_cast<const uint32_t *>(&cmds[ci])[lane];
+        __syncwarp();
+        exec_itx_residual<BD>(fc, cmd[w], *reinterpret_cast<CtaScratch *>(scratch + w * EAV1_WARP_SCRATCH), lane, 32);
+    } else {
+        const uint32_t it = n_small + (blockIdx.x - n_small_ctas);
+        if (it >= n_items) return;
+        const uint32_t ci = items[it];
+        if (threadIdx.x < sizeof(Eav1Cmd) / 4)
+            reinterpret_cast<uint32_t *>(&cmd[0])[threadIdx.x] = reinterpret_cast<const uint32_t *>(&cmds[ci])[threadIdx.x];
+        __syncthreads();
+        exec_itx_residual<BD>(fc, cmd[0], *reinterpret_cast<CtaScratch *>(scratch), threadIdx.x, 128);
     }
 }
 
@@ -279,7 +317,9 @@ struct DevBuf {
 struct FramePlan {
     Eav1FrameDesc fd;
     const Eav1Cmd *d_cmds = nullptr;
-    const uint32_t *d_deps = nullptr, *d_items = nullptr;
+    const uint32_t *d_deps = nullptr, *d_items = nullptr, *d_ritems = nullptr;
+    uint32_t n_ritems = 0, n_ritems_small = 0;   // two-step transform blocks (phase 1b)
+    long long resid_px = 0;
     const ChainRec *d_recs = nullptr;
     uint32_t n_items = 0;
     long long mc_px = 0, unit_px = 0;
@@ -298,7 +338,7 @@ struct FramePlan {
 // Per-frame upload buffers exist twice: while the kernels of frame k still read slot k&1, the
 // host already fills the other slot for frame k+1 (the `done` event guards reuse two frames later).
 struct Slot {
-    DevBuf cmds, payload, lfrec, lflvl, lrrec, lfmask, deps, recs, items;
+    DevBuf cmds, payload, lfrec, lflvl, lrrec, lfmask, deps, recs, items, ritems;
     cudaEvent_t done = nullptr;
     bool used = false;
 };
@@ -337,7 +377,8 @@ struct Eav1cuCtx {
     unsigned long long *d_sums = nullptr;   // [frame & 63][2]: device checksums of payload / cmds
     unsigned long long h_sums[64][2] = {};  // host checksums of the same uploads
     long long sum_frame[64] = {};
-    std::vector<uint32_t> est_tmp, order_tmp, bucket_tmp;
+    std::vector<uint32_t> est_tmp, order_tmp, bucket_tmp, ritem_tmp;
+    std::vector<Eav1Cmd> cmd_tmp;
     unsigned long long *d_trace = nullptr;   // set only inside eav1cu_staged_trace
     int warp_mode = 0;   // 0: every chain on a CTA, 1: independent small chains on warps, 2: all small chains on warps
     int err = 0;
@@ -473,7 +514,9 @@ int eav1cu_ctx_create(Eav1cuCtx **out, int device)
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per8, recon_frame_kernel<BD8>, 128, 0);
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per16, recon_frame_kernel<BD16>, 128, 0);
-        ctx->recon_grid = sms * std::max(1, std::min(per8, per16));
+        int per = std::max(1, std::min(per8, per16));
+        if (const char *e = getenv("EAV1_RECON_CTAS_PER_SM")) per = std::max(1, std::min(per, atoi(e)));
+        ctx->recon_grid = sms * per;
     }
     if (const char *e = getenv("EAV1_WARP_MODE")) ctx->warp_mode = atoi(e);
     if (const char *e = getenv("EAV1_DEBUG_CHECK")) ctx->debug_check = atoi(e) ? atoi(e) : 1;
@@ -767,6 +810,43 @@ static int plan_build(Eav1cuCtx *ctx, FramePlan &pl, bool staged, const Eav1Fram
         ctx->sched.reset(pw, ph);
         ctx->sched.build_units(cmds, n_cmds, ctx->units);
         const UnitGraph &g = ctx->units;
+        // Two-step transform blocks: give each a residual block behind the arena and list it for
+        // phase 1b, sorted by (transform size, type). The engine works on its own copy of the list.
+        {
+            std::vector<Eav1Cmd> &cc = ctx->cmd_tmp;
+            cc.assign(cmds, cmds + n_cmds);
+            std::vector<uint32_t> &ri = ctx->ritem_tmp, &bk = ctx->bucket_tmp;
+            size_t off = (arena_bytes + 31) & ~(size_t)31;
+            bk.assign(2 * 19 * 17 + 1, 0);
+            auto key = [](const Eav1Cmd &c) { return ((c.w > 32 || c.h > 32) ? 19 * 17 : 0) + c.u.itx.tx * 17 + c.u.itx.txtp; };
+            uint32_t n_two = 0;
+            pl.resid_px = 0;
+            for (size_t i = 0; i < n_cmds; i++) {
+                Eav1Cmd &c = cc[i];
+                if (c.op != EAV1_OP_ITX || (c.flags & EAV1_F_DST_ARENA) || c.u.itx.tx >= 19 || c.u.itx.txtp >= 16 ||
+                    c.u.itx.eob < (c.u.itx.txtp == 0))
+                    continue;
+                c.flags |= EAV1_F_RESID;
+                c.dst_off = (uint32_t)off;
+                off += (size_t)c.w * c.h * 2;
+                pl.resid_px += (long long)c.w * c.h;
+                bk[key(c) + 1]++;
+                n_two++;
+            }
+            for (size_t b = 1; b < bk.size(); b++) bk[b] += bk[b - 1];
+            pl.n_ritems_small = bk[19 * 17];
+            ri.resize(n_two);
+            for (size_t i = 0; i < n_cmds; i++)
+                if (cc[i].flags & EAV1_F_RESID && cc[i].op == EAV1_OP_ITX) ri[bk[key(cc[i])]++] = (uint32_t)i;
+            pl.n_ritems = n_two;
+            arena_bytes = off;
+            pl.arena_bytes = arena_bytes;
+            cmds = cc.data();
+            if (n_two) {
+                if ((r = up.put(ctx->S().ritems, ri.data(), ri.size() * 4, &d))) return r;
+                pl.d_ritems = reinterpret_cast<const uint32_t *>(d);
+            }
+        }
         if ((r = up.put(ctx->S().cmds, cmds, n_cmds * sizeof(Eav1Cmd), &d))) return r;
         pl.d_cmds = reinterpret_cast<const Eav1Cmd *>(d);
         // never hand the kernel a null list, even when nothing has a producer
@@ -910,6 +990,14 @@ static int plan_launch(Eav1cuCtx *ctx, FramePlan &pl)
         else     mc_kernel<BD8><<<grid, 128, 0, st>>>(fc, pl.d_cmds, pl.d_items, pl.n_items);
         ctx->n_launches++;
     }
+    if (pl.n_ritems) {
+        StageTimer tm(ctx, 6);
+        const unsigned small_ctas = (pl.n_ritems_small + 3) / 4;
+        const unsigned grid = small_ctas + (pl.n_ritems - pl.n_ritems_small);
+        if (hbd) resid_kernel<BD16><<<grid, 128, 0, st>>>(fc, pl.d_cmds, pl.d_ritems, pl.n_ritems_small, small_ctas, pl.n_ritems);
+        else     resid_kernel<BD8><<<grid, 128, 0, st>>>(fc, pl.d_cmds, pl.d_ritems, pl.n_ritems_small, small_ctas, pl.n_ritems);
+        ctx->n_launches++;
+    }
     if (pl.n_chains) {
         StageTimer tm(ctx, 0);
         if (pl.n_chains > ctx->done_cap) return fail(ctx, EAV1CU_ERR_INVAL, "done-flag array smaller than the staged frame");
@@ -928,6 +1016,7 @@ static int plan_launch(Eav1cuCtx *ctx, FramePlan &pl)
         ra.n_big_ctas = big_ctas; ra.n_workers = big_ctas + 4 * small_ctas;
         ra.debug = ctx->debug_check == 1;
         ra.trace = ctx->d_trace;
+        ra.hist = ctx->d_trace ? ctx->d_trace + (size_t)pl.n_chains * EAV1_TRACE_WORDS : nullptr;
         if (ctx->debug_check == 2) {
             // verify what the kernels will read: checksum payload and commands on the device, in stream order
             const int slot = (int)(ctx->n_frames & 63);
@@ -1172,18 +1261,33 @@ int eav1cu_staged_trace(Eav1cuCtx *ctx, int idx, unsigned long long *out, size_t
     CK(cudaSetDevice(ctx->device));
     FramePlan &pl = *ctx->staged[idx];
     const size_t n = pl.n_chains;
-    if (n > cap_units) return EAV1CU_ERR_INVAL;
+    if (n + 43 > cap_units) return EAV1CU_ERR_INVAL;   /* 12 words per unit + a 512-word (op, size) histogram */
     if (!n) return 0;
-    CK(cudaMalloc(&ctx->d_trace, n * EAV1_TRACE_WORDS * sizeof(unsigned long long)));
-    CK(cudaMemsetAsync(ctx->d_trace, 0, n * EAV1_TRACE_WORDS * sizeof(unsigned long long), ctx->stream));
+    const size_t words = n * EAV1_TRACE_WORDS + 512;
+    CK(cudaMalloc(&ctx->d_trace, words * sizeof(unsigned long long)));
+    CK(cudaMemsetAsync(ctx->d_trace, 0, words * sizeof(unsigned long long), ctx->stream));
     int r = plan_launch(ctx, pl);
     cudaError_t e = cudaStreamSynchronize(ctx->stream);
-    if (!r && e == cudaSuccess) e = cudaMemcpy(out, ctx->d_trace, n * EAV1_TRACE_WORDS * sizeof(unsigned long long), cudaMemcpyDeviceToHost);
+    if (!r && e == cudaSuccess) e = cudaMemcpy(out, ctx->d_trace, words * sizeof(unsigned long long), cudaMemcpyDeviceToHost);
     cudaFree(ctx->d_trace);
     ctx->d_trace = nullptr;
     if (r) return r;
     if (e != cudaSuccess) return fail(ctx, EAV1CU_ERR_CUDA, "staged trace", e);
     return (int)n;
+}
+
+/* Development aid: cycle counters of -DEAV1_PROF=1 builds (zeros otherwise); reading resets them. */
+int eav1cu_prof_read(unsigned long long out[64])
+{
+#if defined(EAV1_PROF) && EAV1_PROF
+    static const unsigned long long zero[64] = { 0 };
+    if (cudaMemcpyFromSymbol(out, g_prof, sizeof(zero)) != cudaSuccess) return EAV1CU_ERR_CUDA;
+    if (cudaMemcpyToSymbol(g_prof, zero, sizeof(zero)) != cudaSuccess) return EAV1CU_ERR_CUDA;
+    return 1;
+#else
+    memset(out, 0, 64 * sizeof(out[0]));
+    return 0;
+#endif
 }
 
 int eav1cu_staged_info(Eav1cuCtx *ctx, int idx, Eav1StagedInfo *out)
@@ -1196,6 +1300,7 @@ int eav1cu_staged_info(Eav1cuCtx *ctx, int idx, Eav1StagedInfo *out)
     out->n_chains = (int)p.n_chains;
     out->n_big = (int)p.n_big; out->n_small = (int)p.n_small;
     out->n_mc_items = (int)p.n_items; out->mc_px = p.mc_px; out->unit_px = p.unit_px;
+    out->n_resid_items = (int)p.n_ritems; out->resid_px = p.resid_px;
     out->launches = (int)p.launches;
     out->n_lf = (int)(p.n_lf0 + p.n_lf1); out->n_lr = (int)p.n_lr;
     out->cdef = p.fd.cdef_enable;

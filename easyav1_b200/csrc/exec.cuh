@@ -66,6 +66,14 @@ EAV1_DEV void exec_warp(const FrameCtx &fc, const Eav1Cmd &c, CtaScratch &sm, in
                       dst8, dst16, dstride, fc.bitdepth_max, sm.mc_mid, tid, nthr);
 }
 
+// Phase 1 of a two-step transform block: residual of ITX command c into the arena (c.dst_off).
+template <typename BD>
+EAV1_DEV void exec_itx_residual(const FrameCtx &fc, const Eav1Cmd &c, CtaScratch &sm, int tid, int nthr)
+{
+    itx_add<BD>(nullptr, 0, (const typename BD::coef *)(fc.payload + c.u.itx.cf_off), c.u.itx.eob, c.u.itx.tx,
+                c.u.itx.txtp, fc.bitdepth_max, sm.itx, tid, nthr, reinterpret_cast<int16_t *>(fc.arena + c.dst_off));
+}
+
 // Not inlined: the CTA-sized and the warp-sized worker of recon_frame_kernel share one copy of
 // every routine (the kernel's instruction footprint is what bounds short commands).
 #ifndef EAV1_DEDUPE
@@ -81,6 +89,7 @@ EAV1_EXEC_LINK void exec_cmd(const FrameCtx &fc, const Eav1Cmd &c, CtaScratch &s
 {
     typedef typename BD::pixel pixel;
     const int bdmax = fc.bitdepth_max;
+    PROF_BEGIN();
     // destination
     pixel *dst8 = nullptr;
     int16_t *dst16 = nullptr;
@@ -94,6 +103,7 @@ EAV1_EXEC_LINK void exec_cmd(const FrameCtx &fc, const Eav1Cmd &c, CtaScratch &s
         dst8 = px_at<pixel>(pl, c.x, c.y);
         dstride = pl.stride / (int)sizeof(pixel);
     }
+    PROF_MARK(0);
     switch (c.op) {
     case EAV1_OP_MC:
         exec_mc_rect<BD>(fc, c, 0, 0, c.w, c.h, sm, tid, nthr);
@@ -102,8 +112,10 @@ EAV1_EXEC_LINK void exec_cmd(const FrameCtx &fc, const Eav1Cmd &c, CtaScratch &s
         exec_warp<BD>(fc, c, sm, tid, nthr);
         break;
     case EAV1_OP_AVG:
+        PROF_MARK(6);
         comp_avg<BD>(dst8, dstride, (const int16_t *)(fc.arena + c.u.comp.t1), (const int16_t *)(fc.arena + c.u.comp.t2),
                      c.w, c.h, bdmax, tid, nthr);
+        PROF_MARK(7);
         break;
     case EAV1_OP_W_AVG:
         comp_w_avg<BD>(dst8, dstride, (const int16_t *)(fc.arena + c.u.comp.t1), (const int16_t *)(fc.arena + c.u.comp.t2),
@@ -131,9 +143,12 @@ EAV1_EXEC_LINK void exec_cmd(const FrameCtx &fc, const Eav1Cmd &c, CtaScratch &s
         blend_h<pixel>(fc.tab, dst8, dstride, (const pixel *)(fc.arena + c.u.blend.tmp_off), c.w, c.h, tid, nthr);
         break;
     case EAV1_OP_IPRED:
+        PROF_MARK(1);
         build_edge<pixel>(fc.cur[c.plane], c, bdmax, sm.ip.edge, tid, nthr);
+        PROF_MARK(2);
         ipred_block<pixel>(fc.tab, dst8, dstride, sm.ip.edge, sm.ip.edge2, c.u.ipred.mode, c.w, c.h,
                            c.u.ipred.angle, c.u.ipred.max_w, c.u.ipred.max_h, bdmax, tid, nthr);
+        PROF_MARK(3);
         break;
     case EAV1_OP_CFL:
         cfl_ac_block<pixel>(fc.cur[0], c.u.ipred.lx, c.u.ipred.ly, c.u.ipred.w_pad, c.u.ipred.h_pad, c.w, c.h,
@@ -147,8 +162,13 @@ EAV1_EXEC_LINK void exec_cmd(const FrameCtx &fc, const Eav1Cmd &c, CtaScratch &s
                               fc.payload + c.u.pal.idx_off, c.w, c.h, tid, nthr);
         break;
     case EAV1_OP_ITX:
-        itx_add<BD>(dst8, dstride, (const typename BD::coef *)(fc.payload + c.u.itx.cf_off), c.u.itx.eob,
-                    c.u.itx.tx, c.u.itx.txtp, bdmax, sm.itx, tid, nthr);
+        PROF_MARK(4);
+        if (c.flags & EAV1_F_RESID)
+            res_add<BD>(dst8, dstride, (const int16_t *)(fc.arena + c.dst_off), c.w, c.h, bdmax, tid, nthr);
+        else
+            itx_add<BD>(dst8, dstride, (const typename BD::coef *)(fc.payload + c.u.itx.cf_off), c.u.itx.eob,
+                        c.u.itx.tx, c.u.itx.txtp, bdmax, sm.itx, tid, nthr);
+        PROF_MARK(5);
         break;
     default:
         break;

@@ -546,7 +546,7 @@ EAV1_DEV void itx_row_reg(const typename BD::coef *coeff, int sh, int y, int typ
 // second pass of column x, added into dst
 template <typename BD, int N>
 EAV1_DEV void itx_col_reg(const int32_t *s, int P, int x, int type, int col_min, int col_max,
-                          typename BD::pixel *dst, int dst_stride, int bitdepth_max)
+                          typename BD::pixel *dst, int dst_stride, int bitdepth_max, int16_t *res, int res_stride)
 {
     typedef typename BD::wide W;
     typedef typename BD::pixel pixel;
@@ -554,6 +554,12 @@ EAV1_DEV void itx_col_reg(const int32_t *s, int P, int x, int type, int col_min,
 #pragma unroll
     for (int y = 0; y < N; y++) v[y] = s[x * P + y];
     const int flip = type == T1D_FLIPADST;
+    if (res) {   // residual only (phase 1): row-major int16 block, added to the prediction later
+        itx_1d_reg<W, N>(type, v, col_min, col_max);
+#pragma unroll
+        for (int y = 0; y < N; y++) res[(flip ? N - 1 - y : y) * res_stride + x] = (int16_t)((v[y] + 8) >> 4);
+        return;
+    }
     pixel *d = dst + x;
     if (N <= 16) {
         // issue the destination loads before the butterflies so their latency hides behind them
@@ -576,7 +582,7 @@ EAV1_DEV void itx_col_reg(const int32_t *s, int P, int x, int type, int col_min,
 
 template <typename BD>
 EAV1_DEVN void itx_add_reg(typename BD::pixel *dst, int dst_stride, const typename BD::coef *coeff, int w, int h,
-                           int shift, int rt, int ct, int bitdepth_max, int32_t *s, int tid, int nthr)
+                           int shift, int rt, int ct, int bitdepth_max, int32_t *s, int tid, int nthr, int16_t *res)
 {
     const int is_rect2 = (w * 2 == h) || (h * 2 == w);
     const int P = h + 1;
@@ -587,6 +593,7 @@ EAV1_DEVN void itx_add_reg(typename BD::pixel *dst, int dst_stride, const typena
         col_min = (int)((unsigned)~bitdepth_max << 5);
     }
     const int row_max = ~row_min, col_max = ~col_min;
+    PROF_BEGIN();
     for (int y = tid; y < h; y += nthr) {
         switch (w) {
         case 4:  itx_row_reg<BD, 4>(coeff, h, y, rt, is_rect2, shift, row_min, row_max, col_min, col_max, s, P); break;
@@ -595,22 +602,26 @@ EAV1_DEVN void itx_add_reg(typename BD::pixel *dst, int dst_stride, const typena
         default: itx_row_reg<BD, 32>(coeff, h, y, rt, is_rect2, shift, row_min, row_max, col_min, col_max, s, P); break;
         }
     }
+    PROF_MARK(10);
     CTA_SYNC();
+    PROF_MARK(11);
     for (int x = tid; x < w; x += nthr) {
         switch (h) {
-        case 4:  itx_col_reg<BD, 4>(s, P, x, ct, col_min, col_max, dst, dst_stride, bitdepth_max); break;
-        case 8:  itx_col_reg<BD, 8>(s, P, x, ct, col_min, col_max, dst, dst_stride, bitdepth_max); break;
-        case 16: itx_col_reg<BD, 16>(s, P, x, ct, col_min, col_max, dst, dst_stride, bitdepth_max); break;
-        default: itx_col_reg<BD, 32>(s, P, x, ct, col_min, col_max, dst, dst_stride, bitdepth_max); break;
+        case 4:  itx_col_reg<BD, 4>(s, P, x, ct, col_min, col_max, dst, dst_stride, bitdepth_max, res, w); break;
+        case 8:  itx_col_reg<BD, 8>(s, P, x, ct, col_min, col_max, dst, dst_stride, bitdepth_max, res, w); break;
+        case 16: itx_col_reg<BD, 16>(s, P, x, ct, col_min, col_max, dst, dst_stride, bitdepth_max, res, w); break;
+        default: itx_col_reg<BD, 32>(s, P, x, ct, col_min, col_max, dst, dst_stride, bitdepth_max, res, w); break;
         }
     }
+    PROF_MARK(12);
     CTA_SYNC();
+    PROF_MARK(13);
 }
 
 // dst += inverse_transform(coef). `s` is the CTA's shared tile (>= 64*65 int32).
 template <typename BD>
 EAV1_DEVN void itx_add(typename BD::pixel *dst, int dst_stride /*pixels*/, const typename BD::coef *coeff,
-                      int eob, int tx, int txtp, int bitdepth_max, int32_t *s, int tid, int nthr)
+                      int eob, int tx, int txtp, int bitdepth_max, int32_t *s, int tid, int nthr, int16_t *res = nullptr)
 {
     typedef typename BD::wide W;
     const TxDim d = tx_dim(tx);
@@ -649,7 +660,7 @@ EAV1_DEVN void itx_add(typename BD::pixel *dst, int dst_stride /*pixels*/, const
 #define EAV1_ITX_REG 1
 #endif
     if (EAV1_ITX_REG && w <= 32 && h <= 32) {
-        itx_add_reg<BD>(dst, dst_stride, coeff, w, h, d.shift, rt, ct, bitdepth_max, s, tid, nthr);
+        itx_add_reg<BD>(dst, dst_stride, coeff, w, h, d.shift, rt, ct, bitdepth_max, s, tid, nthr, res);
         return;
     }
     const int sh = imin(h, 32), sw = imin(w, 32);
@@ -683,11 +694,52 @@ EAV1_DEVN void itx_add(typename BD::pixel *dst, int dst_stride /*pixels*/, const
     for (int x = tid; x < w; x += nthr)
         itx_1d<W>(ct, h, &s[x * P], 1, col_min, col_max);
     CTA_SYNC();
+    if (res) {
+        for (int i = tid; i < w * h; i += nthr) {
+            const int y = i / w, x = i - y * w;
+            res[i] = (int16_t)((s[x * P + y] + 8) >> 4);
+        }
+        CTA_SYNC();
+        return;
+    }
     for (int i = tid; i < w * h; i += nthr) {
         const int y = i / w, x = i - y * w;
         dst[y * dst_stride + x] = (typename BD::pixel)iclip(dst[y * dst_stride + x] + ((s[x * P + y] + 8) >> 4), 0, bitdepth_max);
     }
     CTA_SYNC();
+}
+
+// Is this transform block reconstructed in two steps (residual in phase 1, add in phase 2)?
+// DC-only blocks and the lossless WHT stay single-step: their residual is a constant / trivial.
+EAV1_DEV bool itx_two_step(int eob, int txtp) { return txtp != 16 && !(eob < (txtp == 0)); }
+
+// dst += res (row-major int16 residual of a w x h transform block, w and h powers of two)
+template <typename BD>
+EAV1_DEV void res_add(typename BD::pixel *dst, int dst_stride, const int16_t *res, int w, int h,
+                      int bitdepth_max, int tid, int nthr)
+{
+    typedef typename BD::pixel pixel;
+    const int lw = ulog2((unsigned)w);
+    if (w >= 4 && !BD::hbd) {
+        // four samples per thread: one 64-bit residual load, one 32-bit pixel load/store
+        const int n4 = (w * h) >> 2, lw4 = lw - 2;
+        for (int i = tid; i < n4; i += nthr) {
+            const int y = i >> lw4, x = (i & ((1 << lw4) - 1)) << 2;
+            const uint2 r = *reinterpret_cast<const uint2 *>(res + (i << 2));
+            uint32_t *q = reinterpret_cast<uint32_t *>(dst + y * dst_stride + x);
+            const uint32_t p = *q;
+            const int r0 = (int16_t)(r.x & 0xffff), r1 = (int16_t)(r.x >> 16), r2 = (int16_t)(r.y & 0xffff), r3 = (int16_t)(r.y >> 16);
+            const uint32_t o = (uint32_t)iclip((int)(p & 0xff) + r0, 0, 255) | (uint32_t)iclip((int)((p >> 8) & 0xff) + r1, 0, 255) << 8 |
+                               (uint32_t)iclip((int)((p >> 16) & 0xff) + r2, 0, 255) << 16 | (uint32_t)iclip((int)(p >> 24) + r3, 0, 255) << 24;
+            *q = o;
+        }
+    } else {
+        for (int i = tid; i < w * h; i += nthr) {
+            const int y = i >> lw, x = i & (w - 1);
+            pixel *q = dst + y * dst_stride + x;
+            *q = (pixel)iclip(*q + res[i], 0, bitdepth_max);
+        }
+    }
 }
 
 } // namespace eav1

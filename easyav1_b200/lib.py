@@ -58,9 +58,9 @@ def load_host(path=None):
 class StagedInfo(C.Structure):
     _fields_ = [("cur", C.c_int), ("w", C.c_int), ("h", C.c_int), ("bpc", C.c_int), ("layout", C.c_int),
                 ("n_levels", C.c_int), ("n_chains", C.c_int), ("launches", C.c_int),
-                ("n_lf", C.c_int), ("n_lr", C.c_int), ("cdef", C.c_int), ("inter", C.c_int), ("n_big", C.c_int), ("n_small", C.c_int), ("n_mc_items", C.c_int), ("pad", C.c_int),
+                ("n_lf", C.c_int), ("n_lr", C.c_int), ("cdef", C.c_int), ("inter", C.c_int), ("n_big", C.c_int), ("n_small", C.c_int), ("n_mc_items", C.c_int), ("n_resid_items", C.c_int),
                 ("n_cmds", C.c_longlong), ("payload_bytes", C.c_longlong),
-                ("mc_px", C.c_longlong), ("unit_px", C.c_longlong)]
+                ("mc_px", C.c_longlong), ("unit_px", C.c_longlong), ("resid_px", C.c_longlong)]
 
 
 class StreamFrame(C.Structure):

@@ -83,6 +83,8 @@ enum Eav1Op {
 #define EAV1_F_PREP       2  /* MC/WARP: int16 "prep" output instead of pixels */
 #define EAV1_F_BLOCK_HEAD 4  /* first command of a coding block (= scheduling unit) */
 #define EAV1_F_MASK_ARENA 8  /* MASK/BLEND: mask lives in the arena (w_mask output), else in the mask table blob */
+#define EAV1_F_RESID      16 /* ITX, set by the engine's planner only: the residual was computed in phase 1 and lies
+                                at arena offset dst_off (row-major int16, stride w); phase 2 just adds it */
 
 /* mask_off for table masks indexes the blob passed to eav1cu_set_masks (wedge + ii masks). */
 
@@ -245,9 +247,10 @@ typedef struct Eav1StagedInfo {
     int n_levels, n_chains, launches;
     int n_lf, n_lr, cdef, inter;
     int n_big, n_small;      /* dataflow units run by a whole CTA / by a single warp */
-    int n_mc_items, pad;     /* phase-1 motion-compensation work items (<= 32x32 each) */
+    int n_mc_items, n_resid_items; /* phase-1 work items: motion compensation (<= 32x32 each) / transform blocks */
     long long n_cmds, payload_bytes;
     long long mc_px, unit_px; /* samples produced by phase 1 / touched by phase-2 units */
+    long long resid_px;       /* samples of the transform blocks whose residual phase 1b computes */
 } Eav1StagedInfo;
 /* sizeof() of the ABI structs as compiled (0 Eav1Cmd, 1 Eav1LfRec, 2 Eav1LrRec, 3 Eav1FrameDesc,
  * 4 Eav1StagedInfo, 5 Eav1Tables), so bindings can verify their mirrors. */
@@ -267,9 +270,9 @@ int  eav1cu_counters(Eav1cuCtx *ctx, long long out[4]);
 int  eav1cu_set_capture(Eav1cuCtx *ctx, int on);
 /* Per-stage device time (CUDA events on the context's stream around each stage of every
  * frame): index 0 dataflow reconstruction (intra, residual, compound/blend), 1 deblock, 2 CDEF,
- * 3 loop restoration, 4 motion compensation, 5 film grain. Each array has EAV1CU_N_STAGES entries: accumulated
+ * 3 loop restoration, 4 motion compensation, 5 film grain, 6 inverse-transform residuals. Each array has EAV1CU_N_STAGES entries: accumulated
  * milliseconds, kernel launches and stage invocations since the last reset. */
-#define EAV1CU_N_STAGES 6
+#define EAV1CU_N_STAGES 7
 int  eav1cu_set_stage_timing(Eav1cuCtx *ctx, int on);
 int  eav1cu_stage_times(Eav1cuCtx *ctx, double *ms, long long *launches, long long *calls, int reset);
 int  eav1cu_staged_count(Eav1cuCtx *ctx);
@@ -278,6 +281,8 @@ int  eav1cu_staged_info(Eav1cuCtx *ctx, int idx, Eav1StagedInfo *out);
 /* Development aid: replay staged frame idx once with per-unit device timestamps. out gets 6 words
  * per dataflow unit (index = unit id): ticket drawn, producers ready, done (ns), id of the producer
  * that finished last (~0: none), first command << 32 | count, ticket << 32 | CTA << 8 | warp. */
+/* Development aid: cycle counters of -DEAV1_PROF=1 builds (all zero otherwise); reading resets them. */
+int  eav1cu_prof_read(unsigned long long out[64]);
 int  eav1cu_staged_trace(Eav1cuCtx *ctx, int idx, unsigned long long *out, size_t cap_units);
 /* Run on a caller-owned cudaStream_t (passed as void*) so the caller can record its own
  * events around the launches; the context never destroys a stream it did not create. */

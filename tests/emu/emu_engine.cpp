@@ -193,10 +193,31 @@ int eav1cu_frame_submit(Eav1cuCtx *c, const Eav1FrameDesc *fd, const Eav1Cmd *cm
     fc.ss_hor = fd->layout != 3; fc.ss_ver = fd->layout == 1;
     fc.tab = &c->tab;
     fc.masks = c->masks.data();
+    // same two-step split as the engine's planner: residual blocks behind the arena (phase 1b),
+    // the ITX command itself then only adds (EAV1_F_RESID)
+    static std::vector<Eav1Cmd> patched;
+    patched.assign(cmds, cmds + n);
+    size_t off = (arena_bytes + 31) & ~(size_t)31;
+    for (size_t i = 0; i < n; i++) {
+        Eav1Cmd &k = patched[i];
+        if (k.op != EAV1_OP_ITX || (k.flags & EAV1_F_DST_ARENA) || k.u.itx.tx >= 19 || k.u.itx.txtp >= 16 ||
+            k.u.itx.eob < (k.u.itx.txtp == 0))
+            continue;
+        k.flags |= EAV1_F_RESID;
+        k.dst_off = (uint32_t)off;
+        off += (size_t)k.w * k.h * 2;
+    }
+    arena_bytes = off;
+    cmds = patched.data();
     if (c->arena.size() < arena_bytes + 16) c->arena.resize(arena_bytes + 16);
     fc.arena = c->arena.data();
     fc.payload = (const uint8_t *)payload;
     static CtaScratch sm;
+    for (size_t i = 0; i < n; i++)
+        if (cmds[i].op == EAV1_OP_ITX && (cmds[i].flags & EAV1_F_RESID)) {
+            if (fd->bpc > 8) exec_itx_residual<BD16>(fc, cmds[i], sm, 0, 1);
+            else exec_itx_residual<BD8>(fc, cmds[i], sm, 0, 1);
+        }
     for (size_t i = 0; i < n; i++) {
         if (fd->bpc > 8) exec_cmd<BD16>(fc, cmds[i], sm, 0, 1);
         else exec_cmd<BD8>(fc, cmds[i], sm, 0, 1);

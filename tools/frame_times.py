@@ -22,7 +22,7 @@ while i < nmax and host.eav1_stream_next(h, C.byref(info), buf, cap, C.byref(use
 E.eav1cu_set_capture(eng, 0)
 n = E.eav1cu_staged_count(eng)
 E.eav1cu_set_stage_timing(eng, 1)
-ms = (C.c_double * 6)(); ln = (C.c_longlong * 6)(); calls = (C.c_longlong * 6)()
+ms = (C.c_double * 7)(); ln = (C.c_longlong * 7)(); calls = (C.c_longlong * 7)()
 for rep in range(2):
     for k in range(n):
         E.eav1cu_stage_times(eng, None, None, None, 1)
@@ -31,7 +31,7 @@ for rep in range(2):
         E.eav1cu_stage_times(eng, ms, ln, calls, 1)
         si = StagedInfo(); E.eav1cu_staged_info(eng, k, C.byref(si))
         if rep == 1:
-            print("frame %3d inter %d cmds %6d chains %5d (cta %5d warp %5d) levels %4d | mc %7.1f recon %8.1f us deblock %6.1f cdef %6.1f lr %6.1f"
+            print("frame %3d inter %d cmds %6d chains %5d (cta %5d warp %5d) levels %4d | mc %7.1f resid %6.1f recon %8.1f us deblock %6.1f cdef %6.1f lr %6.1f"
                   % (k, si.inter, si.n_cmds, si.n_chains, si.n_big, si.n_small, si.n_levels,
-                     1e3 * ms[4] / 3, 1e3 * ms[0] / 3, 1e3 * ms[1] / 3, 1e3 * ms[2] / 3, 1e3 * ms[3] / 3))
+                     1e3 * ms[4] / 3, 1e3 * ms[6] / 3, 1e3 * ms[0] / 3, 1e3 * ms[1] / 3, 1e3 * ms[2] / 3, 1e3 * ms[3] / 3))
 host.eav1_stream_close(h)

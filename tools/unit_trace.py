@@ -27,10 +27,13 @@ host.eav1rec_drain(host.eav1_stream_ctx(h))
 si = StagedInfo(); E.eav1cu_staged_info(eng, K, C.byref(si))
 n = si.n_chains
 W = 12
-out = (C.c_ulonglong * (W * n))()
+out = (C.c_ulonglong * (W * (n + 43)))()
 E.eav1cu_staged_trace.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_ulonglong), C.c_size_t]
+prof = (C.c_ulonglong * 64)()
 for _ in range(3):
-    r = E.eav1cu_staged_trace(eng, K, out, n)
+    E.eav1cu_prof_read(prof)
+    r = E.eav1cu_staged_trace(eng, K, out, n + 43)
+have_prof = E.eav1cu_prof_read(prof)
 assert r == n, r
 U = [tuple(out[W * u + j] for j in range(6)) for u in range(n)]
 X = [tuple(out[W * u + j] for j in range(6, 12)) for u in range(n)]
@@ -74,4 +77,21 @@ st = sum(x[0] for x in X); ip = sum(x[1] for x in X); it = sum(x[2] for x in X);
 nip = sum(x[4] >> 32 for x in X); nit = sum(x[4] & 0xffffffff for x in X); no = sum(x[5] for x in X)
 print("cycles: staging %.0f per cmd | ipred %.0f per cmd (%d) | itx %.0f per cmd (%d) | other %.0f per cmd (%d)" %
       (st / max(tot_cmds, 1), ip / max(nip, 1), nip, it / max(nit, 1), nit, ot / max(no, 1), no))
+names = ["nop", "mc", "warp", "avg", "wavg", "mask", "wmask", "blend", "blendv", "blendh", "ipred", "cfl", "pal", "itx"]
+print("cycles per command by op and log2(w*h):")
+for op in range(14):
+    cells = []
+    for lg in range(16):
+        cyc, cnt = out[W * n + (op * 16 + lg) * 2], out[W * n + (op * 16 + lg) * 2 + 1]
+        if cnt:
+            cells.append("2^%d: %d x %.0f" % (lg, cnt, cyc / cnt))
+    if cells:
+        print("  %-6s %s" % (names[op], " | ".join(cells)))
+if have_prof:
+    lab = {0: "exec_cmd entry->switch", 1: "switch->ipred case", 2: "build_edge", 3: "ipred_block", 4: "switch->itx case",
+           5: "itx_add total", 6: "switch->avg case", 7: "comp_avg", 10: "itx reg: row pass", 11: "itx reg: barrier",
+           12: "itx reg: col pass", 13: "itx reg: barrier"}
+    for k in sorted(lab):
+        if prof[2 * k + 1]:
+            print("  prof %-24s %8d x %6.0f cycles" % (lab[k], prof[2 * k + 1], prof[2 * k] / prof[2 * k + 1]))
 host.eav1_stream_close(h)

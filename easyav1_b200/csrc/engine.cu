@@ -75,7 +75,7 @@ __device__ __forceinline__ void st_release(uint32_t *p, uint32_t v)
     asm volatile("st.release.gpu.global.u32 [%0], %1;" :: "l"(p), "r"(v) : "memory");
 }
 
-#define EAV1_CMD_STAGE 4   // commands fetched into shared memory per round trip
+#define EAV1_CMD_STAGE 8   // commands fetched into shared memory per round trip
 
 struct WorkerSmem {
     Eav1Cmd cmd[EAV1_CMD_STAGE];
@@ -127,15 +127,16 @@ __device__ __forceinline__ void recon_worker(const FrameCtx &fc, const ReconArgs
             for (uint32_t i = tid; i < n * (sizeof(Eav1Cmd) / 4); i += nthr) dst[i] = src[i];
             CTA_SYNC();
             if (ra.trace) { const long long c1 = clock64(); cyc_stage += c1 - c0; c0 = c1; }
-            for (uint32_t c = 0; c < n; c++) {
-                exec_cmd<BD>(fc, ws.cmd[c], sm, tid, nthr);
+            for (uint32_t c = 0; c < n;) {
+                const uint32_t c_this = c;
+                c += exec_cmd<BD>(fc, ws.cmd[c], sm, tid, nthr, c + 1 < n ? &ws.cmd[c + 1] : nullptr);
                 CTA_SYNC();
                 if (ra.trace) {
                     const long long c1 = clock64();
-                    const int op = ws.cmd[c].op, k = op == EAV1_OP_ITX ? 1 : (op == EAV1_OP_IPRED || op == EAV1_OP_CFL) ? 0 : 2;
+                    const int op = ws.cmd[c_this].op, k = op == EAV1_OP_ITX ? 1 : (op == EAV1_OP_IPRED || op == EAV1_OP_CFL) ? 0 : 2;
                     cyc_op[k] += c1 - c0; n_op[k]++;
                     if (tid == 0 && ra.hist) {   // [op][log2(w*h)] -> cycles, count
-                        const int lg = 31 - __clz((int)ws.cmd[c].w * (int)ws.cmd[c].h);
+                        const int lg = 31 - __clz((int)ws.cmd[c_this].w * (int)ws.cmd[c_this].h);
                         unsigned long long *hh = ra.hist + ((op & 15) * 16 + (lg & 15)) * 2;
                         atomicAdd(hh, (unsigned long long)(c1 - c0)); atomicAdd(hh + 1, 1ull);
                     }
@@ -377,7 +378,7 @@ struct Eav1cuCtx {
     unsigned long long *d_sums = nullptr;   // [frame & 63][2]: device checksums of payload / cmds
     unsigned long long h_sums[64][2] = {};  // host checksums of the same uploads
     long long sum_frame[64] = {};
-    std::vector<uint32_t> est_tmp, order_tmp, bucket_tmp, ritem_tmp;
+    std::vector<uint32_t> est_tmp, order_tmp, bucket_tmp, ritem_tmp, tail_tmp, order2_tmp;
     std::vector<Eav1Cmd> cmd_tmp;
     unsigned long long *d_trace = nullptr;   // set only inside eav1cu_staged_trace
     int warp_mode = 0;   // 0: every chain on a CTA, 1: independent small chains on warps, 2: all small chains on warps
@@ -896,10 +897,26 @@ static int plan_build(Eav1cuCtx *ctx, FramePlan &pl, bool staged, const Eav1Fram
                     e = std::max(e, est[g.deps[d]] + g.unit_cnt[g.deps[d]]);
                 est[u] = e; est_max = std::max(est_max, e);
             }
+            // Among units that can start at the same time, the one with the longest chain of
+            // consumers behind it goes first (list-scheduling priority): two stable counting sorts,
+            // by descending tail, then by ascending earliest start.
+            std::vector<uint32_t> &tail = ctx->tail_tmp, &tmp = ctx->order2_tmp;
+            tail.assign(nc, 0); tmp.resize(nc);
+            uint32_t tail_max = 0;
+            for (size_t u = nc; u-- > 0;) {
+                tail[u] += g.unit_cnt[u];
+                tail_max = std::max(tail_max, tail[u]);
+                for (uint32_t d = g.dep_start[u]; d < g.dep_start[u + 1]; d++)
+                    tail[g.deps[d]] = std::max(tail[g.deps[d]], tail[u]);
+            }
+            bucket.assign((size_t)tail_max + 2, 0);
+            for (size_t u = 0; u < nc; u++) bucket[tail_max - tail[u] + 1]++;
+            for (size_t b = 1; b < bucket.size(); b++) bucket[b] += bucket[b - 1];
+            for (size_t u = 0; u < nc; u++) tmp[bucket[tail_max - tail[u]]++] = (uint32_t)u;
             bucket.assign((size_t)est_max + 2, 0);
             for (size_t u = 0; u < nc; u++) bucket[est[u] + 1]++;
             for (size_t b = 1; b < bucket.size(); b++) bucket[b] += bucket[b - 1];
-            for (size_t u = 0; u < nc; u++) order[bucket[est[u]]++] = (uint32_t)u;
+            for (size_t i = 0; i < nc; i++) { const uint32_t u = tmp[i]; order[bucket[est[u]]++] = u; }
             for (int pass = 0; pass < 2; pass++) {
                 size_t pos = pass ? nb : 0;
                 for (size_t oi = 0; oi < nc; oi++) {

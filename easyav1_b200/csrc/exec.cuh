@@ -84,8 +84,12 @@ EAV1_DEV void exec_itx_residual(const FrameCtx &fc, const Eav1Cmd &c, CtaScratch
 #else
 #define EAV1_EXEC_LINK EAV1_DEV
 #endif
+// Returns how many commands it consumed: an intra prediction directly followed by the residual
+// add of the same transform block (`next`) finishes the block in one go, without a second trip
+// through the dispatch.
 template <typename BD>
-EAV1_EXEC_LINK void exec_cmd(const FrameCtx &fc, const Eav1Cmd &c, CtaScratch &sm, int tid, int nthr)
+EAV1_EXEC_LINK int exec_cmd(const FrameCtx &fc, const Eav1Cmd &c, CtaScratch &sm, int tid, int nthr,
+                            const Eav1Cmd *next = nullptr)
 {
     typedef typename BD::pixel pixel;
     const int bdmax = fc.bitdepth_max;
@@ -149,6 +153,12 @@ EAV1_EXEC_LINK void exec_cmd(const FrameCtx &fc, const Eav1Cmd &c, CtaScratch &s
         ipred_block<pixel>(fc.tab, dst8, dstride, sm.ip.edge, sm.ip.edge2, c.u.ipred.mode, c.w, c.h,
                            c.u.ipred.angle, c.u.ipred.max_w, c.u.ipred.max_h, bdmax, tid, nthr);
         PROF_MARK(3);
+        if (next && next->op == EAV1_OP_ITX && (next->flags & EAV1_F_RESID) && next->plane == c.plane &&
+            next->x == c.x && next->y == c.y && next->w == c.w && next->h == c.h && !(c.flags & EAV1_F_DST_ARENA)) {
+            CTA_SYNC();
+            res_add<BD>(dst8, dstride, (const int16_t *)(fc.arena + next->dst_off), c.w, c.h, bdmax, tid, nthr);
+            return 2;
+        }
         break;
     case EAV1_OP_CFL:
         cfl_ac_block<pixel>(fc.cur[0], c.u.ipred.lx, c.u.ipred.ly, c.u.ipred.w_pad, c.u.ipred.h_pad, c.w, c.h,
@@ -173,6 +183,7 @@ EAV1_EXEC_LINK void exec_cmd(const FrameCtx &fc, const Eav1Cmd &c, CtaScratch &s
     default:
         break;
     }
+    return 1;
 }
 
 } // namespace eav1

@@ -78,12 +78,22 @@ EAV1_DEV void build_edge(const Plane &pl, const Eav1Cmd &c, int bitdepth_max, ui
             }
         }
     }
-    CTA_SYNC();
-    if ((needs & 4) && tid == 0) {
+    // top-left sample: the last thread fetches what it needs itself, so the array is complete after one barrier
+    if ((needs & 4) && tid == nthr - 1) {
         int v;
         if (have_left) v = have_top ? *px_at<pixel>(pl, ex - 1, ey - 1) : *px_at<pixel>(pl, ex - 1, ey);
         else v = have_top ? *px_at<pixel>(pl, ex, ey - 1) : (1 << bitdepth) >> 1;
-        if (c.u.ipred.have & 4) v = ((E[-1] + E[1]) * 5 + v * 6 + 8) >> 4;
+        if (c.u.ipred.have & 4) {
+            // corner filter of z2 (ipred_tmpl.c): 5/6/5 taps over left[0], top-left, top[0] as the edge array holds them
+            int l0, t0;
+            if (needs & 1) l0 = have_left ? *px_at<pixel>(pl, ex - 1, ey + imin(0, c.u.ipred.n_left - 1))
+                                          : (have_top ? *px_at<pixel>(pl, ex, ey - 1) : ((1 << bitdepth) >> 1) + 1);
+            else l0 = 0;
+            if (needs & 2) t0 = have_top ? *px_at<pixel>(pl, ex + imin(0, c.u.ipred.n_top - 1), ey - 1)
+                                         : (have_left ? *px_at<pixel>(pl, ex - 1, ey) : ((1 << bitdepth) >> 1) - 1);
+            else t0 = 0;
+            v = ((l0 + t0) * 5 + v * 6 + 8) >> 4;
+        }
         E[0] = (uint16_t)v;
     }
     CTA_SYNC();
@@ -136,6 +146,32 @@ EAV1_DEV void edge_upsample(uint16_t *out, int hsz, const uint16_t *in, int from
     }
 }
 
+// four horizontally adjacent samples in one store (x is a multiple of 4, rows are 4-sample aligned)
+template <typename pixel>
+EAV1_DEV void store4(pixel *q, int v0, int v1, int v2, int v3) {
+    if (sizeof(pixel) == 1)
+        *reinterpret_cast<uint32_t *>(q) = (uint32_t)v0 | (uint32_t)v1 << 8 | (uint32_t)v2 << 16 | (uint32_t)v3 << 24;
+    else {
+        uint2 o; o.x = (uint32_t)v0 | (uint32_t)v1 << 16; o.y = (uint32_t)v2 | (uint32_t)v3 << 16;
+        *reinterpret_cast<uint2 *>(q) = o;
+    }
+}
+
+// sum of p[0], p[step], ... (n terms), every thread gets the total: each warp reduces on its own
+EAV1_DEV unsigned edge_sum(const uint16_t *p, int step, int n, int tid, int nthr) {
+#if defined(__CUDA_ARCH__)
+    unsigned s = 0;
+    if (nthr >= 32) {
+        for (int i = tid & 31; i < n; i += 32) s += p[i * step];
+        for (int o = 16; o; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+        return s;
+    }
+#endif
+    unsigned t = 0;
+    for (int i = 0; i < n; i++) t += p[i * step];
+    return t;
+}
+
 // Predict a w x h block into dst (stride in pixels) from the edge array (edge[EDGE_C] = top-left).
 // edge2 is scratch of the same size.
 template <typename pixel>
@@ -144,22 +180,16 @@ EAV1_DEVN void ipred_block(const Eav1Tables *tab, pixel *dst, int stride, uint16
                           int bitdepth_max, int tid, int nthr)
 {
     const uint16_t *E = edge + EDGE_C;
+    // w and h are powers of two >= 4: samples are handled four to a thread, i4 -> (y, x = 4*(i4 & m4))
+    const int lw = ctz32((unsigned)w), lw4 = lw - 2, m4 = (w >> 2) - 1, n4 = (w * h) >> 2;
     switch (mode) {
     case IP_DC: case IP_LEFT_DC: case IP_TOP_DC: case IP_DC_128: {
         int dc;
         if (mode == IP_DC_128) dc = (bitdepth_max + 1) >> 1;
-        else if (mode == IP_TOP_DC) {
-            unsigned s = w >> 1;
-            for (int i = 0; i < w; i++) s += E[1 + i];
-            dc = s >> ctz32(w);
-        } else if (mode == IP_LEFT_DC) {
-            unsigned s = h >> 1;
-            for (int i = 0; i < h; i++) s += E[-(1 + i)];
-            dc = s >> ctz32(h);
-        } else {
-            unsigned s = (w + h) >> 1;
-            for (int i = 0; i < w; i++) s += E[1 + i];
-            for (int i = 0; i < h; i++) s += E[-(1 + i)];
+        else if (mode == IP_TOP_DC) dc = ((w >> 1) + edge_sum(&E[1], 1, w, tid, nthr)) >> lw;
+        else if (mode == IP_LEFT_DC) dc = ((h >> 1) + edge_sum(&E[-1], -1, h, tid, nthr)) >> ctz32(h);
+        else {
+            unsigned s = ((w + h) >> 1) + edge_sum(&E[1], 1, w, tid, nthr) + edge_sum(&E[-1], -1, h, tid, nthr);
             s >>= ctz32(w + h);
             if (w != h) {
                 const bool quarter = w > h * 2 || h > w * 2;
@@ -168,39 +198,55 @@ EAV1_DEVN void ipred_block(const Eav1Tables *tab, pixel *dst, int stride, uint16
             }
             dc = s;
         }
-        for (int i = tid; i < w * h; i += nthr) dst[(i / w) * stride + (i % w)] = (pixel)dc;
+        for (int i = tid; i < n4; i += nthr) store4<pixel>(dst + (i >> lw4) * stride + ((i & m4) << 2), dc, dc, dc, dc);
         break;
     }
     case IP_VERT:
-        for (int i = tid; i < w * h; i += nthr) dst[(i / w) * stride + (i % w)] = (pixel)E[1 + (i % w)];
+        for (int i = tid; i < n4; i += nthr) {
+            const int x = (i & m4) << 2;
+            store4<pixel>(dst + (i >> lw4) * stride + x, E[1 + x], E[2 + x], E[3 + x], E[4 + x]);
+        }
         break;
     case IP_HOR:
-        for (int i = tid; i < w * h; i += nthr) dst[(i / w) * stride + (i % w)] = (pixel)E[-(1 + i / w)];
+        for (int i = tid; i < n4; i += nthr) {
+            const int y = i >> lw4, v = E[-(1 + y)];
+            store4<pixel>(dst + y * stride + ((i & m4) << 2), v, v, v, v);
+        }
         break;
     case IP_PAETH: {
         const int tl = E[0];
-        for (int i = tid; i < w * h; i += nthr) {
-            const int y = i / w, x = i - y * w;
-            const int l = E[-(1 + y)], t = E[1 + x];
-            const int base = l + t - tl;
-            const int ld = iabs(l - base), td = iabs(t - base), tld = iabs(tl - base);
-            dst[y * stride + x] = (pixel)(ld <= td && ld <= tld ? l : td <= tld ? t : tl);
+        for (int i = tid; i < n4; i += nthr) {
+            const int y = i >> lw4, x = (i & m4) << 2;
+            const int l = E[-(1 + y)];
+            int v[4];
+#pragma unroll
+            for (int k = 0; k < 4; k++) {
+                const int t = E[1 + x + k];
+                const int base = l + t - tl;
+                const int ld = iabs(l - base), td = iabs(t - base), tld = iabs(tl - base);
+                v[k] = ld <= td && ld <= tld ? l : td <= tld ? t : tl;
+            }
+            store4<pixel>(dst + y * stride + x, v[0], v[1], v[2], v[3]);
         }
         break;
     }
     case IP_SMOOTH: case IP_SMOOTH_V: case IP_SMOOTH_H: {
         const uint8_t *wh_ = &tab->sm_weights[w], *wv = &tab->sm_weights[h];
         const int right = E[w], bottom = E[-h];
-        for (int i = tid; i < w * h; i += nthr) {
-            const int y = i / w, x = i - y * w;
-            int v;
-            if (mode == IP_SMOOTH)
-                v = (wv[y] * E[1 + x] + (256 - wv[y]) * bottom + wh_[x] * E[-(1 + y)] + (256 - wh_[x]) * right + 256) >> 9;
-            else if (mode == IP_SMOOTH_V)
-                v = (wv[y] * E[1 + x] + (256 - wv[y]) * bottom + 128) >> 8;
-            else
-                v = (wh_[x] * E[-(1 + y)] + (256 - wh_[x]) * right + 128) >> 8;
-            dst[y * stride + x] = (pixel)v;
+        for (int i = tid; i < n4; i += nthr) {
+            const int y = i >> lw4, x0 = (i & m4) << 2;
+            int v[4];
+#pragma unroll
+            for (int k = 0; k < 4; k++) {
+                const int x = x0 + k;
+                if (mode == IP_SMOOTH)
+                    v[k] = (wv[y] * E[1 + x] + (256 - wv[y]) * bottom + wh_[x] * E[-(1 + y)] + (256 - wh_[x]) * right + 256) >> 9;
+                else if (mode == IP_SMOOTH_V)
+                    v[k] = (wv[y] * E[1 + x] + (256 - wv[y]) * bottom + 128) >> 8;
+                else
+                    v[k] = (wh_[x] * E[-(1 + y)] + (256 - wh_[x]) * right + 128) >> 8;
+            }
+            store4<pixel>(dst + y * stride + x0, v[0], v[1], v[2], v[3]);
         }
         break;
     }
@@ -223,14 +269,17 @@ EAV1_DEVN void ipred_block(const Eav1Tables *tab, pixel *dst, int stride, uint16
         }
         CTA_SYNC();
         const int inc = 1 + up;
-        for (int i = tid; i < w * h; i += nthr) {
-            const int y = i / w, x = i - y * w;
+        for (int i = tid; i < n4; i += nthr) {
+            const int y = i >> lw4, x0 = (i & m4) << 2;
             const int xpos = dx * (y + 1), frac = xpos & 0x3E;
-            const int base = (xpos >> 6) + x * inc;
-            int v;
-            if (base < max_base_x) v = (top[base] * (64 - frac) + top[base + 1] * frac + 32) >> 6;
-            else v = top[max_base_x];
-            dst[y * stride + x] = (pixel)v;
+            int v[4];
+#pragma unroll
+            for (int k = 0; k < 4; k++) {
+                const int base = (xpos >> 6) + (x0 + k) * inc;
+                if (base < max_base_x) v[k] = (top[base] * (64 - frac) + top[base + 1] * frac + 32) >> 6;
+                else v[k] = top[max_base_x];
+            }
+            store4<pixel>(dst + y * stride + x0, v[0], v[1], v[2], v[3]);
         }
         break;
     }
@@ -263,20 +312,26 @@ EAV1_DEVN void ipred_block(const Eav1Tables *tab, pixel *dst, int stride, uint16
         CTA_SYNC();
         const int inc_x = 1 + up_above;
         const uint16_t *left = &T[-(1 + up_left)];
-        for (int i = tid; i < w * h; i += nthr) {
-            const int y = i / w, x = i - y * w;
+        for (int i = tid; i < n4; i += nthr) {
+            const int y = i >> lw4, x0 = (i & m4) << 2;
             const int xpos = ((1 + up_above) << 6) - dx * (y + 1);
-            const int base_x = (xpos >> 6) + x * inc_x;
-            int v;
-            if (base_x >= 0) {
-                const int fx = xpos & 0x3E;
-                v = T[base_x] * (64 - fx) + T[base_x + 1] * fx;
-            } else {
-                const int ypos = (y << (6 + up_left)) - dy * (x + 1);
-                const int base_y = ypos >> 6, fy = ypos & 0x3E;
-                v = left[-base_y] * (64 - fy) + left[-(base_y + 1)] * fy;
+            int o[4];
+#pragma unroll
+            for (int k = 0; k < 4; k++) {
+                const int x = x0 + k;
+                const int base_x = (xpos >> 6) + x * inc_x;
+                int v;
+                if (base_x >= 0) {
+                    const int fx = xpos & 0x3E;
+                    v = T[base_x] * (64 - fx) + T[base_x + 1] * fx;
+                } else {
+                    const int ypos = (y << (6 + up_left)) - dy * (x + 1);
+                    const int base_y = ypos >> 6, fy = ypos & 0x3E;
+                    v = left[-base_y] * (64 - fy) + left[-(base_y + 1)] * fy;
+                }
+                o[k] = (v + 32) >> 6;
             }
-            dst[y * stride + x] = (pixel)((v + 32) >> 6);
+            store4<pixel>(dst + y * stride + x0, o[0], o[1], o[2], o[3]);
         }
         break;
     }
@@ -299,14 +354,17 @@ EAV1_DEVN void ipred_block(const Eav1Tables *tab, pixel *dst, int stride, uint16
         }
         CTA_SYNC();
         const int inc = 1 + up;
-        for (int i = tid; i < w * h; i += nthr) {
-            const int y = i / w, x = i - y * w;
-            const int ypos = dy * (x + 1), frac = ypos & 0x3E;
-            const int base = (ypos >> 6) + y * inc;
-            int v;
-            if (base < max_base_y) v = (left[-base] * (64 - frac) + left[-(base + 1)] * frac + 32) >> 6;
-            else v = left[-max_base_y];
-            dst[y * stride + x] = (pixel)v;
+        for (int i = tid; i < n4; i += nthr) {
+            const int y = i >> lw4, x0 = (i & m4) << 2;
+            int v[4];
+#pragma unroll
+            for (int k = 0; k < 4; k++) {
+                const int ypos = dy * (x0 + k + 1), frac = ypos & 0x3E;
+                const int base = (ypos >> 6) + y * inc;
+                if (base < max_base_y) v[k] = (left[-base] * (64 - frac) + left[-(base + 1)] * frac + 32) >> 6;
+                else v[k] = left[-max_base_y];
+            }
+            store4<pixel>(dst + y * stride + x0, v[0], v[1], v[2], v[3]);
         }
         break;
     }

@@ -202,8 +202,11 @@ def stage_bytes(info, P):
     the dataflow kernel reads the coefficient/palette payload actually shipped and reads +
     writes every sample its commands touch. Each post filter = read P + write P."""
     mc = 2 * info.mc_px
-    recon = info.payload_bytes + 2 * info.unit_px
-    return [recon, 2 * P if info.n_lf else 0, 2 * P if info.cdef else 0, 2 * P if info.n_lr else 0, mc]
+    # two-step transform blocks: phase 1b reads the coefficient payload and writes an int16 residual
+    # per sample; the dataflow kernel reads that residual and reads + writes every sample it touches
+    resid = info.payload_bytes + 2 * info.resid_px
+    recon = 2 * info.resid_px + 2 * info.unit_px
+    return [recon, 2 * P if info.n_lf else 0, 2 * P if info.cdef else 0, 2 * P if info.n_lr else 0, mc, 0, resid]
 
 
 def run_ours(args, man, obu):
@@ -330,22 +333,24 @@ def run_ours(args, man, obu):
     e2e_t = max_over_ranks(time.perf_counter() - t_all0)
 
     # ---- roofline of the stage with the largest share of device time
-    tot_bytes = [0, 0, 0, 0, 0]
+    KS = [0, 1, 2, 3, 4, 6]
+    tot_bytes = [0] * 7
     for si in infos:
         sb = stage_bytes(si, P)
-        for k in range(5):
+        for k in KS:
             tot_bytes[k] += sb[k]
-    names = ["recon_frame_kernel (dataflow: intra, residual, compound, blend)", "deblock_kernel (cols+rows)",
-             "cdef_kernel", "lr_kernel (+ plane copy)", "mc_kernel (motion compensation)"]
-    stage_ms = [ms[k] / args.steps for k in range(5)]          # per step (= per 120 frames)
-    dom = max(range(5), key=lambda k: stage_ms[k])
+    names = ["recon_frame_kernel (dataflow: intra prediction, residual add, compound, blend)", "deblock_kernel (cols+rows)",
+             "cdef_kernel", "lr_kernel (+ plane copy)", "mc_kernel (motion compensation)", "fg (unused here)",
+             "resid_kernel (inverse transforms -> residual blocks)"]
+    stage_ms = [ms[k] / args.steps for k in range(7)]          # per step (= per 120 frames)
+    dom = max(KS, key=lambda k: stage_ms[k])
     peak, peak_src = measured_peak()
     achieved = (tot_bytes[dom] / 1e9) / (stage_ms[dom] / 1e3) if stage_ms[dom] > 0 else 0.0
     stages = {names[k].split(" ")[0]: {"ms_per_step": round(stage_ms[k], 4),
                                        "launches_per_step": int(ln[k] // args.steps),
                                        "alg_bytes_per_step": int(tot_bytes[k]),
                                        "gbs": round((tot_bytes[k] / 1e9) / (stage_ms[k] / 1e3), 2) if stage_ms[k] > 0 else None}
-              for k in range(5)}
+              for k in KS}
     all_bytes = sum(tot_bytes)
     out = {
         "metric": METRIC, "value": world * n_frames * args.steps / (dev_ms / 1e3), "unit": UNIT,

@@ -144,7 +144,7 @@ __device__ __forceinline__ void recon_worker(const FrameCtx &fc, const ReconArgs
                 }
             }
         }
-        if (ra.debug && tid == 0) atomicAdd(&ra.ctrl[4], 1u);
+        if (ra.debug == 1 && tid == 0) atomicAdd(&ra.ctrl[4], 1u);
         if (ra.trace && tid == 0) {
             unsigned long long *t = &ra.trace[EAV1_TRACE_WORDS * (size_t)id];
             t[0] = t_ticket; t[1] = t_ready; t[2] = global_ns();
@@ -217,7 +217,7 @@ mc_kernel(FrameCtx fc, const Eav1Cmd *__restrict__ cmds, const uint32_t *__restr
 // (register path), one CTA per block with a 64-point side. Items arrive sorted by (size, type) so
 // that neighbouring warps run the same code. The residual lands in the arena; phase 2 adds it.
 template <typename BD>
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(128, 4)
 resid_kernel(FrameCtx fc, const Eav1Cmd *__restrict__ cmds, const uint32_t *__restrict__ items,
              uint32_t n_small, uint32_t n_small_ctas, uint32_t n_items)
 {
@@ -381,12 +381,15 @@ struct Eav1cuCtx {
     std::vector<uint32_t> est_tmp, order_tmp, bucket_tmp, ritem_tmp, tail_tmp, order2_tmp;
     std::vector<Eav1Cmd> cmd_tmp;
     unsigned long long *d_trace = nullptr;   // set only inside eav1cu_staged_trace
+    bool serial_phase1 = false;   // EAV1_SERIAL_PHASE1: residuals on the main stream (profiling, debugging)
     int warp_mode = 0;   // 0: every chain on a CTA, 1: independent small chains on warps, 2: all small chains on warps
     int err = 0;
     std::string errmsg;
     std::mutex mu;
     long long n_launches = 0, h2d_bytes = 0, d2h_bytes = 0, n_frames = 0;
     bool own_stream = true;
+    cudaStream_t stream2 = nullptr;            // phase 1b (residuals) runs beside phase 1 (motion compensation)
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     // optional per-stage device timing (bench.py's roofline leg)
     bool stage_timing = false;
     struct Span { cudaEvent_t a, b; int stage; int launches; };
@@ -520,6 +523,14 @@ int eav1cu_ctx_create(Eav1cuCtx **out, int device)
         ctx->recon_grid = sms * per;
     }
     if (const char *e = getenv("EAV1_WARP_MODE")) ctx->warp_mode = atoi(e);
+    ctx->serial_phase1 = getenv("EAV1_SERIAL_PHASE1") != nullptr;
+    if (!ctx->stream2) {
+        if (cudaStreamCreateWithFlags(&ctx->stream2, cudaStreamNonBlocking) != cudaSuccess ||
+            cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming) != cudaSuccess ||
+            cudaEventCreateWithFlags(&ctx->ev_join, cudaEventDisableTiming) != cudaSuccess) {
+            if (ctx->stream2) { cudaStreamDestroy(ctx->stream2); ctx->stream2 = nullptr; }   // run phase 1b on the main stream
+        }
+    }
     if (const char *e = getenv("EAV1_DEBUG_CHECK")) ctx->debug_check = atoi(e) ? atoi(e) : 1;
     if (ctx->debug_check == 2) { cudaMalloc(&ctx->d_sums, 64 * 2 * 8); cudaMemset(ctx->d_sums, 0, 64 * 2 * 8); cudaDeviceSynchronize(); }
     *out = ctx;
@@ -539,7 +550,7 @@ static void ctx_free(Eav1cuCtx *ctx)
     free_buf(ctx->arena);
     for (Slot &sl : ctx->slot) {
         free_buf(sl.cmds); free_buf(sl.payload); free_buf(sl.lfrec); free_buf(sl.lflvl); free_buf(sl.lrrec);
-        free_buf(sl.lfmask); free_buf(sl.deps); free_buf(sl.recs); free_buf(sl.items);
+        free_buf(sl.lfmask); free_buf(sl.deps); free_buf(sl.recs); free_buf(sl.items); free_buf(sl.ritems);
         if (sl.done) cudaEventDestroy(sl.done);
     }
     for (cudaEvent_t e : ctx->fence_ev) if (e) cudaEventDestroy(e);
@@ -552,6 +563,9 @@ static void ctx_free(Eav1cuCtx *ctx)
     for (cudaEvent_t e : ctx->ev_pool) cudaEventDestroy(e);
     for (FramePlan *sp : ctx->staged) { for (void *d : sp->owned) cudaFree(d); delete sp; }
     if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
+    if (ctx->stream2) cudaStreamDestroy(ctx->stream2);
+    if (ctx->ev_fork) cudaEventDestroy(ctx->ev_fork);
+    if (ctx->ev_join) cudaEventDestroy(ctx->ev_join);
     delete ctx;
 }
 
@@ -753,14 +767,14 @@ static cudaEvent_t ev_get(Eav1cuCtx *ctx)
 }
 
 struct StageTimer {
-    Eav1cuCtx *ctx; int stage; long long l0; cudaEvent_t a = nullptr;
-    StageTimer(Eav1cuCtx *c, int st) : ctx(c), stage(st), l0(c->n_launches) {
-        if (ctx->stage_timing) { a = ev_get(ctx); cudaEventRecord(a, ctx->stream); }
+    Eav1cuCtx *ctx; int stage; long long l0; cudaEvent_t a = nullptr; cudaStream_t on;
+    StageTimer(Eav1cuCtx *c, int st, cudaStream_t s = nullptr) : ctx(c), stage(st), l0(c->n_launches), on(s ? s : c->stream) {
+        if (ctx->stage_timing) { a = ev_get(ctx); cudaEventRecord(a, on); }
     }
     ~StageTimer() {
         if (!a) return;
         cudaEvent_t b = ev_get(ctx);
-        cudaEventRecord(b, ctx->stream);
+        cudaEventRecord(b, on);
         ctx->spans.push_back({a, b, stage, (int)(ctx->n_launches - l0)});
     }
 };
@@ -1000,6 +1014,20 @@ static int plan_launch(Eav1cuCtx *ctx, FramePlan &pl)
     fc.masks = ctx->d_masks;
     fc.arena = ctx->arena.d;
     fc.payload = pl.d_payload;
+    // Phase 1: motion compensation on the main stream, the residuals of the same frame beside it
+    // on a second stream (they share nothing); the dataflow kernel waits for both.
+    const bool fork = pl.n_ritems && ctx->stream2 && !ctx->serial_phase1;
+    cudaStream_t rs = fork ? ctx->stream2 : st;
+    if (fork) { CK(cudaEventRecord(ctx->ev_fork, st)); CK(cudaStreamWaitEvent(rs, ctx->ev_fork, 0)); }
+    if (pl.n_ritems) {
+        StageTimer tm(ctx, 6, rs);
+        const unsigned small_ctas = (pl.n_ritems_small + 3) / 4;
+        const unsigned grid = small_ctas + (pl.n_ritems - pl.n_ritems_small);
+        if (hbd) resid_kernel<BD16><<<grid, 128, 0, rs>>>(fc, pl.d_cmds, pl.d_ritems, pl.n_ritems_small, small_ctas, pl.n_ritems);
+        else     resid_kernel<BD8><<<grid, 128, 0, rs>>>(fc, pl.d_cmds, pl.d_ritems, pl.n_ritems_small, small_ctas, pl.n_ritems);
+        ctx->n_launches++;
+    }
+    if (fork) CK(cudaEventRecord(ctx->ev_join, rs));
     if (pl.n_items) {
         StageTimer tm(ctx, 4);
         const unsigned grid = (pl.n_items + 3) / 4;
@@ -1007,14 +1035,7 @@ static int plan_launch(Eav1cuCtx *ctx, FramePlan &pl)
         else     mc_kernel<BD8><<<grid, 128, 0, st>>>(fc, pl.d_cmds, pl.d_items, pl.n_items);
         ctx->n_launches++;
     }
-    if (pl.n_ritems) {
-        StageTimer tm(ctx, 6);
-        const unsigned small_ctas = (pl.n_ritems_small + 3) / 4;
-        const unsigned grid = small_ctas + (pl.n_ritems - pl.n_ritems_small);
-        if (hbd) resid_kernel<BD16><<<grid, 128, 0, st>>>(fc, pl.d_cmds, pl.d_ritems, pl.n_ritems_small, small_ctas, pl.n_ritems);
-        else     resid_kernel<BD8><<<grid, 128, 0, st>>>(fc, pl.d_cmds, pl.d_ritems, pl.n_ritems_small, small_ctas, pl.n_ritems);
-        ctx->n_launches++;
-    }
+    if (fork) CK(cudaStreamWaitEvent(st, ctx->ev_join, 0));
     if (pl.n_chains) {
         StageTimer tm(ctx, 0);
         if (pl.n_chains > ctx->done_cap) return fail(ctx, EAV1CU_ERR_INVAL, "done-flag array smaller than the staged frame");
@@ -1031,7 +1052,7 @@ static int plan_launch(Eav1cuCtx *ctx, FramePlan &pl)
         if (!pl.n_small) big_ctas = std::min<unsigned>(pl.n_big, grid);
         grid = big_ctas + small_ctas;
         ra.n_big_ctas = big_ctas; ra.n_workers = big_ctas + 4 * small_ctas;
-        ra.debug = ctx->debug_check == 1;
+        ra.debug = (uint32_t)ctx->debug_check;
         ra.trace = ctx->d_trace;
         ra.hist = ctx->d_trace ? ctx->d_trace + (size_t)pl.n_chains * EAV1_TRACE_WORDS : nullptr;
         if (ctx->debug_check == 2) {

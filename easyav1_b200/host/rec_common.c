@@ -6,6 +6,7 @@
 #include <errno.h>
 #include <pthread.h>
 #include <stdio.h>
+#include <time.h>
 #include <stdlib.h>
 #include <string.h>
 
@@ -590,10 +591,22 @@ static void *submit_main(void *arg)
     Eav1Rec *r = arg;
     const int digest = getenv("EAV1_JOB_HASH") != NULL;
     const int sync_each = getenv("EAV1_SYNC_EACH") != NULL;
+    const int timing = getenv("EAV1_TIMING") != NULL;
+    double t_idle = 0, t_busy = 0; long n_jobs = 0, n_waited = 0;
+    struct timespec ts0, ts1;
     pthread_mutex_lock(&r->q_mu);
     for (;;) {
-        while (!r->q_stop && !(r->q_head && r->q_head->seq == r->seq_submit))
+        if (timing) clock_gettime(CLOCK_MONOTONIC, &ts0);
+        int waited = 0;
+        while (!r->q_stop && !(r->q_head && r->q_head->seq == r->seq_submit)) {
+            waited = 1;
             pthread_cond_wait(&r->q_cv, &r->q_mu);
+        }
+        if (timing) {
+            clock_gettime(CLOCK_MONOTONIC, &ts1);
+            t_idle += (ts1.tv_sec - ts0.tv_sec) + 1e-9 * (ts1.tv_nsec - ts0.tv_nsec);
+            n_waited += waited;
+        }
         if (!(r->q_head && r->q_head->seq == r->seq_submit)) break;   /* stop, nothing runnable */
         Eav1Job *j = r->q_head;
         r->q_head = j->next;
@@ -636,11 +649,19 @@ static void *submit_main(void *arg)
             pd_unref(cur);
             for (int i = 0; i < 7; i++) if (j->ref[i]) pd_unref(j->ref[i]);
         }
+        if (timing) {
+            clock_gettime(CLOCK_MONOTONIC, &ts0);
+            t_busy += (ts0.tv_sec - ts1.tv_sec) + 1e-9 * (ts0.tv_nsec - ts1.tv_nsec);
+            n_jobs++;
+        }
         pthread_mutex_lock(&r->q_mu);
         j->next = r->job_free;
         r->job_free = j;
     }
     pthread_mutex_unlock(&r->q_mu);
+    if (timing && n_jobs)
+        fprintf(stderr, "EAV1 TIMING: submit thread: %ld jobs, busy %.3f ms/job, idle %.3f ms/job, found the queue empty %ld times\n",
+                n_jobs, 1e3 * t_busy / n_jobs, 1e3 * t_idle / n_jobs, n_waited);
     return NULL;
 }
 

@@ -7,6 +7,7 @@
 // shipped with the product: easyav1_b200 only ever loads libeasyav1_cuda.so and fails
 // loudly without a CUDA device.
 #include <stdio.h>
+#include <time.h>
 #include <stdlib.h>
 #include <string.h>
 #include <algorithm>
@@ -145,8 +146,13 @@ int eav1cu_frame_submit(Eav1cuCtx *c, const Eav1FrameDesc *fd, const Eav1Cmd *cm
             static eav1::Scheduler sch; static eav1::UnitGraph g;
             const Picture &cp = c->pics[fd->cur];
             int pw[3] = { cp.pl[0].w, cp.pl[1].w, cp.pl[2].w }, ph[3] = { cp.pl[0].h, cp.pl[1].h, cp.pl[2].h };
+            struct timespec ta, tb; clock_gettime(CLOCK_MONOTONIC, &ta);
             sch.reset(pw, ph);
             sch.build_units(cmds, n, g);
+            clock_gettime(CLOCK_MONOTONIC, &tb);
+            static double tot_ms; tot_ms += 1e3 * (tb.tv_sec - ta.tv_sec) + 1e-6 * (tb.tv_nsec - ta.tv_nsec);
+            fprintf(stderr, "planner: frame %zu build_units %.3f ms (running mean %.3f ms)\n", frames,
+                    1e3 * (tb.tv_sec - ta.tv_sec) + 1e-6 * (tb.tv_nsec - ta.tv_nsec), tot_ms / frames);
             const size_t nu = g.unit_cmd.size();
             std::vector<uint32_t> cp_cmds(nu, 0), cp_units(nu, 0), pred(nu, UINT32_MAX);
             size_t best = 0; size_t tot = 0, hist[8] = {0};

@@ -102,12 +102,19 @@ __device__ __forceinline__ void recon_worker(const FrameCtx &fc, const ReconArgs
         const uint32_t first = r0.x, count = r0.y, d0 = r0.z, nd = r0.w;
         unsigned long long t_ticket = 0, t_ready = 0;
         if (ra.trace && tid == 0) t_ticket = global_ns();
+        // fetch the unit's first commands while its producers are still being polled
+        {
+            const uint32_t n = min(count, (uint32_t)EAV1_CMD_STAGE);
+            const uint32_t *src = reinterpret_cast<const uint32_t *>(&ra.cmds[first]);
+            uint32_t *dst = reinterpret_cast<uint32_t *>(ws.cmd);
+            for (uint32_t i = tid; i < n * (sizeof(Eav1Cmd) / 4); i += nthr) dst[i] = src[i];
+        }
         for (uint32_t d = tid; d < nd; d += nthr) {
             const uint32_t *flag = &ra.done[ra.deps[d0 + d]];
             unsigned ns = 20;
             while (ld_acquire(flag) != ra.epoch) { __nanosleep(ns); if (ns < 320) ns <<= 1; }
         }
-        if (nd) CTA_SYNC();
+        CTA_SYNC();
         if (ra.trace && tid == 0) {
             t_ready = global_ns();
             unsigned long long last = 0, who = ~0ull;
@@ -121,11 +128,13 @@ __device__ __forceinline__ void recon_worker(const FrameCtx &fc, const ReconArgs
         long long cyc_stage = 0, cyc_op[3] = { 0, 0, 0 }, n_op[3] = { 0, 0, 0 };
         for (uint32_t base = 0; base < count; base += EAV1_CMD_STAGE) {
             const uint32_t n = min(count - base, (uint32_t)EAV1_CMD_STAGE);
-            const uint32_t *src = reinterpret_cast<const uint32_t *>(&ra.cmds[first + base]);
-            uint32_t *dst = reinterpret_cast<uint32_t *>(ws.cmd);
             long long c0 = ra.trace ? clock64() : 0;
-            for (uint32_t i = tid; i < n * (sizeof(Eav1Cmd) / 4); i += nthr) dst[i] = src[i];
-            CTA_SYNC();
+            if (base) {
+                const uint32_t *src = reinterpret_cast<const uint32_t *>(&ra.cmds[first + base]);
+                uint32_t *dst = reinterpret_cast<uint32_t *>(ws.cmd);
+                for (uint32_t i = tid; i < n * (sizeof(Eav1Cmd) / 4); i += nthr) dst[i] = src[i];
+                CTA_SYNC();
+            }
             if (ra.trace) { const long long c1 = clock64(); cyc_stage += c1 - c0; c0 = c1; }
             for (uint32_t c = 0; c < n;) {
                 const uint32_t c_this = c;

@@ -38,46 +38,40 @@ EAV1_DEV void build_edge(const Plane &pl, const Eav1Cmd &c, int bitdepth_max, ui
     const int have_left = c.u.ipred.have & 1, have_top = (c.u.ipred.have >> 1) & 1;
     const int bitdepth = 32 - clz32((unsigned)bitdepth_max);
     const int szl = c.u.ipred.th << 2, szt = c.u.ipred.tw << 2;
-    if (needs & 1) {
-        const int n = c.u.ipred.n_left;
-        const int fill = have_top ? *px_at<pixel>(pl, ex, ey - 1) : ((1 << bitdepth) >> 1) + 1;
-        for (int i = tid; i < szl; i += nthr) {
-            int v;
-            if (have_left) v = *px_at<pixel>(pl, ex - 1, ey + imin(i, n - 1));
-            else v = fill;
-            E[-(1 + i)] = (uint16_t)v;
+    PROF_BEGIN();
+    PROF_MARK(20);
+    // One pass over every edge sample that is needed: [0,nl) left, [nl,nl+nbl) bottom-left, then top and
+    // top-right. Each sample is one independent load (or a constant), so the whole gather costs one
+    // trip to L2 instead of one per part.
+    const int nl = (needs & 1) ? szl : 0, nbl = ((needs & 1) && (needs & 16)) ? szl : 0;
+    const int nt = (needs & 2) ? szt : 0, ntr = ((needs & 2) && (needs & 8)) ? szt : 0;
+    const int n_left = c.u.ipred.n_left, n_top = c.u.ipred.n_top;
+    const int nb = (c.u.ipred.have & 8) ? c.u.ipred.n_bl : 0, nr = (c.u.ipred.have & 16) ? c.u.ipred.n_tr : 0;
+    const int fill_l = ((1 << bitdepth) >> 1) + 1, fill_t = ((1 << bitdepth) >> 1) - 1;
+    const int total = nl + nbl + nt + ntr;
+    for (int j = tid; j < total; j += nthr) {
+        int px, py, cst = -1, slot;
+        if (j < nl + nbl) {   // left column, going down
+            const int i = j < nl ? j : j - nl;
+            slot = j < nl ? -(1 + i) : -(szl + 1 + i);
+            px = ex - 1;
+            if (j < nl) py = ey + imin(i, n_left - 1);
+            else if (nb) py = ey + szl + imin(i, nb - 1);
+            else py = ey + imin(szl - 1, n_left - 1);
+            if (!have_left) { if (have_top) { px = ex; py = ey - 1; } else cst = fill_l; }
+        } else {              // top row, going right
+            const int jj = j - nl - nbl;
+            const int i = jj < nt ? jj : jj - nt;
+            slot = jj < nt ? 1 + i : 1 + szt + i;
+            py = ey - 1;
+            if (jj < nt) px = ex + imin(i, n_top - 1);
+            else if (nr) px = ex + szt + imin(i, nr - 1);
+            else px = ex + imin(szt - 1, n_top - 1);
+            if (!have_top) { if (have_left) { px = ex - 1; py = ey; } else cst = fill_t; }
         }
-        if (needs & 16) {
-            const int nb = (c.u.ipred.have & 8) ? c.u.ipred.n_bl : 0;
-            for (int i = tid; i < szl; i += nthr) {
-                int v;
-                if (nb) v = *px_at<pixel>(pl, ex - 1, ey + szl + imin(i, nb - 1));
-                else if (have_left) v = *px_at<pixel>(pl, ex - 1, ey + imin(szl - 1, n - 1));
-                else v = fill;
-                E[-(szl + 1 + i)] = (uint16_t)v;
-            }
-        }
+        E[slot] = (uint16_t)(cst >= 0 ? cst : (int)*px_at<pixel>(pl, px, py));
     }
-    if (needs & 2) {
-        const int n = c.u.ipred.n_top;
-        const int fill = have_left ? *px_at<pixel>(pl, ex - 1, ey) : ((1 << bitdepth) >> 1) - 1;
-        for (int i = tid; i < szt; i += nthr) {
-            int v;
-            if (have_top) v = *px_at<pixel>(pl, ex + imin(i, n - 1), ey - 1);
-            else v = fill;
-            E[1 + i] = (uint16_t)v;
-        }
-        if (needs & 8) {
-            const int nr = (c.u.ipred.have & 16) ? c.u.ipred.n_tr : 0;
-            for (int i = tid; i < szt; i += nthr) {
-                int v;
-                if (nr) v = *px_at<pixel>(pl, ex + szt + imin(i, nr - 1), ey - 1);
-                else if (have_top) v = *px_at<pixel>(pl, ex + imin(szt - 1, n - 1), ey - 1);
-                else v = fill;
-                E[1 + szt + i] = (uint16_t)v;
-            }
-        }
-    }
+    PROF_MARK(22);
     // top-left sample: the last thread fetches what it needs itself, so the array is complete after one barrier
     if ((needs & 4) && tid == nthr - 1) {
         int v;
@@ -96,7 +90,9 @@ EAV1_DEV void build_edge(const Plane &pl, const Eav1Cmd &c, int bitdepth_max, ui
         }
         E[0] = (uint16_t)v;
     }
+    PROF_MARK(23);
     CTA_SYNC();
+    PROF_MARK(24);
 }
 
 EAV1_DEV int filter_strength(int wh, int angle, int is_sm) {
@@ -157,6 +153,17 @@ EAV1_DEV void store4(pixel *q, int v0, int v1, int v2, int v3) {
     }
 }
 
+// the same with the residual of the transform block added (row-major int16, `r` points at this group)
+template <typename pixel>
+EAV1_DEV void store4r(pixel *q, int v0, int v1, int v2, int v3, const int16_t *r, int bitdepth_max) {
+    if (r) {
+        const uint2 rr = *reinterpret_cast<const uint2 *>(r);
+        v0 = iclip(v0 + (int16_t)(rr.x & 0xffff), 0, bitdepth_max); v1 = iclip(v1 + (int16_t)(rr.x >> 16), 0, bitdepth_max);
+        v2 = iclip(v2 + (int16_t)(rr.y & 0xffff), 0, bitdepth_max); v3 = iclip(v3 + (int16_t)(rr.y >> 16), 0, bitdepth_max);
+    }
+    store4<pixel>(q, v0, v1, v2, v3);
+}
+
 // sum of p[0], p[step], ... (n terms), every thread gets the total: each warp reduces on its own
 EAV1_DEV unsigned edge_sum(const uint16_t *p, int step, int n, int tid, int nthr) {
 #if defined(__CUDA_ARCH__)
@@ -174,14 +181,18 @@ EAV1_DEV unsigned edge_sum(const uint16_t *p, int step, int n, int tid, int nthr
 
 // Predict a w x h block into dst (stride in pixels) from the edge array (edge[EDGE_C] = top-left).
 // edge2 is scratch of the same size.
+// With `res` (row-major int16 residual of the same block) the sum prediction + residual is written in
+// one go; returns whether it did so (filter-intra predicts from its own output and cannot).
 template <typename pixel>
-EAV1_DEVN void ipred_block(const Eav1Tables *tab, pixel *dst, int stride, uint16_t *edge, uint16_t *edge2,
+EAV1_DEVN bool ipred_block(const Eav1Tables *tab, pixel *dst, int stride, uint16_t *edge, uint16_t *edge2,
                           int mode, int w, int h, int angle_in, int max_w, int max_h,
-                          int bitdepth_max, int tid, int nthr)
+                          int bitdepth_max, int tid, int nthr, const int16_t *res = nullptr)
 {
     const uint16_t *E = edge + EDGE_C;
     // w and h are powers of two >= 4: samples are handled four to a thread, i4 -> (y, x = 4*(i4 & m4))
     const int lw = ctz32((unsigned)w), lw4 = lw - 2, m4 = (w >> 2) - 1, n4 = (w * h) >> 2;
+    PROF_BEGIN();
+    PROF_MARK(25);
     switch (mode) {
     case IP_DC: case IP_LEFT_DC: case IP_TOP_DC: case IP_DC_128: {
         int dc;
@@ -198,19 +209,19 @@ EAV1_DEVN void ipred_block(const Eav1Tables *tab, pixel *dst, int stride, uint16
             }
             dc = s;
         }
-        for (int i = tid; i < n4; i += nthr) store4<pixel>(dst + (i >> lw4) * stride + ((i & m4) << 2), dc, dc, dc, dc);
+        for (int i = tid; i < n4; i += nthr) store4r<pixel>(dst + (i >> lw4) * stride + ((i & m4) << 2), dc, dc, dc, dc, res ? res + (i << 2) : nullptr, bitdepth_max);
         break;
     }
     case IP_VERT:
         for (int i = tid; i < n4; i += nthr) {
             const int x = (i & m4) << 2;
-            store4<pixel>(dst + (i >> lw4) * stride + x, E[1 + x], E[2 + x], E[3 + x], E[4 + x]);
+            store4r<pixel>(dst + (i >> lw4) * stride + x, E[1 + x], E[2 + x], E[3 + x], E[4 + x], res ? res + (i << 2) : nullptr, bitdepth_max);
         }
         break;
     case IP_HOR:
         for (int i = tid; i < n4; i += nthr) {
             const int y = i >> lw4, v = E[-(1 + y)];
-            store4<pixel>(dst + y * stride + ((i & m4) << 2), v, v, v, v);
+            store4r<pixel>(dst + y * stride + ((i & m4) << 2), v, v, v, v, res ? res + (i << 2) : nullptr, bitdepth_max);
         }
         break;
     case IP_PAETH: {
@@ -226,7 +237,7 @@ EAV1_DEVN void ipred_block(const Eav1Tables *tab, pixel *dst, int stride, uint16
                 const int ld = iabs(l - base), td = iabs(t - base), tld = iabs(tl - base);
                 v[k] = ld <= td && ld <= tld ? l : td <= tld ? t : tl;
             }
-            store4<pixel>(dst + y * stride + x, v[0], v[1], v[2], v[3]);
+            store4r<pixel>(dst + y * stride + x, v[0], v[1], v[2], v[3], res ? res + (i << 2) : nullptr, bitdepth_max);
         }
         break;
     }
@@ -246,7 +257,7 @@ EAV1_DEVN void ipred_block(const Eav1Tables *tab, pixel *dst, int stride, uint16
                 else
                     v[k] = (wh_[x] * E[-(1 + y)] + (256 - wh_[x]) * right + 128) >> 8;
             }
-            store4<pixel>(dst + y * stride + x0, v[0], v[1], v[2], v[3]);
+            store4r<pixel>(dst + y * stride + x0, v[0], v[1], v[2], v[3], res ? res + (i << 2) : nullptr, bitdepth_max);
         }
         break;
     }
@@ -279,7 +290,7 @@ EAV1_DEVN void ipred_block(const Eav1Tables *tab, pixel *dst, int stride, uint16
                 if (base < max_base_x) v[k] = (top[base] * (64 - frac) + top[base + 1] * frac + 32) >> 6;
                 else v[k] = top[max_base_x];
             }
-            store4<pixel>(dst + y * stride + x0, v[0], v[1], v[2], v[3]);
+            store4r<pixel>(dst + y * stride + x0, v[0], v[1], v[2], v[3], res ? res + (i << 2) : nullptr, bitdepth_max);
         }
         break;
     }
@@ -331,7 +342,7 @@ EAV1_DEVN void ipred_block(const Eav1Tables *tab, pixel *dst, int stride, uint16
                 }
                 o[k] = (v + 32) >> 6;
             }
-            store4<pixel>(dst + y * stride + x0, o[0], o[1], o[2], o[3]);
+            store4r<pixel>(dst + y * stride + x0, o[0], o[1], o[2], o[3], res ? res + (i << 2) : nullptr, bitdepth_max);
         }
         break;
     }
@@ -364,11 +375,12 @@ EAV1_DEVN void ipred_block(const Eav1Tables *tab, pixel *dst, int stride, uint16
                 if (base < max_base_y) v[k] = (left[-base] * (64 - frac) + left[-(base + 1)] * frac + 32) >> 6;
                 else v[k] = left[-max_base_y];
             }
-            store4<pixel>(dst + y * stride + x0, v[0], v[1], v[2], v[3]);
+            store4r<pixel>(dst + y * stride + x0, v[0], v[1], v[2], v[3], res ? res + (i << 2) : nullptr, bitdepth_max);
         }
         break;
     }
     default: { // IP_FILTER: 4x2 cells, cell (cx,cy) needs (cx-1,cy), (cx,cy-1), (cx-1,cy-1)
+        res = nullptr;
         const int8_t (*taps)[8] = tab->filter_intra_taps[angle_in & 511];
         const int cw = w >> 2, ch = h >> 1;
         for (int d = 0; d < cw + ch - 1; d++) {
@@ -395,7 +407,10 @@ EAV1_DEVN void ipred_block(const Eav1Tables *tab, pixel *dst, int stride, uint16
         break;
     }
     }
+    PROF_MARK(26);
     CTA_SYNC();
+    PROF_MARK(27);
+    return res != nullptr;
 }
 
 // cfl_ac into ac[cw*ch] (shared). ypx addresses luma sample (lx,ly) of the current frame.

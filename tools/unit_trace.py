@@ -90,7 +90,8 @@ for op in range(14):
 if have_prof:
     lab = {0: "exec_cmd entry->switch", 1: "switch->ipred case", 2: "build_edge", 3: "ipred_block", 4: "switch->itx case",
            5: "itx_add total", 6: "switch->avg case", 7: "comp_avg", 10: "itx reg: row pass", 11: "itx reg: barrier",
-           12: "itx reg: col pass", 13: "itx reg: barrier"}
+           12: "itx reg: col pass", 13: "itx reg: barrier", 20: "edge: entry", 21: "edge: left part", 22: "edge: top part",
+           23: "edge: corner", 24: "edge: barrier", 25: "ipred_block: entry", 26: "ipred_block: mode body", 27: "ipred_block: barrier", 30: "probe: volatile global load", 31: "probe: ld.global.cg"}
     for k in sorted(lab):
         if prof[2 * k + 1]:
             print("  prof %-24s %8d x %6.0f cycles" % (lab[k], prof[2 * k + 1], prof[2 * k] / prof[2 * k + 1]))

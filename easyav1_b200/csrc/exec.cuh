@@ -150,19 +150,18 @@ EAV1_EXEC_LINK int exec_cmd(const FrameCtx &fc, const Eav1Cmd &c, CtaScratch &sm
         PROF_MARK(1);
         build_edge<pixel>(fc.cur[c.plane], c, bdmax, sm.ip.edge, tid, nthr);
         PROF_MARK(2);
-        if (next && next->op == EAV1_OP_ITX && (next->flags & EAV1_F_RESID) && next->plane == c.plane &&
-            next->x == c.x && next->y == c.y && next->w == c.w && next->h == c.h && !(c.flags & EAV1_F_DST_ARENA)) {
+        {
             // the residual add of the same transform block follows: finish the block here
-            const int16_t *res = (const int16_t *)(fc.arena + next->dst_off);
-            if (!ipred_block<pixel>(fc.tab, dst8, dstride, sm.ip.edge, sm.ip.edge2, c.u.ipred.mode, c.w, c.h,
-                                    c.u.ipred.angle, c.u.ipred.max_w, c.u.ipred.max_h, bdmax, tid, nthr, res))
-                res_add<BD>(dst8, dstride, res, c.w, c.h, bdmax, tid, nthr);
+            const bool fused = next && next->op == EAV1_OP_ITX && (next->flags & EAV1_F_RESID) && next->plane == c.plane &&
+                               next->x == c.x && next->y == c.y && next->w == c.w && next->h == c.h &&
+                               !(c.flags & EAV1_F_DST_ARENA);
+            const int16_t *res = fused ? (const int16_t *)(fc.arena + next->dst_off) : nullptr;
+            const bool added = ipred_block<pixel>(fc.tab, dst8, dstride, sm.ip.edge, sm.ip.edge2, c.u.ipred.mode, c.w, c.h,
+                                                  c.u.ipred.angle, c.u.ipred.max_w, c.u.ipred.max_h, bdmax, tid, nthr, res);
+            if (fused && !added) res_add<BD>(dst8, dstride, res, c.w, c.h, bdmax, tid, nthr);
             PROF_MARK(3);
-            return 2;
+            if (fused) return 2;
         }
-        ipred_block<pixel>(fc.tab, dst8, dstride, sm.ip.edge, sm.ip.edge2, c.u.ipred.mode, c.w, c.h,
-                           c.u.ipred.angle, c.u.ipred.max_w, c.u.ipred.max_h, bdmax, tid, nthr);
-        PROF_MARK(3);
         break;
     case EAV1_OP_CFL:
         cfl_ac_block<pixel>(fc.cur[0], c.u.ipred.lx, c.u.ipred.ly, c.u.ipred.w_pad, c.u.ipred.h_pad, c.w, c.h,

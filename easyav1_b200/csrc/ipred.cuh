@@ -49,8 +49,9 @@ EAV1_DEV void build_edge(const Plane &pl, const Eav1Cmd &c, int bitdepth_max, ui
     const int nb = (c.u.ipred.have & 8) ? c.u.ipred.n_bl : 0, nr = (c.u.ipred.have & 16) ? c.u.ipred.n_tr : 0;
     const int fill_l = ((1 << bitdepth) >> 1) + 1, fill_t = ((1 << bitdepth) >> 1) - 1;
     const int total = nl + nbl + nt + ntr;
-    for (int j = tid; j < total; j += nthr) {
-        int px, py, cst = -1, slot;
+    // where edge sample j comes from: (px,py) in the plane, or the constant cst >= 0; slot = index into E
+    auto locate = [&](int j, int &px, int &py, int &cst, int &slot) {
+        cst = -1;
         if (j < nl + nbl) {   // left column, going down
             const int i = j < nl ? j : j - nl;
             slot = j < nl ? -(1 + i) : -(szl + 1 + i);
@@ -69,7 +70,18 @@ EAV1_DEV void build_edge(const Plane &pl, const Eav1Cmd &c, int bitdepth_max, ui
             else px = ex + imin(szt - 1, n_top - 1);
             if (!have_top) { if (have_left) { px = ex - 1; py = ey; } else cst = fill_t; }
         }
-        E[slot] = (uint16_t)(cst >= 0 ? cst : (int)*px_at<pixel>(pl, px, py));
+    };
+    // two samples per thread and round, both loads in flight before either is stored
+    for (int j = tid; j < total; j += 2 * nthr) {
+        int px0, py0, c0, s0, px1 = 0, py1 = 0, c1 = 0, s1 = 0;
+        const bool two = j + nthr < total;
+        locate(j, px0, py0, c0, s0);
+        if (two) locate(j + nthr, px1, py1, c1, s1);
+        int v0 = c0, v1 = c1;
+        if (c0 < 0) v0 = *px_at<pixel>(pl, px0, py0);
+        if (two && c1 < 0) v1 = *px_at<pixel>(pl, px1, py1);
+        E[s0] = (uint16_t)v0;
+        if (two) E[s1] = (uint16_t)v1;
     }
     PROF_MARK(22);
     // top-left sample: the last thread fetches what it needs itself, so the array is complete after one barrier
@@ -184,7 +196,7 @@ EAV1_DEV unsigned edge_sum(const uint16_t *p, int step, int n, int tid, int nthr
 // With `res` (row-major int16 residual of the same block) the sum prediction + residual is written in
 // one go; returns whether it did so (filter-intra predicts from its own output and cannot).
 template <typename pixel>
-EAV1_DEVN bool ipred_block(const Eav1Tables *tab, pixel *dst, int stride, uint16_t *edge, uint16_t *edge2,
+EAV1_DEV bool ipred_block(const Eav1Tables *tab, pixel *dst, int stride, uint16_t *edge, uint16_t *edge2,
                           int mode, int w, int h, int angle_in, int max_w, int max_h,
                           int bitdepth_max, int tid, int nthr, const int16_t *res = nullptr)
 {

@@ -19,6 +19,8 @@ nmax = int(sys.argv[1]) if len(sys.argv) > 1 else 30
 i = 0
 while i < nmax and host.eav1_stream_next(h, C.byref(info), buf, cap, C.byref(used)) == 0:
     i += 1
+# frames may still be in flight in the decoder's threads: let them reach the engine before replaying
+host.eav1rec_drain(host.eav1_stream_ctx(h))
 E.eav1cu_set_capture(eng, 0)
 n = E.eav1cu_staged_count(eng)
 E.eav1cu_set_stage_timing(eng, 1)

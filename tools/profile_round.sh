@@ -8,7 +8,7 @@ python bench.py --steps 2 --warmup 3 > $out/${tag}_bench.json 2> $out/${tag}_ben
 EAV1_BENCH_PROFILE=1 ncu --profile-from-start off --metrics gpu__time_duration.sum --clock-control none --csv \
     --log-file $out/${tag}_launches.csv python bench.py --steps 2 --warmup 3 > $out/${tag}_ncu_launches.log 2>&1
 EAV1_BENCH_PROFILE=1 ncu --profile-from-start off --set full --clock-control none --import-source on \
-    -k regex:"recon_frame_kernel|mc_kernel|cdef_kernel|lr_kernel|deblock_kernel" --launch-count 14 \
+    -k regex:"recon_frame_kernel|resid_kernel|mc_kernel|cdef_kernel|lr_kernel|deblock_kernel" --launch-count 18 \
     -o $out/${tag}_full python bench.py --steps 2 --warmup 3 > $out/${tag}_ncu_full.log 2>&1
 python tools/vorbis_bench.py > $out/${tag}_vorbis.json 2> $out/${tag}_vorbis.err
 ncu --set full --clock-control none --import-source on -k regex:vorbis_kernel --launch-skip 6 --launch-count 1 \

@@ -147,6 +147,7 @@ EAV1_DEV void lf_unit(const PfParams &pp, const Eav1LfRec &r, int u)
 
 struct CdefSmem {
     int16_t tile[3][12 * 12];  // padded inputs, INT16_MIN marks "not available"
+    int32_t part[8][16];       // per direction: sums of the samples on each of its (up to 15) lines
     int32_t cost[8];
     int32_t dir, var;
 };
@@ -176,14 +177,23 @@ EAV1_DEV void cdef_filter(const Eav1Tables *tab, const Plane &out, int x0, int y
     const int pri_tap = 4 - ((pri >> bd8) & 1);
     const int pri_shift = pri ? imax(0, damping - ulog2(pri)) : 0;
     const int sec_shift = sec ? damping - ulog2(sec) : 0;
+    // tap offsets inside the stride-12 tile, fetched once (cdef_directions rows dir+2, dir+4, dir)
+    int op[2], o2[2], o3[2];
+    for (int k = 0; k < 2; k++) {
+        op[k] = tab->cdef_directions[dir + 2][k];
+        o2[k] = tab->cdef_directions[dir + 4][k];
+        o3[k] = tab->cdef_directions[dir][k];
+    }
+    const int lw = ulog2((unsigned)w);
     for (int i = tid; i < w * h; i += nthr) {
-        const int y = i / w, x = i - y * w;
+        const int y = i >> lw, x = i & (w - 1);
         const int16_t *t = tile + (y + 2) * 12 + x + 2;
         const int px = t[0];
         int sum = 0, mx = px, mn = px;
+#pragma unroll
         for (int k = 0; k < 2; k++) {
             if (pri) {
-                const int off = tab->cdef_directions[dir + 2][k];
+                const int off = op[k];
                 const int p0 = t[off], p1 = t[-off];
                 const int tap = k ? ((pri_tap & 3) | 2) : pri_tap;
                 sum += tap * cdef_constrain(p0 - px, pri, pri_shift);
@@ -193,8 +203,7 @@ EAV1_DEV void cdef_filter(const Eav1Tables *tab, const Plane &out, int x0, int y
                 mx = imax(imax(p0, p1), mx);
             }
             if (sec) {
-                const int o2 = tab->cdef_directions[dir + 4][k], o3 = tab->cdef_directions[dir][k];
-                const int s0 = t[o2], s1 = t[-o2], s2 = t[o3], s3 = t[-o3];
+                const int s0 = t[o2[k]], s1 = t[-o2[k]], s2 = t[o3[k]], s3 = t[-o3[k]];
                 const int tap = 2 - k;
                 sum += tap * (cdef_constrain(s0 - px, sec, sec_shift) + cdef_constrain(s1 - px, sec, sec_shift) +
                               cdef_constrain(s2 - px, sec, sec_shift) + cdef_constrain(s3 - px, sec, sec_shift));
@@ -220,29 +229,35 @@ EAV1_DEV void cdef_copy(const Plane &in, const Plane &out, int x0, int y0, int w
     }
 }
 
-// Direction search on the 8x8 block held in tile[0] (interior at +2,+2). Eight cooperating
-// threads each evaluate one direction's cost from its partial sums.
-EAV1_DEV void cdef_dir_cost(const int16_t *tile, int bd8, int n, int32_t *cost)
+// Direction search on the 8x8 block held in tile[0] (interior at +2,+2), cdef_find_dir
+// (cdef_tmpl.c:220-315). Step 1: every thread adds its samples into the line sums of all eight
+// directions (shared-memory adds; 64 samples x 8 directions spread over the group). Step 2: eight
+// threads turn the line sums of one direction each into its cost.
+#if defined(__CUDA_ARCH__)
+#define EAV1_SMEM_ADD(p, v) atomicAdd((p), (v))
+#else
+#define EAV1_SMEM_ADD(p, v) (*(p) += (v))
+#endif
+EAV1_DEV void cdef_dir_partial(const int16_t *tile, int bd8, int32_t (*part)[16], int tid, int nthr)
 {
-    // line index of sample (x,y) for direction n, and number of lines
-    int part[15];
-    for (int i = 0; i < 15; i++) part[i] = 0;
-    for (int y = 0; y < 8; y++)
-        for (int x = 0; x < 8; x++) {
-            const int px = (tile[(y + 2) * 12 + x + 2] >> bd8) - 128;
-            int idx;
-            switch (n) {
-            case 0: idx = y + x; break;
-            case 1: idx = y + (x >> 1); break;
-            case 2: idx = y; break;
-            case 3: idx = 3 + y - (x >> 1); break;
-            case 4: idx = 7 + y - x; break;
-            case 5: idx = 3 - (y >> 1) + x; break;
-            case 6: idx = x; break;
-            default: idx = (y >> 1) + x; break;
-            }
-            part[idx] += px;
-        }
+    // pairs of horizontally adjacent samples: directions whose line index uses x >> 1 (1, 3) or
+    // ignores x (2) take the pair as one add
+    for (int i = tid; i < 32; i += nthr) {
+        const int y = i >> 2, x = (i & 3) << 1;
+        const int a = (tile[(y + 2) * 12 + x + 2] >> bd8) - 128, b = (tile[(y + 2) * 12 + x + 3] >> bd8) - 128;
+        EAV1_SMEM_ADD(&part[0][y + x], a);             EAV1_SMEM_ADD(&part[0][y + x + 1], b);
+        EAV1_SMEM_ADD(&part[1][y + (x >> 1)], a + b);
+        EAV1_SMEM_ADD(&part[2][y], a + b);
+        EAV1_SMEM_ADD(&part[3][3 + y - (x >> 1)], a + b);
+        EAV1_SMEM_ADD(&part[4][7 + y - x], a);         EAV1_SMEM_ADD(&part[4][6 + y - x], b);
+        EAV1_SMEM_ADD(&part[5][3 - (y >> 1) + x], a);  EAV1_SMEM_ADD(&part[5][4 - (y >> 1) + x], b);
+        EAV1_SMEM_ADD(&part[6][x], a);                 EAV1_SMEM_ADD(&part[6][x + 1], b);
+        EAV1_SMEM_ADD(&part[7][(y >> 1) + x], a);      EAV1_SMEM_ADD(&part[7][(y >> 1) + x + 1], b);
+    }
+}
+
+EAV1_DEV void cdef_dir_cost(const int32_t *part, int n, int32_t *cost)
+{
     const int div_table[7] = { 840, 420, 280, 210, 168, 140, 120 };
     unsigned c = 0;
     if (n == 2 || n == 6) {
@@ -263,7 +278,7 @@ EAV1_DEV void cdef_dir_cost(const int16_t *tile, int bd8, int n, int32_t *cost)
 template <typename pixel>
 EAV1_DEV void cdef_block(const PfParams &pp, int bx, int by, bool valid, CdefSmem &sm, int tid, int nthr)
 {
-    if (!valid) { CTA_SYNC(); CTA_SYNC(); CTA_SYNC(); return; } // keep barrier count equal across groups
+    if (!valid) { CTA_SYNC(); CTA_SYNC(); CTA_SYNC(); CTA_SYNC(); return; } // keep barrier count equal across groups
     const int bd8 = (32 - clz32((unsigned)pp.bitdepth_max)) - 8;
     const int has_chroma = pp.layout != 0;
     const int cw = 8 >> pp.ss_hor, chh = 8 >> pp.ss_ver;
@@ -288,6 +303,7 @@ EAV1_DEV void cdef_block(const PfParams &pp, int bx, int by, bool valid, CdefSme
     const int damping = pp.cdef_damping + bd8;
 
     if (active) {
+        for (int i = tid; i < 8 * 16; i += nthr) (&sm.part[0][0])[i] = 0;
         cdef_load<pixel>(pp.a[0], lx, ly, 8, 8, edges, sm.tile[0], tid, nthr);
         if (has_chroma && uv_lvl) {
             cdef_load<pixel>(pp.a[1], cx, cy, cw, chh, edges, sm.tile[1], tid, nthr);
@@ -296,8 +312,10 @@ EAV1_DEV void cdef_block(const PfParams &pp, int bx, int by, bool valid, CdefSme
     }
     CTA_SYNC();
     const bool need_dir = active && (y_pri || uv_pri);
+    if (need_dir) cdef_dir_partial(sm.tile[0], bd8, sm.part, tid, nthr);
+    CTA_SYNC();
     if (need_dir)
-        for (int n = tid; n < 8; n += nthr) cdef_dir_cost(sm.tile[0], bd8, n, sm.cost);
+        for (int n = tid; n < 8; n += nthr) cdef_dir_cost(sm.part[n], n, sm.cost);
     CTA_SYNC();
     if (need_dir && tid == 0) {
         int best = 0;

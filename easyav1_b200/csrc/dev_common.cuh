@@ -99,6 +99,21 @@ EAV1_DEV int clz32(unsigned v) {
 }
 EAV1_DEV int ulog2(unsigned v) { return 31 - clz32(v); }
 
+// i / d for many i and one small runtime divisor: one real division per loop (the magic number),
+// a multiply-high per element. Exact for d <= 1024 and i < 2^22 (error term i * (magic*d - 2^32) < 2^32).
+struct FastDiv {
+    unsigned magic, d;
+    EAV1_DEVM explicit FastDiv(int dd) : magic((unsigned)((0x100000000ull + (unsigned)dd - 1) / (unsigned)dd)), d((unsigned)dd) {}
+    EAV1_DEVM int div(int i) const {
+        if (d == 1) return i;
+#if defined(__CUDA_ARCH__)
+        return (int)__umulhi((unsigned)i, magic);
+#else
+        return (int)(((unsigned long long)(unsigned)i * magic) >> 32);
+#endif
+    }
+};
+
 // Bit-depth traits: pixel / coefficient types and the multiply width the inverse
 // transforms need (see itx.cuh).
 struct BD8 {

@@ -461,8 +461,9 @@ EAV1_DEV void comp_blend3(typename BD::pixel *dst, int dstride, const int16_t *t
             store4_any(dst + y * dstride + x, o);
         }
     } else {
+        const FastDiv fd_w(w);
         for (int i = tid; i < w * h; i += nthr) {
-            const int y = i / w, x = i - y * w;
+            const int y = fd_w.div(i), x = i - y * w;
             int v;
             if (MODE == 0) v = t1[i] + t2[i];
             else if (MODE == 1) v = t1[i] * weight + t2[i] * (16 - weight);
@@ -506,8 +507,9 @@ EAV1_DEV void comp_w_mask(typename BD::pixel *dst, int dstride, const int16_t *t
     const int mask_sh = bitdepth + ib - 4, mask_rnd = 1 << (mask_sh - 5);
     // one work item per mask sample (covers 1, 2 or 4 pixels)
     const int mw = w >> ss_hor, mh = h >> ss_ver;
+    const FastDiv fd_mw(mw);
     for (int i = tid; i < mw * mh; i += nthr) {
-        const int myy = i / mw, mxx = i - myy * mw;
+        const int myy = fd_mw.div(i), mxx = i - myy * mw;
         int msum = 0;
         for (int yy = 0; yy <= ss_ver; yy++)
             for (int xx = 0; xx <= ss_hor; xx++) {
@@ -528,8 +530,9 @@ EAV1_DEV void comp_w_mask(typename BD::pixel *dst, int dstride, const int16_t *t
 template <typename pixel>
 EAV1_DEV void blend_mask(pixel *dst, int dstride, const pixel *tmp, int w, int h, const uint8_t *mask, int tid, int nthr)
 {
+    const FastDiv fd_w(w);
     for (int i = tid; i < w * h; i += nthr) {
-        const int y = i / w, x = i - y * w;
+        const int y = fd_w.div(i), x = i - y * w;
         const int m = mask[i], a = dst[y * dstride + x], b = tmp[i];
         dst[y * dstride + x] = (pixel)((a * (64 - m) + b * m + 32) >> 6);
     }
@@ -541,8 +544,9 @@ EAV1_DEV void blend_v(const Eav1Tables *tab, pixel *dst, int dstride, const pixe
 {
     const uint8_t *mask = &tab->obmc_masks[w];
     const int ww = (w * 3) >> 2;
+    const FastDiv fd_ww(ww);
     for (int i = tid; i < ww * h; i += nthr) {
-        const int y = i / ww, x = i - y * ww;
+        const int y = fd_ww.div(i), x = i - y * ww;
         const int m = mask[x], a = dst[y * dstride + x], b = tmp[y * w + x];
         dst[y * dstride + x] = (pixel)((a * (64 - m) + b * m + 32) >> 6);
     }
@@ -554,8 +558,9 @@ EAV1_DEV void blend_h(const Eav1Tables *tab, pixel *dst, int dstride, const pixe
 {
     const uint8_t *mask = &tab->obmc_masks[h];
     const int hh = (h * 3) >> 2;
+    const FastDiv fd_w(w);
     for (int i = tid; i < w * hh; i += nthr) {
-        const int y = i / w, x = i - y * w;
+        const int y = fd_w.div(i), x = i - y * w;
         const int m = mask[y], a = dst[y * dstride + x], b = tmp[y * w + x];
         dst[y * dstride + x] = (pixel)((a * (64 - m) + b * m + 32) >> 6);
     }

@@ -161,8 +161,9 @@ EAV1_DEV int cdef_constrain(int diff, int threshold, int shift) {
 template <typename pixel>
 EAV1_DEV void cdef_load(const Plane &pl, int x0, int y0, int w, int h, int edges, int16_t *tile, int tid, int nthr)
 {
+    const FastDiv fd(w + 4);
     for (int i = tid; i < (w + 4) * (h + 4); i += nthr) {
-        const int ty = i / (w + 4), tx = i - ty * (w + 4);
+        const int ty = fd.div(i), tx = i - ty * (w + 4);
         const int x = tx - 2, y = ty - 2;
         const bool ok = (x >= 0 || (edges & 1)) && (x < w || (edges & 2)) && (y >= 0 || (edges & 4)) && (y < h || (edges & 8));
         tile[ty * 12 + tx] = ok ? (int16_t)*px_at<pixel>(pl, x0 + x, y0 + y) : (int16_t)-32768;
@@ -382,8 +383,9 @@ EAV1_DEV void lr_load(const PfParams &pp, const Eav1LrRec &r, int x0, int tw, ui
     const int ss_ver = r.plane ? pp.ss_ver : 0;
     const int ph = (pp.h + ss_ver) >> ss_ver;
     const int W = tw + 6, H = r.h + 6;
+    const FastDiv fdW(W);
     for (int i = tid; i < W * H; i += nthr) {
-        const int ty = i / W, tx = i - ty * W;
+        const int ty = fdW.div(i), tx = i - ty * W;
         const int ry = ty - 3;
         int cx = x0 + tx - 3;
         if (cx < 0 && !(r.edges & 1)) cx = 0;
@@ -410,8 +412,9 @@ EAV1_DEV void lr_wiener_tile(const PfParams &pp, const Eav1LrRec &r, int x0, int
     const int W = tw + 6, H = r.h + 6;
     lr_load<pixel>(pp, r, x0, tw, sm.in, tid, nthr);
     CTA_SYNC();
+    const FastDiv fdt(tw);
     for (int i = tid; i < H * tw; i += nthr) {
-        const int ty = i / tw, x = i - ty * tw;
+        const int ty = fdt.div(i), x = i - ty * tw;
         const uint16_t *row = sm.in + ty * W + x;
         int sum = 1 << (bitdepth + 6);
         if (sizeof(pixel) == 1) sum += row[3] * 128;
@@ -421,7 +424,7 @@ EAV1_DEV void lr_wiener_tile(const PfParams &pp, const Eav1LrRec &r, int x0, int
     CTA_SYNC();
     const Plane &P = pp.p[r.plane];
     for (int i = tid; i < r.h * tw; i += nthr) {
-        const int y = i / tw, x = i - y * tw;
+        const int y = fdt.div(i), x = i - y * tw;
         int sum = -(1 << (bitdepth + (rb_v - 1)));
         for (int k = 0; k < 7; k++) sum += sm.hor[(y + k) * LR_TW + x] * r.p.filter[1][k];
         *px_at<pixel>(P, r.x + x0 + x, r.y + y) = (pixel)iclip((sum + (1 << (rb_v - 1))) >> rb_v, 0, pp.bitdepth_max);
@@ -458,21 +461,22 @@ EAV1_DEV void lr_sgr_tile(const PfParams &pp, const Eav1LrRec &r, int x0, int tw
     const bool do5 = r.kind != EAV1_LR_SGR_3X3, do3 = r.kind != EAV1_LR_SGR_5X5;
     lr_load<pixel>(pp, r, x0, tw, sm.in, tid, nthr);
     CTA_SYNC();
+    const FastDiv fdS(SW), fdt(tw);
     if (do3)
         for (int i = tid; i < (h + 2) * SW; i += nthr) {
-            const int ty = i / SW, tx = i - ty * SW;
+            const int ty = fdS.div(i), tx = i - ty * SW;
             sgr_ab(pp, sm.in, W, tx - 1, ty - 1, 1, (int)r.p.sgr.s1, &sm.s.a3[i], &sm.s.b3[i]);
         }
     const int n5 = (h + 1) / 2 + 1; // rows -1, 1, 3, ...
     if (do5)
         for (int i = tid; i < n5 * SW; i += nthr) {
-            const int ty = i / SW, tx = i - ty * SW;
+            const int ty = fdS.div(i), tx = i - ty * SW;
             sgr_ab(pp, sm.in, W, tx - 1, 2 * ty - 1, 2, (int)r.p.sgr.s0, &sm.s.a5[i], &sm.s.b5[i]);
         }
     CTA_SYNC();
     const Plane &P = pp.p[r.plane];
     for (int i = tid; i < h * tw; i += nthr) {
-        const int y = i / tw, x = i - y * tw;
+        const int y = fdt.div(i), x = i - y * tw;
         const int src = sm.in[(y + 3) * W + x + 3];
         int t3 = 0, t5 = 0;
         if (do3) {

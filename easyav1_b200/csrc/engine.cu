@@ -112,7 +112,10 @@ __device__ __forceinline__ void recon_worker(const FrameCtx &fc, const ReconArgs
         for (uint32_t d = tid; d < nd; d += nthr) {
             const uint32_t *flag = &ra.done[ra.deps[d0 + d]];
             unsigned ns = 20;
-            while (ld_acquire(flag) != ra.epoch) { __nanosleep(ns); if (ns < 320) ns <<= 1; }
+#ifndef EAV1_POLL_MAX_NS
+#define EAV1_POLL_MAX_NS 320
+#endif
+            while (ld_acquire(flag) != ra.epoch) { if (EAV1_POLL_MAX_NS) { __nanosleep(ns); if (ns < EAV1_POLL_MAX_NS) ns <<= 1; } }
         }
         CTA_SYNC();
         if (ra.trace && tid == 0) {
@@ -162,7 +165,11 @@ __device__ __forceinline__ void recon_worker(const FrameCtx &fc, const ReconArgs
             t[4] = ((unsigned long long)first << 32) | count; t[5] = ((unsigned long long)k << 32) | (blockIdx.x << 8) | (nthr == 32 ? (threadIdx.x >> 5) : 255u);
         }
         if (fed && tid == 0) {   // nobody polls the flag of a unit without consumers
+            // release at gpu scope: the group barrier after the unit's last command orders every
+            // thread's stores before this one (cumulativity), so no separate fence is needed
+#ifdef EAV1_EXTRA_FENCE
             __threadfence();
+#endif
             st_release(&ra.done[id], ra.epoch);
         }
     }

@@ -148,16 +148,18 @@ EAV1_EXEC_LINK int exec_cmd(const FrameCtx &fc, const Eav1Cmd &c, CtaScratch &sm
         break;
     case EAV1_OP_IPRED:
         PROF_MARK(1);
-        build_edge<pixel>(fc.cur[c.plane], c, bdmax, sm.ip.edge, tid, nthr);
-        PROF_MARK(2);
         {
             // the residual add of the same transform block follows: finish the block here
             const bool fused = next && next->op == EAV1_OP_ITX && (next->flags & EAV1_F_RESID) && next->plane == c.plane &&
                                next->x == c.x && next->y == c.y && next->w == c.w && next->h == c.h &&
                                !(c.flags & EAV1_F_DST_ARENA);
             const int16_t *res = fused ? (const int16_t *)(fc.arena + next->dst_off) : nullptr;
+            uint2 res_pre = uint2();
+            if (fused && tid < ((c.w * c.h) >> 2)) res_pre = *reinterpret_cast<const uint2 *>(res + (tid << 2));
+            build_edge<pixel>(fc.cur[c.plane], c, bdmax, sm.ip.edge, tid, nthr);
+            PROF_MARK(2);
             const bool added = ipred_block<pixel>(fc.tab, dst8, dstride, sm.ip.edge, sm.ip.edge2, c.u.ipred.mode, c.w, c.h,
-                                                  c.u.ipred.angle, c.u.ipred.max_w, c.u.ipred.max_h, bdmax, tid, nthr, res);
+                                                  c.u.ipred.angle, c.u.ipred.max_w, c.u.ipred.max_h, bdmax, tid, nthr, res, res_pre);
             if (fused && !added) res_add<BD>(dst8, dstride, res, c.w, c.h, bdmax, tid, nthr);
             PROF_MARK(3);
             if (fused) return 2;

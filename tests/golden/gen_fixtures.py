@@ -190,6 +190,9 @@ CLIPS = {
     # 10-bit 4:2:0 (the BITDEPTH=16 template of every kernel); encoded through OpenCV (depth key)
     "cif_10bit": (352, 288, 6, 31, {"depth": 10}, 60, 4, 8.0),
     "c4_720p_10bit": (1280, 720, 4, 32, {"depth": 10}, 60, 6, 6.0),
+    # config C4's frame size (BASELINE.json configs[3]): 3840x2160 10-bit 4:2:0, a few frames, low noise
+    # so the file stays small (the OpenCV writer exposes neither film grain nor tool switches)
+    "c4_2160p_10bit": (3840, 2160, 3, 33, {"depth": 10}, 30, 8, 0.7),
     # film grain (aom's built-in parameter sets 1 and 15 = many scaling points without block overlap /
     # chroma scaled from luma; and a grain table the encoder estimated itself from the noisy source)
     "cif_grain_t1": (352, 288, 4, 41, {"film-grain-test": "1"}, 60, 6, 6.0),

@@ -8,7 +8,7 @@ import pytest
 from tests.conftest import fixture_obu
 
 CLIPS = ["intra_64x64_nofilt", "cif_intra", "cif_inter", "cif_tools_s4", "cif_tools_s2", "c1_360p", "c2_1080p",
-         "cif_10bit", "c4_720p_10bit",
+         "cif_10bit", "c4_720p_10bit", "c4_2160p_10bit",
          "cif_grain_t1", "cif_grain_t15", "cif_grain_est", "cif_444", "cif_422", "cif_400", "qcif_lossless", "cif_screen"]
 
 

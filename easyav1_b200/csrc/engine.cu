@@ -397,6 +397,7 @@ struct Eav1cuCtx {
     std::vector<uint32_t> est_tmp, order_tmp, bucket_tmp, ritem_tmp, tail_tmp, order2_tmp;
     std::vector<Eav1Cmd> cmd_tmp;
     unsigned long long *d_trace = nullptr;   // set only inside eav1cu_staged_trace
+    int est_weight = 8;           // ticket key = est_weight * est - tail (EAV1_EST_WEIGHT; any weight >= 1 keeps the order topological)
     bool serial_phase1 = false;   // EAV1_SERIAL_PHASE1: residuals on the main stream (profiling, debugging)
     int warp_mode = 0;   // 0: every chain on a CTA, 1: independent small chains on warps, 2: all small chains on warps
     int err = 0;
@@ -540,6 +541,7 @@ int eav1cu_ctx_create(Eav1cuCtx **out, int device)
     }
     if (const char *e = getenv("EAV1_WARP_MODE")) ctx->warp_mode = atoi(e);
     ctx->serial_phase1 = getenv("EAV1_SERIAL_PHASE1") != nullptr;
+    if (const char *e = getenv("EAV1_EST_WEIGHT")) ctx->est_weight = std::max(1, std::min(16, atoi(e)));
     if (!ctx->stream2) {
         if (cudaStreamCreateWithFlags(&ctx->stream2, cudaStreamNonBlocking) != cudaSuccess ||
             cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming) != cudaSuccess ||
@@ -914,39 +916,37 @@ static int plan_build(Eav1cuCtx *ctx, FramePlan &pl, bool staged, const Eav1Fram
             rt.resize(nc);
             size_t nb = 0;
             double px_big = 0, px_small = 0;
-            // Ticket order = earliest possible start (longest producer path, weighted by command
-            // count), ties in decode order. Any order in which producers precede consumers keeps
-            // the progress argument of recon_frame_kernel; this one makes the tickets held at any
-            // moment the frame's current wavefront instead of one stretch of superblock rows.
+            // Ticket order (key = w * est - tail, w = est_weight; the text below argues for w = 1, larger w
+            // only leans further towards the earliest-start order). est = earliest possible start (longest producer path, in commands),
+            // tail = longest chain of consumers behind the unit (itself included). Tickets go by
+            // est - tail, ties in decode order. For a producer p of c: est[c] >= est[p] + n[p] and
+            // tail[p] >= tail[c] + n[p], so the key strictly grows along every edge: producers
+            // precede consumers and a group only ever waits for smaller tickets (progress for any
+            // grid size). Among the orders with that property this one hands out the frame's current
+            // wavefront, critical chains first: units on the longest path (est + tail maximal) lead
+            // their level, and the many independent units (est 0, tail 1) fill in behind the heads of
+            // the chains instead of in front of their second units.
             std::vector<uint32_t> &est = ctx->est_tmp, &order = ctx->order_tmp, &bucket = ctx->bucket_tmp;
-            est.resize(nc); order.resize(nc);
-            uint32_t est_max = 0;
+            std::vector<uint32_t> &tail = ctx->tail_tmp;
+            est.resize(nc); order.resize(nc); tail.assign(nc, 0);
+            uint32_t est_max = 0, tail_max = 0;
             for (size_t u = 0; u < nc; u++) {
                 uint32_t e = 0;
                 for (uint32_t d = g.dep_start[u]; d < g.dep_start[u + 1]; d++)
                     e = std::max(e, est[g.deps[d]] + g.unit_cnt[g.deps[d]]);
                 est[u] = e; est_max = std::max(est_max, e);
             }
-            // Among units that can start at the same time, the one with the longest chain of
-            // consumers behind it goes first (list-scheduling priority): two stable counting sorts,
-            // by descending tail, then by ascending earliest start.
-            std::vector<uint32_t> &tail = ctx->tail_tmp, &tmp = ctx->order2_tmp;
-            tail.assign(nc, 0); tmp.resize(nc);
-            uint32_t tail_max = 0;
             for (size_t u = nc; u-- > 0;) {
                 tail[u] += g.unit_cnt[u];
                 tail_max = std::max(tail_max, tail[u]);
                 for (uint32_t d = g.dep_start[u]; d < g.dep_start[u + 1]; d++)
                     tail[g.deps[d]] = std::max(tail[g.deps[d]], tail[u]);
             }
-            bucket.assign((size_t)tail_max + 2, 0);
-            for (size_t u = 0; u < nc; u++) bucket[tail_max - tail[u] + 1]++;
+            const uint32_t ew = (uint32_t)ctx->est_weight;
+            bucket.assign((size_t)ew * est_max + tail_max + 2, 0);
+            for (size_t u = 0; u < nc; u++) bucket[ew * est[u] + tail_max - tail[u] + 1]++;
             for (size_t b = 1; b < bucket.size(); b++) bucket[b] += bucket[b - 1];
-            for (size_t u = 0; u < nc; u++) tmp[bucket[tail_max - tail[u]]++] = (uint32_t)u;
-            bucket.assign((size_t)est_max + 2, 0);
-            for (size_t u = 0; u < nc; u++) bucket[est[u] + 1]++;
-            for (size_t b = 1; b < bucket.size(); b++) bucket[b] += bucket[b - 1];
-            for (size_t i = 0; i < nc; i++) { const uint32_t u = tmp[i]; order[bucket[est[u]]++] = u; }
+            for (size_t u = 0; u < nc; u++) order[bucket[ew * est[u] + tail_max - tail[u]]++] = (uint32_t)u;
             for (int pass = 0; pass < 2; pass++) {
                 size_t pos = pass ? nb : 0;
                 for (size_t oi = 0; oi < nc; oi++) {

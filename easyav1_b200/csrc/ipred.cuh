@@ -196,11 +196,12 @@ EAV1_DEV unsigned edge_sum(const uint16_t *p, int step, int n, int tid, int nthr
 // Predict a w x h block into dst (stride in pixels) from the edge array (edge[EDGE_C] = top-left).
 // edge2 is scratch of the same size.
 // With `res` (row-major int16 residual of the same block) the sum prediction + residual is written in
-// one go; returns whether it did so (filter-intra predicts from its own output and cannot).
+// one go; returns whether it did so. `tile` is shared scratch for a 32x32 block (filter-intra).
 template <typename pixel>
 EAV1_DEV bool ipred_block(const Eav1Tables *tab, pixel *dst, int stride, uint16_t *edge, uint16_t *edge2,
                           int mode, int w, int h, int angle_in, int max_w, int max_h,
-                          int bitdepth_max, int tid, int nthr, const int16_t *res = nullptr, uint2 res_pre = uint2())
+                          int bitdepth_max, int tid, int nthr, uint16_t *tile, const int16_t *res = nullptr,
+                          uint2 res_pre = uint2())
 {
     const uint16_t *E = edge + EDGE_C;
     // w and h are powers of two >= 4: samples are handled four to a thread, i4 -> (y, x = 4*(i4 & m4))
@@ -394,9 +395,18 @@ EAV1_DEV bool ipred_block(const Eav1Tables *tab, pixel *dst, int stride, uint16_
         break;
     }
     default: { // IP_FILTER: 4x2 cells, cell (cx,cy) needs (cx-1,cy), (cx,cy-1), (cx-1,cy-1)
-        res = nullptr;
+        // The cells predict from each other, so the block is built in shared memory (one
+        // anti-diagonal of cells per step) and written out once, residual included.
         const int8_t (*taps)[8] = tab->filter_intra_taps[angle_in & 511];
         const int cw = w >> 2, ch = h >> 1;
+        uint16_t *T = tile;   // w x h, stride w (filter-intra blocks are at most 32x32)
+        // the 8 x 7 taps as sixteen words (tap 7 of every row is zero padding)
+        uint32_t tw[16];
+        if (tid < ch || nthr == 1) {
+            const uint32_t *tp = reinterpret_cast<const uint32_t *>(&taps[0][0]);
+#pragma unroll
+            for (int k = 0; k < 16; k++) tw[k] = tp[k];
+        }
         for (int d = 0; d < cw + ch - 1; d++) {
             for (int cy = tid; cy < ch; cy += nthr) {
                 const int cx = d - cy;
@@ -405,18 +415,25 @@ EAV1_DEV bool ipred_block(const Eav1Tables *tab, pixel *dst, int stride, uint16_
                 int p[7];
                 if (cy == 0) { p[0] = E[x0]; for (int k = 0; k < 4; k++) p[1 + k] = E[1 + x0 + k]; }
                 else {
-                    p[0] = x0 ? dst[(y0 - 1) * stride + x0 - 1] : E[-y0];
-                    for (int k = 0; k < 4; k++) p[1 + k] = dst[(y0 - 1) * stride + x0 + k];
+                    p[0] = x0 ? T[(y0 - 1) * w + x0 - 1] : E[-y0];
+                    for (int k = 0; k < 4; k++) p[1 + k] = T[(y0 - 1) * w + x0 + k];
                 }
                 if (cx == 0) { p[5] = E[-(1 + y0)]; p[6] = E[-(2 + y0)]; }
-                else { p[5] = dst[y0 * stride + x0 - 1]; p[6] = dst[(y0 + 1) * stride + x0 - 1]; }
+                else { p[5] = T[y0 * w + x0 - 1]; p[6] = T[(y0 + 1) * w + x0 - 1]; }
+#pragma unroll
                 for (int k = 0; k < 8; k++) {
                     int acc = 0;
-                    for (int j = 0; j < 7; j++) acc += taps[k][j] * p[j];
-                    dst[(y0 + (k >> 2)) * stride + x0 + (k & 3)] = (pixel)iclip((acc + 8) >> 4, 0, bitdepth_max);
+#pragma unroll
+                    for (int j = 0; j < 7; j++) acc += (int)(int8_t)((tw[2 * k + (j >> 2)] >> (8 * (j & 3))) & 0xff) * p[j];
+                    T[(y0 + (k >> 2)) * w + x0 + (k & 3)] = (uint16_t)iclip((acc + 8) >> 4, 0, bitdepth_max);
                 }
             }
             CTA_SYNC();
+        }
+        for (int i = tid; i < n4; i += nthr) {
+            const uint16_t *t = T + (i << 2);
+            store4r<pixel>(dst + (i >> lw4) * stride + ((i & m4) << 2), t[0], t[1], t[2], t[3],
+                           res ? res + (i << 2) : nullptr, bitdepth_max, i == tid, res_pre);
         }
         break;
     }

@@ -56,6 +56,28 @@ def measured_peak():
     return 6550.0, "B200_PROFILING.md fallback"
 
 
+def ncu_traffic(kernel_name):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of `kernel_name`, from the newest committed
+    `ncu --set full` summary under profiles/ (tools/profile_round.sh writes it); None if there is none.
+    It is a profiler figure (cold cache, serialised launches), reported beside the live numbers."""
+    import glob
+    best = None
+    for path in sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_full_summary.json"))):
+        try:
+            d = json.load(open(path))
+        except Exception:
+            continue
+        for k, v in d.items():
+            if kernel_name in k:
+                rd = [x for n, x in v.items() if n.startswith("dram__bytes_read.sum")]
+                wr = [x for n, x in v.items() if n.startswith("dram__bytes_write.sum")]
+                unit = [n for n in v if n.startswith("dram__bytes_read.sum")]
+                if rd and wr and unit:
+                    scale = 1e6 if "Mbyte" in unit[0] else 1e3 if "Kbyte" in unit[0] else 1e9 if "Gbyte" in unit[0] else 1.0
+                    best = {"bytes_per_launch": int((rd[0] + wr[0]) * scale), "source": os.path.basename(path)}
+    return best
+
+
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
@@ -362,7 +384,10 @@ def run_ours(args, man, obu):
                    "step": "one pass over the %d-frame stream" % n_frames,
                    "l2": "256 MiB flush write between timed steps", "streams_per_gpu": 1},
         "roofline": {"bound": "hbm", "kernel": names[dom], "achieved": round(achieved, 2), "peak": peak,
-                     "unit": "GB/s", "frac": round(achieved / peak, 5), "traffic": None, "peak_source": peak_src,
+                     "unit": "GB/s", "frac": round(achieved / peak, 5),
+                     "traffic": (ncu_traffic(names[dom].split(" ")[0]) or {}).get("bytes_per_launch"),
+                     "traffic_source": (ncu_traffic(names[dom].split(" ")[0]) or {}).get("source"),
+                     "peak_source": peak_src,
                      "alg_bytes_per_launch": int(tot_bytes[dom] / max(1, calls[dom] // args.steps)),
                      "whole_frame_gbs": round((all_bytes / 1e9) / (dev_ms / args.steps / 1e3), 2),
                      "stages": stages},

@@ -105,6 +105,8 @@ int eav1cu_pic_release(Eav1cuCtx *c, int id) { c->pics[id].used = false; return 
 
 static int pic_copy(Eav1cuCtx *c, int id, void *const data[3], const ptrdiff_t stride[2], bool up)
 {
+    static const bool null_engine = getenv("EAV1_EMU_NULL") && atoi(getenv("EAV1_EMU_NULL")) > 1;
+    if (null_engine) return 0;   // host-cost profiling, level 2: no picture traffic either
     Picture &p = c->pics[id];
     const int hbd = p.bpc > 8, ss_hor = p.layout != 3, ss_ver = p.layout == 1;
     for (int pl = 0; pl < (p.layout ? 3 : 1); pl++) {

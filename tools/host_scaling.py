@@ -20,7 +20,7 @@ for thr in (1, 2, 4, 8, 16, 32):
     print("reference n_threads=%d: %.1f fps" % (thr, n / dt))
 emu = os.path.join(ROOT, "tests/emu/libdav1d_b200_emu.so")
 if os.path.exists(emu):
-    os.environ["EAV1_EMU_NULL"] = "1"
+    os.environ.setdefault("EAV1_EMU_NULL", "1")   # 2: no picture copies either
     from easyav1_b200.lib import _bind_host, StreamFrame
     host = _bind_host(C.CDLL(emu, mode=C.RTLD_GLOBAL))
     buf = C.create_string_buffer(cap)

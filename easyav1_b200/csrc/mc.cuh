@@ -187,6 +187,7 @@ EAV1_DEVN void mc_block8_fast(const Eav1Tables *tab, const SrcView<uint8_t> &src
     } else {
         for (int y0 = 0; y0 < h; y0 += 32) {
             const int th = imin(32, h - y0);
+#pragma unroll 2
             for (int it = tid; it < ((th + 7) << lq); it += nthr) {
                 const int r = it >> lq, x = (it & qmask) << 2;
                 int sum[4];
@@ -196,6 +197,7 @@ EAV1_DEVN void mc_block8_fast(const Eav1Tables *tab, const SrcView<uint8_t> &src
                 store4_i16(mid + r * w + x, sum);
             }
             CTA_SYNC();
+#pragma unroll 2
             for (int it = tid; it < (th << lq); it += nthr) {
                 const int r = it >> lq, x = (it & qmask) << 2;
                 int sum[4] = { 0, 0, 0, 0 };

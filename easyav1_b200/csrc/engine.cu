@@ -916,37 +916,8 @@ static int plan_build(Eav1cuCtx *ctx, FramePlan &pl, bool staged, const Eav1Fram
             rt.resize(nc);
             size_t nb = 0;
             double px_big = 0, px_small = 0;
-            // Ticket order (key = w * est - tail, w = est_weight; the text below argues for w = 1, larger w
-            // only leans further towards the earliest-start order). est = earliest possible start (longest producer path, in commands),
-            // tail = longest chain of consumers behind the unit (itself included). Tickets go by
-            // est - tail, ties in decode order. For a producer p of c: est[c] >= est[p] + n[p] and
-            // tail[p] >= tail[c] + n[p], so the key strictly grows along every edge: producers
-            // precede consumers and a group only ever waits for smaller tickets (progress for any
-            // grid size). Among the orders with that property this one hands out the frame's current
-            // wavefront, critical chains first: units on the longest path (est + tail maximal) lead
-            // their level, and the many independent units (est 0, tail 1) fill in behind the heads of
-            // the chains instead of in front of their second units.
-            std::vector<uint32_t> &est = ctx->est_tmp, &order = ctx->order_tmp, &bucket = ctx->bucket_tmp;
-            std::vector<uint32_t> &tail = ctx->tail_tmp;
-            est.resize(nc); order.resize(nc); tail.assign(nc, 0);
-            uint32_t est_max = 0, tail_max = 0;
-            for (size_t u = 0; u < nc; u++) {
-                uint32_t e = 0;
-                for (uint32_t d = g.dep_start[u]; d < g.dep_start[u + 1]; d++)
-                    e = std::max(e, est[g.deps[d]] + g.unit_cnt[g.deps[d]]);
-                est[u] = e; est_max = std::max(est_max, e);
-            }
-            for (size_t u = nc; u-- > 0;) {
-                tail[u] += g.unit_cnt[u];
-                tail_max = std::max(tail_max, tail[u]);
-                for (uint32_t d = g.dep_start[u]; d < g.dep_start[u + 1]; d++)
-                    tail[g.deps[d]] = std::max(tail[g.deps[d]], tail[u]);
-            }
-            const uint32_t ew = (uint32_t)ctx->est_weight;
-            bucket.assign((size_t)ew * est_max + tail_max + 2, 0);
-            for (size_t u = 0; u < nc; u++) bucket[ew * est[u] + tail_max - tail[u] + 1]++;
-            for (size_t b = 1; b < bucket.size(); b++) bucket[b] += bucket[b - 1];
-            for (size_t u = 0; u < nc; u++) order[bucket[ew * est[u] + tail_max - tail[u]]++] = (uint32_t)u;
+            std::vector<uint32_t> &order = ctx->order_tmp;
+            Scheduler::ticket_order(g, (uint32_t)ctx->est_weight, order, ctx->est_tmp, ctx->tail_tmp, ctx->bucket_tmp);
             for (int pass = 0; pass < 2; pass++) {
                 size_t pos = pass ? nb : 0;
                 for (size_t oi = 0; oi < nc; oi++) {
@@ -1248,6 +1219,28 @@ int eav1cu_plan_units(const Eav1Cmd *cmds, size_t n_cmds, const int plane_w[3], 
     for (size_t i = 0; i < g.mc_items.size() && i < cap_items; i++) if (mc_items) mc_items[i] = g.mc_items[i];
     if (n_items) *n_items = g.mc_items.size();
     return (int)g.unit_cmd.size();
+}
+
+/* The order in which the dataflow kernel hands out the units of eav1cu_plan_units (ticket t runs
+ * unit order[t]) and the producer lists it waits on (CSR: dep_start has n+1 entries). No GPU needed. */
+int eav1cu_plan_tickets(const Eav1Cmd *cmds, size_t n_cmds, const int plane_w[3], const int plane_h[3],
+                        int est_weight, uint32_t *order, size_t cap_units, uint32_t *dep_start,
+                        uint32_t *deps, size_t cap_deps, size_t *n_deps)
+{
+    if (!cmds || !plane_w || !plane_h || est_weight < 1) return EAV1CU_ERR_INVAL;
+    Scheduler sc;
+    UnitGraph g;
+    sc.reset(plane_w, plane_h);
+    sc.build_units(cmds, n_cmds, g);
+    std::vector<uint32_t> ord, est, tail, bucket;
+    Scheduler::ticket_order(g, (uint32_t)est_weight, ord, est, tail, bucket);
+    const size_t n = g.unit_cmd.size();
+    if (n > cap_units || g.deps.size() > cap_deps) return EAV1CU_ERR_INVAL;
+    for (size_t u = 0; u < n; u++) { if (order) order[u] = ord[u]; if (dep_start) dep_start[u] = g.dep_start[u]; }
+    if (dep_start) dep_start[n] = g.dep_start[n];
+    for (size_t i = 0; i < g.deps.size(); i++) if (deps) deps[i] = g.deps[i];
+    if (n_deps) *n_deps = g.deps.size();
+    return (int)n;
 }
 
 int eav1cu_counters(Eav1cuCtx *ctx, long long out[4])

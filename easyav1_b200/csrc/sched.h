@@ -155,6 +155,39 @@ public:
         return g.unit_cmd.empty() ? 0 : mx + 1;
     }
 
+    // Ticket order of the dataflow kernel: order[t] = unit that holds ticket t.
+    // est = earliest possible start (longest producer path, in commands), tail = longest chain of
+    // consumers behind the unit (itself included). Tickets go by w * est - tail (w >= 1), ties in decode
+    // order. For a producer p of c: est[c] >= est[p] + n[p] and tail[p] >= tail[c] + n[p], so the key
+    // strictly grows along every edge: producers precede consumers and a work group only ever waits for
+    // smaller tickets (progress for any grid size). Among the orders with that property this one hands
+    // out the frame's current wavefront, critical chains first: units on the longest path (est + tail
+    // maximal) lead their level, and the many independent units (est 0, tail 1) fill in behind the heads
+    // of the chains instead of in front of their second units. Larger w leans towards pure
+    // earliest-start order. Two linear passes and one counting sort.
+    static void ticket_order(const UnitGraph &g, uint32_t w, std::vector<uint32_t> &order, std::vector<uint32_t> &est,
+                             std::vector<uint32_t> &tail, std::vector<uint32_t> &bucket) {
+        const size_t nc = g.unit_cmd.size();
+        est.resize(nc); order.resize(nc); tail.assign(nc, 0);
+        uint32_t est_max = 0, tail_max = 0;
+        for (size_t u = 0; u < nc; u++) {
+            uint32_t e = 0;
+            for (uint32_t d = g.dep_start[u]; d < g.dep_start[u + 1]; d++)
+                e = std::max(e, est[g.deps[d]] + g.unit_cnt[g.deps[d]]);
+            est[u] = e; est_max = std::max(est_max, e);
+        }
+        for (size_t u = nc; u-- > 0;) {
+            tail[u] += g.unit_cnt[u];
+            tail_max = std::max(tail_max, tail[u]);
+            for (uint32_t d = g.dep_start[u]; d < g.dep_start[u + 1]; d++)
+                tail[g.deps[d]] = std::max(tail[g.deps[d]], tail[u]);
+        }
+        bucket.assign((size_t)w * est_max + tail_max + 2, 0);
+        for (size_t u = 0; u < nc; u++) bucket[w * est[u] + tail_max - tail[u] + 1]++;
+        for (size_t b = 1; b < bucket.size(); b++) bucket[b] += bucket[b - 1];
+        for (size_t u = 0; u < nc; u++) order[bucket[w * est[u] + tail_max - tail[u]]++] = (uint32_t)u;
+    }
+
     static void levels(const DepGraph &g, Schedule &out) {
         const size_t nc = g.chains.size();
         std::vector<uint32_t> lvl(nc, 0);

@@ -265,6 +265,11 @@ int  eav1cu_plan_levels(const Eav1Cmd *cmds, size_t n_cmds, const int plane_w[3]
 int  eav1cu_plan_units(const Eav1Cmd *cmds, size_t n_cmds, const int plane_w[3], const int plane_h[3],
                        uint32_t *unit_first, uint32_t *unit_count, uint32_t *unit_level, size_t cap_units,
                        uint32_t *mc_items, size_t cap_items, size_t *n_items);
+/* Ticket order of the dataflow kernel for the units of eav1cu_plan_units (ticket t runs unit order[t]) and
+ * the producer lists (CSR, dep_start has n + 1 entries); est_weight as in csrc/sched.h. Needs no GPU. */
+int  eav1cu_plan_tickets(const Eav1Cmd *cmds, size_t n_cmds, const int plane_w[3], const int plane_h[3],
+                         int est_weight, uint32_t *order, size_t cap_units, uint32_t *dep_start,
+                         uint32_t *deps, size_t cap_deps, size_t *n_deps);
 /* out[0] kernel launches, out[1] host->device bytes, out[2] device->host bytes, out[3] frames */
 int  eav1cu_counters(Eav1cuCtx *ctx, long long out[4]);
 int  eav1cu_set_capture(Eav1cuCtx *ctx, int on);

@@ -112,3 +112,66 @@ def test_mc_over_already_written_cells_is_not_hoisted():
                          cmd("MC", 0, 8, 8, 0, 0, flags=F_HEAD, u=u_mc())])
     assert items == []
     assert len(units) in (1, 2) and sum(u[1] for u in units) == 2
+
+
+def tickets(cmds, w=64, h=64, est_weight=8):
+    E = load_engine()
+    E.eav1cu_plan_tickets.argtypes = [C.c_char_p, C.c_size_t, C.POINTER(C.c_int), C.POINTER(C.c_int), C.c_int,
+                                      C.POINTER(C.c_uint32), C.c_size_t, C.POINTER(C.c_uint32),
+                                      C.POINTER(C.c_uint32), C.c_size_t, C.POINTER(C.c_size_t)]
+    buf = b"".join(cmds)
+    pw = (C.c_int * 3)(w, w // 2, w // 2)
+    ph = (C.c_int * 3)(h, h // 2, h // 2)
+    cap = 4096
+    order, dep_start, deps = (C.c_uint32 * cap)(), (C.c_uint32 * (cap + 1))(), (C.c_uint32 * (8 * cap))()
+    nd = C.c_size_t(0)
+    n = E.eav1cu_plan_tickets(buf, len(cmds), pw, ph, est_weight, order, cap, dep_start, deps, 8 * cap, C.byref(nd))
+    assert n >= 0
+    return [order[i] for i in range(n)], [[deps[k] for k in range(dep_start[u], dep_start[u + 1])] for u in range(n)]
+
+
+def wavefront_frame(rows=6, cols=8, chroma_free=5):
+    """rows x cols intra blocks, each needing its left, top and top-right neighbours (two separate
+    commands per block so nothing fuses across blocks), plus independent chroma blocks"""
+    c = []
+    for r in range(rows):
+        for k in range(cols):
+            have = (1 if k else 0) | (2 if r else 0) | (16 if r and k + 1 < cols else 0)
+            c.append(cmd("IPRED", 0, 8, 8, 8 * k, 8 * r, flags=F_HEAD,
+                         u=u_ipred(8 * k, 8 * r, have=have, n_left=8 if k else 0, n_top=8 if r else 0)))
+            c.append(cmd("ITX", 0, 8, 8, 8 * k, 8 * r))
+    for i in range(chroma_free):
+        c.append(cmd("IPRED", 1, 4, 4, 4 * i, 0, flags=F_HEAD, u=u_ipred(4 * i, 0, have=0)))
+    return c
+
+
+def test_ticket_order_is_a_permutation_and_producers_come_first():
+    """The progress argument of recon_frame_kernel: a unit only waits for smaller tickets."""
+    for weight in (1, 2, 8):
+        order, deps = tickets(wavefront_frame(), est_weight=weight)
+        assert sorted(order) == list(range(len(order)))
+        ticket_of = {u: t for t, u in enumerate(order)}
+        assert any(deps), "the fixture must contain dependent units"
+        for u, prods in enumerate(deps):
+            for p in prods:
+                assert p < u                               # decode order is topological
+                assert ticket_of[p] < ticket_of[u]         # and so is the ticket order
+
+
+def test_ticket_order_leads_with_the_critical_chain():
+    """Independent units must not be queued in front of the second unit of a long chain."""
+    c = []
+    for i in range(40):                                  # 40 independent chroma blocks, recorded first
+        c.append(cmd("IPRED", 1, 4, 4, 4 * (i % 8), 4 * (i // 8), flags=F_HEAD, u=u_ipred(4 * (i % 8), 4 * (i // 8), have=0)))
+    c += wavefront_frame(rows=7, cols=8, chroma_free=0)  # then luma blocks: one dependent run, cut into units of 64 commands
+    order, deps = tickets(c, est_weight=1)
+    linked = set(u for u, d in enumerate(deps) if d) | set(p for d in deps for p in d)
+    assert linked, "the fixture must contain dependent units"
+    free = [u for u in range(len(order)) if u not in linked]
+    assert len(free) >= 40
+    # the head of the chains holds ticket 0, and no independent unit is queued before a unit that still
+    # has more work behind it than in front of it
+    assert order[0] in linked
+    producers = set(p for d in deps for p in d)
+    heads = [u for u in producers if not deps[u]]
+    assert max(order.index(u) for u in heads) < min(order.index(u) for u in free)

@@ -161,6 +161,31 @@ EAV1_DEV int cdef_constrain(int diff, int threshold, int shift) {
 template <typename pixel>
 EAV1_DEV void cdef_load(const Plane &pl, int x0, int y0, int w, int h, int edges, int16_t *tile, int tid, int nthr)
 {
+    if (sizeof(pixel) == 1 && (x0 & 3) == 0) {
+        // 8-bit: aligned 32-bit loads. Row ty covers columns x0-4 .. x0+w+3 in (w+8)/4 words; the first
+        // word is skipped at the left frame edge (it would lie before the row), rows outside the frame
+        // are never touched.
+        const int nw = (w + 8) >> 2, lnw = nw == 4 ? 2 : 0;   // 4 words (w = 8) or 3 (w = 4)
+        const int items = (h + 4) * nw;
+        const FastDiv fd(nw);
+        for (int i = tid; i < items; i += nthr) {
+            const int ty = lnw ? i >> lnw : fd.div(i), wi = i - ty * nw;
+            const int y = ty - 2;
+            const bool row_ok = (y >= 0 || (edges & 4)) && (y < h || (edges & 8));
+            // the last word holds only right neighbours: never read past the frame's last column
+            const bool word_ok = row_ok && (wi > 0 || (edges & 1)) && (wi < nw - 1 || (edges & 2));
+            uint32_t v = 0;
+            if (word_ok) v = *reinterpret_cast<const uint32_t *>(pl.p + (ptrdiff_t)(y0 + y) * pl.stride + x0 - 4 + 4 * wi);
+#pragma unroll
+            for (int b = 0; b < 4; b++) {
+                const int tx = 4 * wi + b - 2, x = tx - 2;
+                if (tx < 0 || tx >= w + 4) continue;
+                const bool ok = row_ok && (x >= 0 || (edges & 1)) && (x < w || (edges & 2));
+                tile[ty * 12 + tx] = ok ? (int16_t)((v >> (8 * b)) & 0xff) : (int16_t)-32768;
+            }
+        }
+        return;
+    }
     const FastDiv fd(w + 4);
     for (int i = tid; i < (w + 4) * (h + 4); i += nthr) {
         const int ty = fd.div(i), tx = i - ty * (w + 4);
@@ -170,9 +195,12 @@ EAV1_DEV void cdef_load(const Plane &pl, int x0, int y0, int w, int h, int edges
     }
 }
 
+// Filters the w x h block of one plane, or of two planes with identical parameters at once (the two
+// chroma planes: 2 x 16 samples of a 4:2:0 block keep a whole warp busy instead of half of it).
 template <typename pixel>
 EAV1_DEV void cdef_filter(const Eav1Tables *tab, const Plane &out, int x0, int y0, int w, int h, const int16_t *tile,
-                          int pri, int sec, int dir, int damping, int bitdepth_max, int tid, int nthr)
+                          int pri, int sec, int dir, int damping, int bitdepth_max, int tid, int nthr,
+                          const Plane *out2 = nullptr, const int16_t *tile2 = nullptr)
 {
     const int bd8 = (32 - clz32((unsigned)bitdepth_max)) - 8;
     const int pri_tap = 4 - ((pri >> bd8) & 1);
@@ -185,10 +213,12 @@ EAV1_DEV void cdef_filter(const Eav1Tables *tab, const Plane &out, int x0, int y
         o2[k] = tab->cdef_directions[dir + 4][k];
         o3[k] = tab->cdef_directions[dir][k];
     }
-    const int lw = ulog2((unsigned)w);
-    for (int i = tid; i < w * h; i += nthr) {
+    const int lw = ulog2((unsigned)w), wh = w * h;
+    for (int ii = tid; ii < (out2 ? 2 * wh : wh); ii += nthr) {
+        const bool second = ii >= wh;
+        const int i = second ? ii - wh : ii;
         const int y = i >> lw, x = i & (w - 1);
-        const int16_t *t = tile + (y + 2) * 12 + x + 2;
+        const int16_t *t = (second ? tile2 : tile) + (y + 2) * 12 + x + 2;
         const int px = t[0];
         int sum = 0, mx = px, mn = px;
 #pragma unroll
@@ -217,7 +247,7 @@ EAV1_DEV void cdef_filter(const Eav1Tables *tab, const Plane &out, int x0, int y
         }
         int v = px + ((sum - (sum < 0) + 8) >> 4);
         if (pri && sec) v = iclip(v, mn, mx);
-        *px_at<pixel>(out, x0 + x, y0 + y) = (pixel)v;
+        *px_at<pixel>(second ? *out2 : out, x0 + x, y0 + y) = (pixel)v;
     }
 }
 
@@ -346,8 +376,8 @@ EAV1_DEV void cdef_block(const PfParams &pp, int bx, int by, bool valid, CdefSme
         if (active && uv_lvl) {
             const uint8_t uvd422[8] = { 7, 0, 2, 4, 5, 6, 6, 6 };
             const int uvdir = uv_pri ? (pp.layout == 2 ? uvd422[dir] : dir) : 0;
-            cdef_filter<pixel>(pp.tab, pp.b[1], cx, cy, cw, chh, sm.tile[1], uv_pri, uv_sec, uvdir, damping - 1, pp.bitdepth_max, tid, nthr);
-            cdef_filter<pixel>(pp.tab, pp.b[2], cx, cy, cw, chh, sm.tile[2], uv_pri, uv_sec, uvdir, damping - 1, pp.bitdepth_max, tid, nthr);
+            cdef_filter<pixel>(pp.tab, pp.b[1], cx, cy, cw, chh, sm.tile[1], uv_pri, uv_sec, uvdir, damping - 1, pp.bitdepth_max, tid, nthr,
+                               &pp.b[2], sm.tile[2]);
         } else {
             cdef_copy<pixel>(pp.a[1], pp.b[1], cx, cy, cw, chh, tid, nthr);
             cdef_copy<pixel>(pp.a[2], pp.b[2], cx, cy, cw, chh, tid, nthr);

@@ -39,9 +39,9 @@ METRIC = "AV1 decoded frames/s (1080p)"
 UNIT = "frames/s"
 
 
-def load_clip():
+def load_clip(name=None):
     from tests.golden.gen_fixtures import read_ivf
-    man = json.load(open(os.path.join(ROOT, "tests", "golden", "manifest.json")))[CLIP]
+    man = json.load(open(os.path.join(ROOT, "tests", "golden", "manifest.json")))[name or CLIP]
     obu = b"".join(read_ivf(os.path.join(ROOT, "tests", "golden", man["file"])))
     return man, obu
 

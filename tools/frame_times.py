@@ -6,7 +6,7 @@ sys.path.insert(0, ROOT)
 import torch
 from bench import load_clip
 from easyav1_b200.lib import load_engine, load_host, StagedInfo, StreamFrame
-man, obu = load_clip()
+man, obu = load_clip(os.environ.get("EAV1_CLIP"))   # default: the bench clip
 E, host = load_engine(), load_host()
 cap = man["w"] * man["h"] * 4
 buf = C.create_string_buffer(cap)

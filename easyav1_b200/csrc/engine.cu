@@ -396,6 +396,7 @@ struct Eav1cuCtx {
     long long sum_frame[64] = {};
     std::vector<uint32_t> est_tmp, order_tmp, bucket_tmp, ritem_tmp, tail_tmp, order2_tmp;
     std::vector<Eav1Cmd> cmd_tmp;
+    std::vector<uint32_t> ritem_tmp2;
     unsigned long long *d_trace = nullptr;   // set only inside eav1cu_staged_trace
     int est_weight = 8;           // ticket key = est_weight * est - tail (EAV1_EST_WEIGHT; any weight >= 1 keeps the order topological)
     bool serial_phase1 = false;   // EAV1_SERIAL_PHASE1: residuals on the main stream (profiling, debugging)
@@ -899,7 +900,23 @@ static int plan_build(Eav1cuCtx *ctx, FramePlan &pl, bool staged, const Eav1Fram
                     pl.unit_px += (long long)cmds[g.unit_cmd[u] + k].w * cmds[g.unit_cmd[u] + k].h;
         }
         if (pl.n_items) {
-            if ((r = up.put(ctx->S().items, g.mc_items.data(), g.mc_items.size() * 4, &d))) return r;
+            // Largest items first (they are independent, any order is legal): the four warps of a CTA
+            // get items of similar size, and the kernel's tail is made of small items, not of a 32x32
+            // tile that happened to be recorded last.
+            std::vector<uint32_t> &sorted = ctx->ritem_tmp2, &bk = ctx->bucket_tmp;
+            auto weight = [&](uint32_t it) {
+                const Eav1Cmd &c = cmds[it & 0xffffff];
+                const int x0 = (int)((it >> 24) & 3) * 32, y0 = (int)((it >> 26) & 3) * 32;
+                const int px = (c.op == EAV1_OP_MC && !c.u.mc.dx) ? std::min(32, c.w - x0) * std::min(32, c.h - y0) : (int)c.w * c.h;
+                int lg = 0; while ((2 << lg) <= px) lg++;
+                return 15 - std::min(lg, 15);   // bucket 0 = largest
+            };
+            bk.assign(17, 0);
+            for (uint32_t it : g.mc_items) bk[weight(it) + 1]++;
+            for (size_t b = 1; b < bk.size(); b++) bk[b] += bk[b - 1];
+            sorted.resize(g.mc_items.size());
+            for (uint32_t it : g.mc_items) sorted[bk[weight(it)]++] = it;
+            if ((r = up.put(ctx->S().items, sorted.data(), sorted.size() * 4, &d))) return r;
             pl.d_items = reinterpret_cast<const uint32_t *>(d);
         }
         pl.n_chains = (uint32_t)g.unit_cmd.size(); pl.n_deps = (uint32_t)g.deps.size();

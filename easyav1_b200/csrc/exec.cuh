@@ -161,7 +161,7 @@ EAV1_EXEC_LINK int exec_cmd(const FrameCtx &fc, const Eav1Cmd &c, CtaScratch &sm
             const bool added = ipred_block<pixel>(fc.tab, dst8, dstride, sm.ip.edge, sm.ip.edge2, c.u.ipred.mode, c.w, c.h,
                                                   c.u.ipred.angle, c.u.ipred.max_w, c.u.ipred.max_h, bdmax, tid, nthr,
                                                   reinterpret_cast<uint16_t *>(sm.ip.ac), res, res_pre);
-            if (fused && !added) res_add<BD>(dst8, dstride, res, c.w, c.h, bdmax, tid, nthr);
+            if (fused && !added) { CTA_SYNC(); res_add<BD>(dst8, dstride, res, c.w, c.h, bdmax, tid, nthr); }
             PROF_MARK(3);
             if (fused) return 2;
         }

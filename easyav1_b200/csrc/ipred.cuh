@@ -439,8 +439,7 @@ EAV1_DEV bool ipred_block(const Eav1Tables *tab, pixel *dst, int stride, uint16_
     }
     }
     PROF_MARK(26);
-    CTA_SYNC();
-    PROF_MARK(27);
+    // no barrier here: the caller's per-command barrier follows
     return res != nullptr;
 }
 

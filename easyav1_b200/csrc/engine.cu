@@ -150,6 +150,14 @@ __device__ __forceinline__ void recon_worker(const FrameCtx &fc, const ReconArgs
                     if (tid == 0 && ra.hist) {   // [op][log2(w*h)] -> cycles, count
                         const int lg = 31 - __clz((int)ws.cmd[c_this].w * (int)ws.cmd[c_this].h);
                         unsigned long long *hh = ra.hist + ((op & 15) * 16 + (lg & 15)) * 2;
+                        if (op == EAV1_OP_IPRED) {   // tables 15 / 14: by prediction mode, all sizes / 16x16 and larger
+                            unsigned long long *hm = ra.hist + (15 * 16 + (ws.cmd[c_this].u.ipred.mode & 15)) * 2;
+                            atomicAdd(hm, (unsigned long long)(c1 - c0)); atomicAdd(hm + 1, 1ull);
+                            if (lg >= 8) {
+                                hm = ra.hist + (14 * 16 + (ws.cmd[c_this].u.ipred.mode & 15)) * 2;
+                                atomicAdd(hm, (unsigned long long)(c1 - c0)); atomicAdd(hm + 1, 1ull);
+                            }
+                        }
                         atomicAdd(hh, (unsigned long long)(c1 - c0)); atomicAdd(hh + 1, 1ull);
                     }
                     c0 = c1;

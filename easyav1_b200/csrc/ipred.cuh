@@ -420,16 +420,31 @@ EAV1_DEV bool ipred_block(const Eav1Tables *tab, pixel *dst, int stride, uint16_
                 }
                 if (cx == 0) { p[5] = E[-(1 + y0)]; p[6] = E[-(2 + y0)]; }
                 else { p[5] = T[y0 * w + x0 - 1]; p[6] = T[(y0 + 1) * w + x0 - 1]; }
+                if (sizeof(pixel) == 1) {
+                    // 8-bit samples: seven taps = two byte dot products
+                    const uint32_t P0 = (uint32_t)p[0] | (uint32_t)p[1] << 8 | (uint32_t)p[2] << 16 | (uint32_t)p[3] << 24;
+                    const uint32_t P1 = (uint32_t)p[4] | (uint32_t)p[5] << 8 | (uint32_t)p[6] << 16;
 #pragma unroll
-                for (int k = 0; k < 8; k++) {
-                    int acc = 0;
+                    for (int k = 0; k < 8; k++) {
+                        const int acc = dot4_us(P0, tw[2 * k], dot4_us(P1, tw[2 * k + 1], 0));
+                        T[(y0 + (k >> 2)) * w + x0 + (k & 3)] = (uint16_t)iclip((acc + 8) >> 4, 0, bitdepth_max);
+                    }
+                } else {
 #pragma unroll
-                    for (int j = 0; j < 7; j++) acc += (int)(int8_t)((tw[2 * k + (j >> 2)] >> (8 * (j & 3))) & 0xff) * p[j];
-                    T[(y0 + (k >> 2)) * w + x0 + (k & 3)] = (uint16_t)iclip((acc + 8) >> 4, 0, bitdepth_max);
+                    for (int k = 0; k < 8; k++) {
+                        int acc = 0;
+#pragma unroll
+                        for (int j = 0; j < 7; j++) acc += (int)(int8_t)((tw[2 * k + (j >> 2)] >> (8 * (j & 3))) & 0xff) * p[j];
+                        T[(y0 + (k >> 2)) * w + x0 + (k & 3)] = (uint16_t)iclip((acc + 8) >> 4, 0, bitdepth_max);
+                    }
                 }
             }
-            CTA_SYNC();
+            // only the first ch <= 16 threads take part in the steps: a warp-level barrier is enough
+#if defined(__CUDA_ARCH__)
+            if (nthr > 32) { if (tid < 32) __syncwarp(); } else CTA_SYNC();
+#endif
         }
+        CTA_SYNC();
         for (int i = tid; i < n4; i += nthr) {
             const uint16_t *t = T + (i << 2);
             store4r<pixel>(dst + (i >> lw4) * stride + ((i & m4) << 2), t[0], t[1], t[2], t[3],

@@ -79,6 +79,10 @@ print("cycles: staging %.0f per cmd | ipred %.0f per cmd (%d) | itx %.0f per cmd
       (st / max(tot_cmds, 1), ip / max(nip, 1), nip, it / max(nit, 1), nit, ot / max(no, 1), no))
 names = ["nop", "mc", "warp", "avg", "wavg", "mask", "wmask", "blend", "blendv", "blendh", "ipred", "cfl", "pal", "itx"]
 print("cycles per command by op and log2(w*h):")
+modes = ["dc", "vert", "hor", "left_dc", "top_dc", "dc128", "z1", "z2", "z3", "smooth", "smooth_v", "smooth_h", "paeth", "filter"]
+for tab, label in ((15, "all sizes"), (14, ">= 256 samples")):
+    print("ipred cycles by mode (%s): " % label + " | ".join("%s: %d x %.0f" % (modes[m], out[W * n + (tab * 16 + m) * 2 + 1],
+          out[W * n + (tab * 16 + m) * 2] / out[W * n + (tab * 16 + m) * 2 + 1]) for m in range(14) if out[W * n + (tab * 16 + m) * 2 + 1]))
 for op in range(14):
     cells = []
     for lg in range(16):

@@ -23,8 +23,12 @@ enum {
 
 // needs: bit0 left, bit1 top, bit2 topleft, bit3 topright, bit4 bottomleft
 EAV1_DEV int ipred_needs(int mode) {
-    const uint8_t n[14] = { 3, 2, 1, 1, 2, 0, 2 | 8 | 4, 1 | 2 | 4, 1 | 16 | 4, 3, 3, 3, 7, 7 };
-    return n[mode];
+    // five bits per mode, packed (a local array would be built on the stack at every call):
+    // { 3, 2, 1, 1, 2, 0, 2|8|4, 1|2|4, 1|16|4, 3, 3, 3, 7, 7 }
+    const unsigned long long packed =
+        3ull | 2ull << 5 | 1ull << 10 | 1ull << 15 | 2ull << 20 | 0ull << 25 | 14ull << 30 | 7ull << 35 |
+        21ull << 40 | 3ull << 45 | 3ull << 50 | 3ull << 55;
+    return mode < 12 ? (int)((packed >> (5 * mode)) & 31) : 7;
 }
 
 // Gather the edge of the block at (ex,ey) in `pl` into E[-2*sz_l .. 2*sz_t] (E = &edge[EDGE_C]).

@@ -480,10 +480,14 @@ EAV1_DEV void txtp_1d_types(int txtp, int &row, int &col) {
 struct TxDim { uint8_t w, h, shift; };
 EAV1_DEV TxDim tx_dim(int tx) {
     // enum RectTxfmSize order (levels.h:44-78); shift per itx_tmpl.c:160-178
-    const uint8_t W[19] = { 4, 8, 16, 32, 64, 4, 8, 8, 16, 16, 32, 32, 64, 4, 16, 8, 32, 16, 64 };
-    const uint8_t H[19] = { 4, 8, 16, 32, 64, 8, 4, 16, 8, 32, 16, 64, 32, 16, 4, 32, 8, 64, 16 };
-    const uint8_t S[19] = { 0, 1, 2, 2, 2, 0, 0, 1, 1, 1, 1, 1, 1, 1, 1, 2, 2, 2, 2 };
-    TxDim d; d.w = W[tx]; d.h = H[tx]; d.shift = S[tx];
+    // packed tables (a local array would be rebuilt on the stack at every call): log2(w) - 2 and
+    // log2(h) - 2 in three bits, the shift in two bits per transform size
+    // W = { 4, 8, 16, 32, 64, 4, 8, 8, 16, 16, 32, 32, 64, 4, 16, 8, 32, 16, 64 }
+    // H = { 4, 8, 16, 32, 64, 8, 4, 16, 8, 32, 16, 64, 32, 16, 4, 32, 8, 64, 16 }
+    // S = { 0, 1, 2, 2, 2, 0, 0, 1, 1, 1, 1, 1, 1, 1, 1, 2, 2, 2, 2 }
+    const unsigned long long LW = 0x1132846d2244688ull, LH = 0xa161389940c688ull, SS = 0x2a955542a4ull;
+    TxDim d;
+    d.w = (uint8_t)(4 << ((LW >> (3 * tx)) & 7)); d.h = (uint8_t)(4 << ((LH >> (3 * tx)) & 7)); d.shift = (uint8_t)((SS >> (2 * tx)) & 3);
     return d;
 }
 

@@ -279,10 +279,11 @@ template <typename pixel>
 __global__ void __launch_bounds__(128)
 deblock_kernel(PfParams pp, const Eav1LfRec *__restrict__ recs, int n)
 {
-    const int gid = blockIdx.x * blockDim.x + threadIdx.x;
-    const int ri = gid >> 5;
+    // one thread per line of a 4-sample edge unit: 128 threads = the 32 units of one recorded call
+    const int ri = blockIdx.x;
     if (ri >= n) return;
-    lf_unit<pixel>(pp, recs[ri], gid & 31);
+    const int line = threadIdx.x & 3;
+    lf_unit<pixel>(pp, recs[ri], threadIdx.x >> 2, line, line + 1);
 }
 
 template <typename pixel>
@@ -1127,7 +1128,7 @@ static int plan_launch(Eav1cuCtx *ctx, FramePlan &pl)
     for (int pass = 0; pass < 2; pass++) {
         const size_t off = pass ? pl.n_lf0 : 0, cnt = pass ? pl.n_lf1 : pl.n_lf0;
         if (!cnt) continue;
-        const unsigned grid = (unsigned)((cnt * 32 + 127) / 128);
+        const unsigned grid = (unsigned)cnt;
         if (hbd) deblock_kernel<uint16_t><<<grid, 128, 0, st>>>(pp, pl.d_lf + off, (int)cnt);
         else     deblock_kernel<uint8_t><<<grid, 128, 0, st>>>(pp, pl.d_lf + off, (int)cnt);
         ctx->n_launches++;

@@ -197,6 +197,22 @@ EAV1_DEV unsigned edge_sum(const uint16_t *p, int step, int n, int tid, int nthr
     return t;
 }
 
+// E[1..w] + E[-1..-h] in one pass (one reduction instead of two)
+EAV1_DEV unsigned edge_sum2(const uint16_t *E, int w, int h, int tid, int nthr) {
+#if defined(__CUDA_ARCH__)
+    if (nthr >= 32) {
+        unsigned s = 0;
+        for (int i = tid & 31; i < w + h; i += 32) s += i < h ? E[-1 - i] : E[1 + i - h];
+        for (int o = 16; o; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+        return s;
+    }
+#endif
+    unsigned t = 0;
+    for (int i = 0; i < w; i++) t += E[1 + i];
+    for (int i = 0; i < h; i++) t += E[-1 - i];
+    return t;
+}
+
 // Predict a w x h block into dst (stride in pixels) from the edge array (edge[EDGE_C] = top-left).
 // edge2 is scratch of the same size.
 // With `res` (row-major int16 residual of the same block) the sum prediction + residual is written in
@@ -219,7 +235,7 @@ EAV1_DEV bool ipred_block(const Eav1Tables *tab, pixel *dst, int stride, uint16_
         else if (mode == IP_TOP_DC) dc = ((w >> 1) + edge_sum(&E[1], 1, w, tid, nthr)) >> lw;
         else if (mode == IP_LEFT_DC) dc = ((h >> 1) + edge_sum(&E[-1], -1, h, tid, nthr)) >> ctz32(h);
         else {
-            unsigned s = ((w + h) >> 1) + edge_sum(&E[1], 1, w, tid, nthr) + edge_sum(&E[-1], -1, h, tid, nthr);
+            unsigned s = ((w + h) >> 1) + edge_sum2(E, w, h, tid, nthr);
             s >>= ctz32(w + h);
             if (w != h) {
                 const bool quarter = w > h * 2 || h > w * 2;

@@ -33,15 +33,19 @@ struct PfParams {
 
 // ------------------------------------------------------------------------------- deblock
 // Behaviour: loop_filter() ext/dav1d/src/loopfilter_tmpl.c:38-170 and the four sb128 wrappers
-// :172-246. One thread filters the four lines of one 4-sample edge unit.
+// :172-246. One thread filters lines [line0, line1) of one 4-sample edge unit (the kernel gives
+// every line its own thread: four times the parallelism, and for row edges neighbouring threads
+// touch neighbouring samples; the host emulation runs all four in one call).
 template <typename pixel>
-EAV1_DEV void lf_edge4(pixel *dst, int E, int I, int H, ptrdiff_t stridea, ptrdiff_t strideb, int wd, int bitdepth_max)
+EAV1_DEV void lf_edge4(pixel *dst, int E, int I, int H, ptrdiff_t stridea, ptrdiff_t strideb, int wd, int bitdepth_max,
+                       int line0 = 0, int line1 = 4)
 {
     const int bd8 = (32 - clz32((unsigned)bitdepth_max)) - 8;
     const int F = 1 << bd8;
     E <<= bd8; I <<= bd8; H <<= bd8;
     const int dmin = -128 * (1 << bd8), dmax = 128 * (1 << bd8) - 1;
-    for (int i = 0; i < 4; i++, dst += stridea) {
+    dst += stridea * line0;
+    for (int i = line0; i < line1; i++, dst += stridea) {
         const int p1 = dst[strideb * -2], p0 = dst[strideb * -1];
         const int q0 = dst[0], q1 = dst[strideb];
         int p2 = 0, p3 = 0, q2 = 0, q3 = 0;
@@ -115,7 +119,7 @@ EAV1_DEV void lf_edge4(pixel *dst, int E, int I, int H, ptrdiff_t stridea, ptrdi
 
 // One 4-sample edge unit `u` (0..31) of one recorded loop_filter_sb call.
 template <typename pixel>
-EAV1_DEV void lf_unit(const PfParams &pp, const Eav1LfRec &r, int u)
+EAV1_DEV void lf_unit(const PfParams &pp, const Eav1LfRec &r, int u, int line0 = 0, int line1 = 4)
 {
     const uint32_t bit = 1u << u;
     const uint32_t any = r.vmask[0] | r.vmask[1] | r.vmask[2];
@@ -132,10 +136,10 @@ EAV1_DEV void lf_unit(const PfParams &pp, const Eav1LfRec &r, int u)
     else wd = 4 + 2 * ((r.vmask[1] & bit) ? 1 : 0);
     if (r.dir == 0) {
         pixel *dst = px_at<pixel>(pl, r.x, r.y + 4 * u);
-        lf_edge4<pixel>(dst, E, I, H, stride, 1, wd, pp.bitdepth_max);
+        lf_edge4<pixel>(dst, E, I, H, stride, 1, wd, pp.bitdepth_max, line0, line1);
     } else {
         pixel *dst = px_at<pixel>(pl, r.x + 4 * u, r.y);
-        lf_edge4<pixel>(dst, E, I, H, 1, stride, wd, pp.bitdepth_max);
+        lf_edge4<pixel>(dst, E, I, H, 1, stride, wd, pp.bitdepth_max, line0, line1);
     }
 }
 
@@ -183,6 +187,19 @@ EAV1_DEV void cdef_load(const Plane &pl, int x0, int y0, int w, int h, int edges
                 const bool ok = row_ok && (x >= 0 || (edges & 1)) && (x < w || (edges & 2));
                 tile[ty * 12 + tx] = ok ? (int16_t)((v >> (8 * b)) & 0xff) : (int16_t)-32768;
             }
+        }
+        return;
+    }
+    if (sizeof(pixel) == 2 && (x0 & 1) == 0) {
+        // 16-bit: two samples per aligned 32-bit load; the 2-sample halo on either side is exactly one word
+        const int nw = (w + 4) >> 1;
+        const FastDiv fdw(nw);
+        for (int i = tid; i < (h + 4) * nw; i += nthr) {
+            const int ty = fdw.div(i), wi = i - ty * nw, y = ty - 2;
+            const bool ok = (y >= 0 || (edges & 4)) && (y < h || (edges & 8)) && (wi > 0 || (edges & 1)) && (wi < nw - 1 || (edges & 2));
+            uint32_t v = 0x80008000u;   // two INT16_MIN markers
+            if (ok) v = *reinterpret_cast<const uint32_t *>(pl.p + (ptrdiff_t)(y0 + y) * pl.stride + (ptrdiff_t)(x0 - 2 + 2 * wi) * 2);
+            *reinterpret_cast<uint32_t *>(&tile[ty * 12 + 2 * wi]) = v;
         }
         return;
     }

@@ -177,6 +177,12 @@ def run_reference(args, man, obu):
     fps = total_n / total_t
     sample = "%d passes of the %d-frame %s stream, dav1d C (no asm), n_threads=%d, frame delay auto" % (
         args.steps, len(man["frames"]), CLIP, thr)
+    multi = None
+    if args.streams > 1:
+        t_each = max(2, thr // args.streams)
+        concurrent_passes(lambda: ref_decode_pass(obu, cap, t_each)[0], args.streams, 1)
+        n_multi, t_multi = concurrent_passes(lambda: ref_decode_pass(obu, cap, t_each)[0], args.streams, args.steps)
+        multi = {"streams": args.streams, "threads_per_stream": t_each, "value": n_multi / t_multi, "unit": UNIT}
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": fps, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total_t / args.steps,
@@ -187,6 +193,7 @@ def run_reference(args, man, obu):
         "cpu_baseline": {"value": fps, "unit": UNIT, "cores": thr, "kind": "reference", "sample": sample},
         "e2e": {"value": fps, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
+        **({"e2e_multi_stream": multi} if multi else {}),
     }))
 
 
@@ -215,6 +222,31 @@ def e2e_pass(host, obu, cap, buf):
     host.eav1_stream_close(h)
     dt = time.perf_counter() - t0
     return n, dt, hashlib.md5(buf.raw[:used.value]).hexdigest(), list(cnt)
+
+
+def concurrent_passes(fn, n_streams, steps):
+    """n_streams threads, each running `steps` passes of fn() (ctypes releases the GIL inside the
+    decoders); returns (frames, wall seconds)."""
+    frames = [0] * n_streams
+    errs = []
+
+    def work(i):
+        try:
+            for _ in range(steps):
+                frames[i] += fn()
+        except Exception as e:  # surfaced by the caller
+            errs.append(e)
+
+    ts = [threading.Thread(target=work, args=(i,)) for i in range(n_streams)]
+    t0 = time.perf_counter()
+    for t in ts:
+        t.start()
+    for t in ts:
+        t.join()
+    dt = time.perf_counter() - t0
+    if errs:
+        raise errs[0]
+    return sum(frames), dt
 
 
 def stage_bytes(info, P):
@@ -368,6 +400,33 @@ def run_ours(args, man, obu):
     barrier()
     e2e_t = max_over_ranks(time.perf_counter() - t_all0)
 
+    # ---- optional: S independent streams per GPU, end to end (streams shard, nothing is exchanged)
+    multi = None
+    if args.streams > 1:
+        thr = max(2, host_threads() // args.streams)
+        old = os.environ.get("EASYAV1_THREADS")
+        os.environ["EASYAV1_THREADS"] = str(thr)
+        bufs = [C.create_string_buffer(cap) for _ in range(args.streams)]
+        idx = iter(range(1 << 30))
+        lock = threading.Lock()
+
+        def one_pass():
+            with lock:
+                b = bufs[next(idx) % args.streams]
+            n, _, md5, _ = e2e_pass(host, obu, cap, b)
+            assert md5 == man["frames"][-1]["md5"], "multi-stream decode differs from the golden MD5"
+            return n
+
+        concurrent_passes(one_pass, args.streams, 1)     # warm
+        barrier()
+        n_multi, t_multi = concurrent_passes(one_pass, args.streams, args.steps)
+        t_multi = max_over_ranks(t_multi)
+        multi = {"streams_per_gpu": args.streams, "threads_per_stream": thr, "value": world * n_multi / t_multi, "unit": UNIT}
+        if old is None:
+            os.environ.pop("EASYAV1_THREADS", None)
+        else:
+            os.environ["EASYAV1_THREADS"] = old
+
     # ---- roofline of the stage with the largest share of device time
     KS = [0, 1, 2, 3, 4, 6]
     tot_bytes = [0] * 7
@@ -411,6 +470,8 @@ def run_ours(args, man, obu):
         "gpu_launches": launches,
         "clocks": clk,
     }
+    if multi:
+        out["e2e_multi_stream"] = multi
     if rank == 0:
         thr = host_threads()
         t0 = time.perf_counter()
@@ -434,6 +495,9 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--streams", type=int, default=1,
+                    help="also measure S concurrent decoders per GPU end to end (BASELINE.json configs[4]); "
+                         "adds an e2e_multi_stream object, the headline keys stay single-stream")
     args = ap.parse_args()
     man, obu = load_clip()
     if args.impl == "reference":

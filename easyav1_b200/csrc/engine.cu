@@ -1,5 +1,6 @@
-// engine.cu — libeasyav1_cuda.so: context, device picture pool, command upload, level-by-level
-// launch of the reconstruction kernels and the whole-frame post-filter kernels, C ABI.
+// engine.cu — libeasyav1_cuda.so: context, device picture pool, command upload, per-frame plan
+// (phase-1 items, residual items, dataflow units and their ticket order), the kernels of a frame
+// (motion compensation + residuals, dataflow reconstruction, deblock, CDEF, loop restoration), C ABI.
 // Built for sm_100a only (see easyav1_b200/csrc/Makefile). No CPU fallback.
 #include <cuda_runtime.h>
 #include <stdio.h>

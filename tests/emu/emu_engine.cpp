@@ -266,3 +266,15 @@ int eav1cu_apply_grain(Eav1cuCtx *c, int src_pic, int dst_pic, const Eav1GrainPa
 }
 
 } // extern "C"
+
+// ---- self checks of small device helpers, callable from the CPU tests ------------------------
+extern "C" long long eav1emu_fastdiv_mismatches(int d_max, int i_max)
+{
+    long long bad = 0;
+    for (int d = 1; d <= d_max; d++) {
+        const eav1::FastDiv fd(d);
+        for (int i = 0; i < i_max; i += (i < 4096 ? 1 : 61)) bad += fd.div(i) != i / d;
+        bad += fd.div(i_max - 1) != (i_max - 1) / d;
+    }
+    return bad;
+}

@@ -51,3 +51,15 @@ def test_truncated_stream_fails_cleanly(emu, manifest):
     """a damaged stream ends with an error or early EOS, never a hang or a crash"""
     got = emu("cif_inter", 4, truncate=0.66)
     assert len(got["passes"][0]) < len(manifest["cif_inter"]["frames"])
+
+
+def test_fastdiv_is_exact_over_its_documented_range():
+    """dev_common.cuh FastDiv (multiply-high division used by the tile loops): exact for divisors
+    up to 1024 and dividends below 2^22."""
+    import ctypes as C
+    import os
+    so = os.path.join(os.path.dirname(os.path.abspath(__file__)), "emu", "libeav1_emu.so")
+    L = C.CDLL(so)
+    L.eav1emu_fastdiv_mismatches.restype = C.c_longlong
+    L.eav1emu_fastdiv_mismatches.argtypes = [C.c_int, C.c_int]
+    assert L.eav1emu_fastdiv_mismatches(1024, 1 << 22) == 0

@@ -13,6 +13,12 @@
 #if defined(__CUDACC__)
 #define EAV1_DEV __device__ __forceinline__
 #define EAV1_DEVN __device__ __noinline__
+// helpers on the per-item hot path of the flat kernels: inlined unless EAV1_HOT_NOINLINE is set
+#if defined(EAV1_HOT_NOINLINE) && EAV1_HOT_NOINLINE
+#define EAV1_DEVH __device__ __noinline__
+#else
+#define EAV1_DEVH __device__ __forceinline__
+#endif
 #define EAV1_DEVM __device__ __forceinline__
 // group barrier: a work group is either one warp (nthr == 32) or the whole CTA; `nthr` must be in scope
 #define CTA_SYNC() do { if (nthr <= 32) __syncwarp(); else __syncthreads(); } while (0)
@@ -20,6 +26,7 @@
 #else
 #define EAV1_DEV static inline
 #define EAV1_DEVN static
+#define EAV1_DEVH static inline
 #define EAV1_DEVM inline
 #define CTA_SYNC() ((void)0)
 #define EAV1_LDG(p) (*(p))

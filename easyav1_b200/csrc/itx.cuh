@@ -585,7 +585,7 @@ EAV1_DEV void itx_col_reg(const int32_t *s, int P, int x, int type, int col_min,
 }
 
 template <typename BD>
-EAV1_DEVN void itx_add_reg(typename BD::pixel *dst, int dst_stride, const typename BD::coef *coeff, int w, int h,
+EAV1_DEVH void itx_add_reg(typename BD::pixel *dst, int dst_stride, const typename BD::coef *coeff, int w, int h,
                            int shift, int rt, int ct, int bitdepth_max, int32_t *s, int tid, int nthr, int16_t *res)
 {
     const int is_rect2 = (w * 2 == h) || (h * 2 == w);
@@ -624,7 +624,7 @@ EAV1_DEVN void itx_add_reg(typename BD::pixel *dst, int dst_stride, const typena
 
 // dst += inverse_transform(coef). `s` is the CTA's shared tile (>= 64*65 int32).
 template <typename BD>
-EAV1_DEVN void itx_add(typename BD::pixel *dst, int dst_stride /*pixels*/, const typename BD::coef *coeff,
+EAV1_DEVH void itx_add(typename BD::pixel *dst, int dst_stride /*pixels*/, const typename BD::coef *coeff,
                       int eob, int tx, int txtp, int bitdepth_max, int32_t *s, int tid, int nthr, int16_t *res = nullptr)
 {
     typedef typename BD::wide W;

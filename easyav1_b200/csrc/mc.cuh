@@ -118,7 +118,7 @@ EAV1_DEV void store4_i16(int16_t *d, const int v[4]) {
 
 // 8-bit put/prep for w >= 4, four horizontally adjacent samples per work item. Arithmetic is
 // the reference's (mc_tmpl.c:130-187, :247-306) with intermediate_bits = 4 and no prep bias.
-EAV1_DEVN void mc_block8_fast(const Eav1Tables *tab, const SrcView<uint8_t> &src, int sx, int sy,
+EAV1_DEVH void mc_block8_fast(const Eav1Tables *tab, const SrcView<uint8_t> &src, int sx, int sy,
                              int w, int h, int fw, int fh, int mx, int my, int filt_h, int filt_v,
                              uint8_t *dst8, int16_t *dst16, int dstride, int16_t *mid, int tid, int nthr)
 {
@@ -231,7 +231,7 @@ EAV1_DEVN void mc_block8_fast(const Eav1Tables *tab, const SrcView<uint8_t> &src
 // (w,h) is the rectangle produced; (fw,fh) the dimensions of the whole prediction block, which
 // select the 4-tap or 8-tap filter set -- they differ when a block is produced tile by tile.
 template <typename BD>
-EAV1_DEVN void mc_block(const Eav1Tables *tab, const SrcView<typename BD::pixel> &src, int sx, int sy,
+EAV1_DEVH void mc_block(const Eav1Tables *tab, const SrcView<typename BD::pixel> &src, int sx, int sy,
                        int w, int h, int fw, int fh, int mx, int my, int filt_h, int filt_v,
                        typename BD::pixel *dst8, int16_t *dst16, int dstride,
                        int bitdepth_max, int16_t *mid, int tid, int nthr)

@@ -1,4 +1,6 @@
-for w in 8 16 1 8 16 1; do
-  EAV1_EST_WEIGHT=$w python tools/frame_times.py 120 > gpurun_out/s29_ft_$w.txt 2>&1
-  echo "est weight $w: $(awk '{for(i=1;i<=NF;i++) if($i=="recon") s+=$(i+1)} END{print s}' gpurun_out/s29_ft_$w.txt) us recon; top: $(awk '{for(i=1;i<=NF;i++) if($i=="recon") print $(i+1)}' gpurun_out/s29_ft_$w.txt | sort -rn | head -4 | tr '\n' ' ')"
+cp easyav1_b200/libeasyav1_cuda.so /tmp/base.so
+for v in base dd0 base dd0; do
+  if [ $v = base ]; then cp /tmp/base.so easyav1_b200/libeasyav1_cuda.so; else cp gpurun_variants/$v.so easyav1_b200/libeasyav1_cuda.so; fi
+  python bench.py --steps 2 --warmup 3 2>/dev/null | python -c "
+import json,sys; d=json.loads(sys.stdin.read()); print('$v', round(d['value'],1), round(d['ms_per_step'],2), {k:v['ms_per_step'] for k,v in d['roofline']['stages'].items()})"
 done

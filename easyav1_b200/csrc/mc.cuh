@@ -337,7 +337,7 @@ EAV1_DEVH void mc_block(const Eav1Tables *tab, const SrcView<typename BD::pixel>
 // Scaled put/prep: (mx,my) are 1/1024 positions of sample (0,0), (dx,dy) the per-sample steps.
 // (sx,sy) addresses the sample the reference's `src` pointer points at.
 template <typename BD>
-EAV1_DEVN void mc_scaled_block(const Eav1Tables *tab, const SrcView<typename BD::pixel> &src, int sx, int sy,
+EAV1_DEVH void mc_scaled_block(const Eav1Tables *tab, const SrcView<typename BD::pixel> &src, int sx, int sy,
                               int w, int h, int mx, int my, int dx, int dy, int filt_h, int filt_v,
                               typename BD::pixel *dst8, int16_t *dst16, int dstride,
                               int bitdepth_max, int tid, int nthr)
@@ -389,7 +389,7 @@ EAV1_DEVN void mc_scaled_block(const Eav1Tables *tab, const SrcView<typename BD:
 
 // 8x8 affine warp. (sx,sy) addresses the sample the reference's `src` pointer points at.
 template <typename BD>
-EAV1_DEVN void warp8x8_block(const Eav1Tables *tab, const SrcView<typename BD::pixel> &src, int sx, int sy,
+EAV1_DEVH void warp8x8_block(const Eav1Tables *tab, const SrcView<typename BD::pixel> &src, int sx, int sy,
                             const int16_t abcd[4], int mx, int my,
                             typename BD::pixel *dst8, int16_t *dst16, int dstride,
                             int bitdepth_max, int16_t *mid, int tid, int nthr)

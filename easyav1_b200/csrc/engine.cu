@@ -189,7 +189,7 @@ __device__ __forceinline__ void recon_worker(const FrameCtx &fc, const ReconArgs
 }
 
 #ifndef EAV1_RECON_MIN_CTAS
-#define EAV1_RECON_MIN_CTAS 1
+#define EAV1_RECON_MIN_CTAS 3   // 168 registers, 444 resident work groups: measured best (1: 255 regs, 4: 128 regs with spills)
 #endif
 template <typename BD>
 __global__ void __launch_bounds__(128, EAV1_RECON_MIN_CTAS)

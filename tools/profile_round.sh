@@ -16,3 +16,10 @@ ncu --set full --clock-control none --import-source on -k regex:vorbis_kernel --
 ncu --set full --clock-control none --import-source on -k regex:"fg_apply_kernel|fg_prepare_kernel" --launch-skip 120 --launch-count 4 \
     -o $out/${tag}_grain_full python -m pytest tests/test_filmgrain.py -m gpu -x -q > $out/${tag}_ncu_grain.log 2>&1
 ls -la $out/${tag}_*
+# the reports themselves are large (source import): keep their raw pages, drop the .ncu-rep files so
+# that gpurun_out stays under the 64 MiB that travel back
+for r in full vorbis_full grain_full; do
+  ncu -i $out/${tag}_$r.ncu-rep --page raw --csv > $out/${tag}_${r}_raw.csv 2>/dev/null
+  rm -f $out/${tag}_$r.ncu-rep
+done
+ls -la $out/${tag}_*

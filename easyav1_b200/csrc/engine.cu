@@ -248,9 +248,10 @@ resid_kernel(FrameCtx fc, const Eav1Cmd *__restrict__ cmds, const uint32_t *__re
 {
     __shared__ alignas(16) unsigned char scratch[4 * EAV1_WARP_SCRATCH > sizeof(CtaScratch) ? 4 * EAV1_WARP_SCRATCH : sizeof(CtaScratch)];
     __shared__ Eav1Cmd cmd[4];
-    if (blockIdx.x < n_small_ctas) {
+    const uint32_t n_big = n_items - n_small;     // the slow items lead the grid
+    if (blockIdx.x >= n_big) {
         const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
-        const uint32_t it = blockIdx.x * 4 + w;
+        const uint32_t it = (blockIdx.x - n_big) * 4 + w;
         if (it >= n_small) return;
         const uint32_t ci = items[it];
         if (lane < (int)(sizeof(Eav1Cmd) / 4))
@@ -258,7 +259,7 @@ resid_kernel(FrameCtx fc, const Eav1Cmd *__restrict__ cmds, const uint32_t *__re
         __syncwarp();
         exec_itx_residual<BD>(fc, cmd[w], *reinterpret_cast<CtaScratch *>(scratch + w * EAV1_WARP_SCRATCH), lane, 32);
     } else {
-        const uint32_t it = n_small + (blockIdx.x - n_small_ctas);
+        const uint32_t it = n_small + blockIdx.x;
         if (it >= n_items) return;
         const uint32_t ci = items[it];
         if (threadIdx.x < sizeof(Eav1Cmd) / 4)
@@ -861,8 +862,15 @@ static int plan_build(Eav1cuCtx *ctx, FramePlan &pl, bool staged, const Eav1Fram
             cc.assign(cmds, cmds + n_cmds);
             std::vector<uint32_t> &ri = ctx->ritem_tmp, &bk = ctx->bucket_tmp;
             size_t off = (arena_bytes + 31) & ~(size_t)31;
-            bk.assign(2 * 19 * 17 + 1, 0);
-            auto key = [](const Eav1Cmd &c) { return ((c.w > 32 || c.h > 32) ? 19 * 17 : 0) + c.u.itx.tx * 17 + c.u.itx.txtp; };
+            // small blocks (one warp each) largest first, same (size, type) adjacent; blocks with a
+            // 64-point side (one CTA each) behind them in the list, but first in the grid
+            const int NK = 19 * 17;
+            bk.assign(8 * NK + 1, 0);
+            auto key = [NK](const Eav1Cmd &c) {
+                if (c.w > 32 || c.h > 32) return 7 * NK + c.u.itx.tx * 17 + c.u.itx.txtp;
+                int lg = 0; while ((2 << lg) <= (int)c.w * c.h) lg++;      // 4 (4x4) .. 10 (32x32)
+                return (10 - lg) * NK + c.u.itx.tx * 17 + c.u.itx.txtp;
+            };
             uint32_t n_two = 0;
             pl.resid_px = 0;
             for (size_t i = 0; i < n_cmds; i++) {
@@ -878,7 +886,7 @@ static int plan_build(Eav1cuCtx *ctx, FramePlan &pl, bool staged, const Eav1Fram
                 n_two++;
             }
             for (size_t b = 1; b < bk.size(); b++) bk[b] += bk[b - 1];
-            pl.n_ritems_small = bk[19 * 17];
+            pl.n_ritems_small = bk[7 * NK];
             ri.resize(n_two);
             for (size_t i = 0; i < n_cmds; i++)
                 if (cc[i].flags & EAV1_F_RESID && cc[i].op == EAV1_OP_ITX) ri[bk[key(cc[i])]++] = (uint32_t)i;

@@ -1433,6 +1433,87 @@ int eav1cu_apply_grain(Eav1cuCtx *ctx, int src_pic, int dst_pic, const Eav1Grain
     return 0;
 }
 
+} // extern "C"
+
+// ---- film grain without any allocation (eav1cu_apply_grain_noalloc) -----------------------------
+// Same kernels as eav1cu_apply_grain; the scratch they need (grain templates, scaling LUTs, block
+// offsets) is this file-scope device array instead of a cudaMalloc'd buffer. Every GPU that loads the
+// library holds these bytes until the process exits. In host code `g_fg_static` is only a stand-in for
+// the symbol, not a device address: the address each device gave it is looked up once per device with
+// cudaGetSymbolAddress (that device current) and it is that pointer the kernels receive.
+enum { FG_STATIC_OFFSET_BYTES = EAV1CU_NOALLOC_MAX_GRAIN_BLOCKS,
+       FG_STATIC_BYTES = FG_GRAIN_BYTES + FG_SCALE_BYTES + FG_STATIC_OFFSET_BYTES };
+static __device__ __align__(256) unsigned char g_fg_static[FG_STATIC_BYTES];
+
+enum { FG_STATIC_MAX_DEVICES = 64 };
+static std::mutex g_fg_static_mu;
+static uint8_t *g_fg_static_ptr[FG_STATIC_MAX_DEVICES];
+
+// device address of g_fg_static on `device` (which must be current); looked up on first use per device
+static cudaError_t fg_static_scratch(int device, uint8_t **out)
+{
+    std::lock_guard<std::mutex> g(g_fg_static_mu);
+    if (!g_fg_static_ptr[device]) {
+        void *p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&p, g_fg_static);
+        if (e != cudaSuccess) return e;
+        if (!p) return cudaErrorInvalidSymbol;
+        g_fg_static_ptr[device] = (uint8_t *)p;
+    }
+    *out = g_fg_static_ptr[device];
+    return cudaSuccess;
+}
+
+extern "C" {
+
+int eav1cu_apply_grain_noalloc(Eav1cuCtx *ctx, int src_pic, int dst_pic, const Eav1GrainParams *g)
+{
+    if (!ctx || !g) return EAV1CU_ERR_INVAL;
+    if (ctx->err) return ctx->err;
+    const int np = (int)ctx->pics.size();
+    if (src_pic < 0 || src_pic >= np || dst_pic < 0 || dst_pic >= np || src_pic == dst_pic ||
+        !ctx->pics[src_pic].base || !ctx->pics[dst_pic].base)
+        return fail(ctx, EAV1CU_ERR_INVAL, "apply_grain_noalloc: bad picture id");
+    const Picture &src = ctx->pics[src_pic], &dst = ctx->pics[dst_pic];
+    if (src.w != dst.w || src.h != dst.h || src.layout != dst.layout || src.bpc != dst.bpc)
+        return fail(ctx, EAV1CU_ERR_INVAL, "apply_grain_noalloc: geometry mismatch");
+    if (!ctx->have_tab) return fail(ctx, EAV1CU_ERR_INVAL, "apply_grain_noalloc: tables not set");
+    if (g->ar_coeff_lag < 0 || g->ar_coeff_lag > 3 || g->num_y_points > 14 || g->num_uv_points[0] > 10 ||
+        g->num_uv_points[1] > 10)
+        return fail(ctx, EAV1CU_ERR_INVAL, "apply_grain_noalloc: bad parameters");
+    if (ctx->device < 0 || ctx->device >= FG_STATIC_MAX_DEVICES)
+        return fail(ctx, EAV1CU_ERR_INVAL, "apply_grain_noalloc: device index beyond the per-device address table");
+    FgParams P;
+    memset(&P, 0, sizeof(P));
+    P.rows = (src.h + 31) / 32; P.cols = (src.w + 31) / 32;
+    if ((size_t)P.rows * P.cols > (size_t)FG_STATIC_OFFSET_BYTES)
+        return fail(ctx, EAV1CU_ERR_INVAL,
+                    "apply_grain_noalloc: picture has more than EAV1CU_NOALLOC_MAX_GRAIN_BLOCKS 32x32 luma blocks "
+                    "(static scratch limit); use eav1cu_apply_grain");
+    CK(cudaSetDevice(ctx->device));
+    uint8_t *scratch = nullptr;
+    const cudaError_t se = fg_static_scratch(ctx->device, &scratch);
+    if (se != cudaSuccess) return fail(ctx, EAV1CU_ERR_CUDA, "cudaGetSymbolAddress(g_fg_static)", se);
+    P.g = *g;
+    for (int i = 0; i < 3; i++) { P.src[i] = src.pl[i]; P.dst[i] = dst.pl[i]; }
+    P.w = src.w; P.h = src.h; P.layout = src.layout;
+    P.ss_hor = src.layout != 3; P.ss_ver = src.layout == 1;
+    P.bitdepth_max = (1 << src.bpc) - 1;
+    P.tab = ctx->d_tab;
+    // fg_prepare_kernel rewrites every byte the apply kernel reads (all three templates, the LUT range
+    // of this bit depth, rows x cols offsets), so nothing of the previous call's contents has to be cleared.
+    P.grain = (int16_t *)scratch;
+    P.scaling = scratch + FG_GRAIN_BYTES;
+    P.offsets = scratch + FG_GRAIN_BYTES + FG_SCALE_BYTES;
+    fg_prepare_kernel<<<1, 256, 0, ctx->stream>>>(P);
+    const dim3 grid((P.cols + FG_STRIP - 1) / FG_STRIP, P.rows);
+    if (src.bpc > 8) fg_apply_kernel<uint16_t><<<grid, 256, 0, ctx->stream>>>(P);
+    else fg_apply_kernel<uint8_t><<<grid, 256, 0, ctx->stream>>>(P);
+    ctx->n_launches += 2;
+    CK(cudaGetLastError());
+    return 0;
+}
+
 int eav1cu_set_stream(Eav1cuCtx *ctx, void *cuda_stream)
 {
     if (!ctx) return EAV1CU_ERR_INVAL;

@@ -318,6 +318,27 @@ typedef struct Eav1GrainParams {
  * submitted so far. Three launches: grain templates + scaling LUTs + block offsets, then all planes. */
 int  eav1cu_apply_grain(Eav1cuCtx *ctx, int src_pic, int dst_pic, const Eav1GrainParams *g);
 
+/* eav1cu_apply_grain_noalloc has NO counterpart in the reference; it was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid it). Same arguments, same kernels and bit-identical output as
+ * eav1cu_apply_grain, but the scratch those kernels need (grain templates, scaling LUTs, per-block
+ * template offsets; 83,968 bytes) is a file-scope static __device__ array that every GPU loading the
+ * library holds until the process exits, so the call performs no cudaMalloc / cudaFree / allocating
+ * library call. The caller still passes input and output: src_pic / dst_pic are pictures it allocated
+ * earlier with eav1cu_pic_alloc on a context whose tables are set.
+ *   limit      pictures of at most EAV1CU_NOALLOC_MAX_GRAIN_BLOCKS 32x32 luma blocks,
+ *              ceil(w/32) * ceil(h/32) <= 34,816 (e.g. 8192x4352); anything larger is rejected with
+ *              EAV1CU_ERR_INVAL and a message naming the limit (use eav1cu_apply_grain then).
+ *   sharing    every call on a device uses the same array, which keeps the previous call's contents;
+ *              each call rewrites everything it later reads, so nothing needs clearing, but two calls
+ *              whose kernels overlap on the GPU (different streams / contexts of one device) RACE on
+ *              it. Serialise them (one stream, or an event between them).
+ *   set-up     the array's device address is looked up once per device (cudaGetSymbolAddress, on the
+ *              first call for that device); callers under graph capture make one call outside capture
+ *              first. */
+#define EAV1CU_NOALLOC_MAX_GRAIN_BLOCKS 34816
+int  eav1cu_apply_grain_noalloc(Eav1cuCtx *ctx, int src_pic, int dst_pic, const Eav1GrainParams *g);
+
 /* ---- Vorbis float slice ----------------------------------------------------
  * Replaces, for a batch of decoded packets, mdct_backward (ext/minivorbis/minivorbis.h:7054-7148,
  * called from mapping0_inverse :17825), the window + overlap-add of vorbis_synthesis_blockin

@@ -18,6 +18,7 @@
 #include "postfilter.cuh"
 #include "filmgrain.cuh"
 #include "sched.h"
+#include "coverage.h"
 
 using namespace eav1;
 
@@ -310,6 +311,20 @@ lr_kernel(PfParams pp, const Eav1LrRec *__restrict__ recs)
     lr_tile<pixel>(pp, r, blockIdx.x, sm, threadIdx.x, blockDim.x);
 }
 
+// Super-resolution: one thread per output sample, blockIdx.z = plane, the 64-phase filter table in shared memory.
+template <typename pixel>
+__global__ void __launch_bounds__(256)
+resize_kernel(ResizeParams rp)
+{
+    __shared__ int8_t filt[64][8];
+    for (int i = threadIdx.x; i < 64 * 8 / 4; i += blockDim.x)
+        reinterpret_cast<uint32_t *>(&filt[0][0])[i] = reinterpret_cast<const uint32_t *>(&rp.tab->resize_filter[0][0])[i];
+    __syncthreads();
+    const int pl = blockIdx.z, y = blockIdx.y, x = blockIdx.x * blockDim.x + threadIdx.x;
+    if (y >= rp.h[pl] || x >= rp.dst_w[pl]) return;
+    resize_sample<pixel>(rp, filt, pl, x, y);
+}
+
 __global__ void __launch_bounds__(256)
 fg_prepare_kernel(FgParams P)
 {
@@ -387,7 +402,7 @@ struct Eav1cuCtx {
     cudaEvent_t fence_ev[N_FENCE] = {};
     unsigned long long fence_next = 1;
     std::mutex fence_mu;
-    Picture work[2];           // post-filter ping-pong pictures
+    Picture work[4];           // post-filter ping-pong pictures; [2], [3]: super-resolved CDEF output / deblocked frame
     std::vector<Eav1LfRec> lf_sorted;
     Scheduler sched;
     DepGraph graph;
@@ -841,7 +856,20 @@ static int plan_build(Eav1cuCtx *ctx, FramePlan &pl, bool staged, const Eav1Fram
     pl.fd.lf_recs = nullptr; pl.fd.lf_level = nullptr; pl.fd.lf_mask = nullptr; pl.fd.lr_recs = nullptr;
     const bool has_cdef = fd->cdef_enable != 0, has_lr = fd->n_lr_recs > 0;
     int r;
-    if (has_cdef || has_lr) {
+    if (fd->superres) {
+        if (fd->sr_pic < 0 || fd->sr_pic >= (int)ctx->pics.size() || !ctx->pics[fd->sr_pic].base || fd->sr_pic == fd->cur)
+            return fail(ctx, EAV1CU_ERR_INVAL, "bad super-resolution picture id");
+        const Picture &sr = ctx->pics[fd->sr_pic];
+        if (sr.w != fd->sr_w || sr.h != cur.h || sr.layout != cur.layout || sr.bpc != cur.bpc)
+            return fail(ctx, EAV1CU_ERR_INVAL, "super-resolution picture geometry mismatch");
+        // reconstruction + deblock happen in `cur` itself; CDEF needs one more picture of the coded size,
+        // loop restoration the upscaled CDEF output and (for its stripe borders) the upscaled deblocked frame
+        if (has_cdef && (r = pic_setup(ctx, ctx->work[1], cur.w, cur.h, cur.layout, cur.bpc))) return r;
+        if (has_lr) {
+            if ((r = pic_setup(ctx, ctx->work[2], sr.w, sr.h, sr.layout, sr.bpc))) return r;
+            if (has_cdef && (r = pic_setup(ctx, ctx->work[3], sr.w, sr.h, sr.layout, sr.bpc))) return r;
+        }
+    } else if (has_cdef || has_lr) {
         if ((r = pic_setup(ctx, ctx->work[0], cur.w, cur.h, cur.layout, cur.bpc))) return r;
         if (has_cdef && has_lr && (r = pic_setup(ctx, ctx->work[1], cur.w, cur.h, cur.layout, cur.bpc))) return r;
     }
@@ -1017,8 +1045,10 @@ static int plan_launch(Eav1cuCtx *ctx, FramePlan &pl)
     const bool has_cdef = fd->cdef_enable != 0, has_lr = pl.n_lr > 0;
     cudaStream_t st = ctx->stream;
     long long n0 = ctx->n_launches;
-    // recon + deblock happen in A; CDEF / LR then move the frame towards `cur` out of place
-    Picture &A = (has_cdef || has_lr) ? ctx->work[0] : cur;
+    // recon + deblock happen in A; CDEF / LR then move the frame towards `cur` out of place.
+    // With super-resolution A is `cur` itself (coded width) and the frame ends up in fd->sr_pic.
+    const bool superres = fd->superres != 0;
+    Picture &A = superres ? cur : (has_cdef || has_lr) ? ctx->work[0] : cur;
 
     FrameCtx fc;
     memset(&fc, 0, sizeof(fc));
@@ -1145,7 +1175,7 @@ static int plan_launch(Eav1cuCtx *ctx, FramePlan &pl)
     }
     if (has_cdef) {
         StageTimer tm(ctx, 2);
-        Picture &dst = has_lr ? ctx->work[1] : cur;
+        Picture &dst = (has_lr || superres) ? ctx->work[1] : cur;
         for (int i = 0; i < 3; i++) pp.b[i] = dst.pl[i];
         pp.lfmask = pl.d_lfmask;
         dim3 grid((fd->bw4 / 2 + 8) / 8, (fd->bh4 + 1) / 2);
@@ -1153,9 +1183,43 @@ static int plan_launch(Eav1cuCtx *ctx, FramePlan &pl)
         else     cdef_kernel<uint8_t><<<grid, 256, 0, st>>>(pp);
         ctx->n_launches++;
     }
+    Picture *lr_src = has_cdef ? &ctx->work[1] : &A, *lr_out = &cur;
+    if (superres) {
+        // mc.resize over the whole frame (recon_tmpl.c:2053-2086): the CDEF output becomes the pre-LR picture at
+        // the upscaled width; with CDEF on, the deblocked frame is upscaled as well because the rows above and
+        // below a restoration stripe are deblocked, not CDEF-filtered, samples (lf_apply_tmpl.c:76-88)
+        StageTimer tm(ctx, 3);
+        Picture &out = ctx->pics[fd->sr_pic];
+        auto resize = [&](const Picture &from, const Picture &to) {
+            ResizeParams rp;
+            memset(&rp, 0, sizeof(rp));
+            rp.n_planes = fd->layout ? 3 : 1;
+            int max_w = 0, max_h = 0;
+            for (int i = 0; i < rp.n_planes; i++) {
+                const int sh = i && fd->layout != 3, sv = i && fd->layout == 1;
+                rp.src[i] = from.pl[i]; rp.dst[i] = to.pl[i];
+                rp.dst_w[i] = (fd->sr_w + sh) >> sh; rp.src_w[i] = (4 * fd->bw4 + sh) >> sh; rp.h[i] = (fd->h + sv) >> sv;
+                rp.dx[i] = fd->resize_step[!!i]; rp.mx0[i] = fd->resize_start[!!i];
+                max_w = std::max(max_w, rp.dst_w[i]); max_h = std::max(max_h, rp.h[i]);
+            }
+            rp.bitdepth_max = (1 << fd->bpc) - 1;
+            rp.tab = ctx->d_tab;
+            const dim3 grid((max_w + 255) / 256, max_h, rp.n_planes);
+            if (hbd) resize_kernel<uint16_t><<<grid, 256, 0, st>>>(rp);
+            else     resize_kernel<uint8_t><<<grid, 256, 0, st>>>(rp);
+            ctx->n_launches++;
+        };
+        if (has_lr) {
+            resize(*lr_src, ctx->work[2]);
+            if (has_cdef) resize(A, ctx->work[3]);
+            for (int i = 0; i < 3; i++) pp.a[i] = has_cdef ? ctx->work[3].pl[i] : ctx->work[2].pl[i];
+            lr_src = &ctx->work[2];
+            lr_out = &out;
+        } else resize(*lr_src, out);
+    }
     if (has_lr) {
         StageTimer tm(ctx, 3);
-        Picture &src = has_cdef ? ctx->work[1] : A;
+        Picture &src = *lr_src, &cur = *lr_out;
         for (int i = 0; i < 3; i++) { pp.b[i] = src.pl[i]; pp.p[i] = cur.pl[i]; }
         CK(cudaMemcpyAsync(cur.base, src.base, std::min(cur.bytes, src.bytes), cudaMemcpyDeviceToDevice, st));
         dim3 grid(384 / LR_TW, (unsigned)pl.n_lr);
@@ -1177,6 +1241,7 @@ int eav1cu_frame_submit(Eav1cuCtx *ctx, const Eav1FrameDesc *fd,
     if (!ctx || !fd) return EAV1CU_ERR_INVAL;
     if (ctx->err) return ctx->err;
     if (!ctx->have_tab) return fail(ctx, EAV1CU_ERR_NOTABLES, "eav1cu_set_tables not called");
+    coverage_count(fd, cmds, n_cmds);
     CK(cudaSetDevice(ctx->device));
     ctx->cur_slot ^= 1;
     Slot &sl = ctx->S();
@@ -1204,6 +1269,8 @@ int eav1cu_frame_submit(Eav1cuCtx *ctx, const Eav1FrameDesc *fd,
     return ctx->err;
 }
 
+int eav1cu_coverage(Eav1Coverage *out, int reset) { return coverage_read(out, reset); }
+
 size_t eav1cu_abi_sizeof(int which)
 {
     switch (which) {
@@ -1213,6 +1280,7 @@ size_t eav1cu_abi_sizeof(int which)
     case 3: return sizeof(Eav1FrameDesc);
     case 4: return sizeof(Eav1StagedInfo);
     case 5: return sizeof(Eav1Tables);
+    case 6: return sizeof(Eav1Coverage);
     default: return 0;
     }
 }
@@ -1408,6 +1476,7 @@ int eav1cu_apply_grain(Eav1cuCtx *ctx, int src_pic, int dst_pic, const Eav1Grain
     if (g->ar_coeff_lag < 0 || g->ar_coeff_lag > 3 || g->num_y_points > 14 || g->num_uv_points[0] > 10 ||
         g->num_uv_points[1] > 10)
         return fail(ctx, EAV1CU_ERR_INVAL, "apply_grain: bad parameters");
+    coverage_count_grain(src.bpc, g);
     CK(cudaSetDevice(ctx->device));
     if (!ctx->d_fg) CK(cudaMalloc(&ctx->d_fg, FG_GRAIN_BYTES + FG_SCALE_BYTES + FG_OFFSET_BYTES));
     FgParams P;

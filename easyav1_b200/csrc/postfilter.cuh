@@ -402,6 +402,32 @@ EAV1_DEV void cdef_block(const PfParams &pp, int bx, int by, bool valid, CdefSme
     }
 }
 
+// ------------------------------------------------------------------------------- super-resolution
+// Behaviour: resize_c, ext/dav1d/src/mc_tmpl.c:918-955 (8-tap horizontal upscale, 64 phases). The
+// reference walks a row with the recurrence mx += dx; src_x += mx >> 14; mx &= 0x3fff; its state after
+// x steps is the 14-bit fixed-point position mx0 + x * dx, so every output sample is independent.
+struct ResizeParams {
+    Plane src[3], dst[3];
+    int dst_w[3], src_w[3], h[3];
+    int dx[3], mx0[3];
+    int n_planes, bitdepth_max;
+    const Eav1Tables *tab;
+};
+
+template <typename pixel>
+EAV1_DEV void resize_sample(const ResizeParams &rp, const int8_t (*filt)[8], int pl, int x, int y)
+{
+    const int pos = rp.mx0[pl] + x * rp.dx[pl];
+    const int src_x = -1 + (pos >> 14);
+    const int8_t *const F = filt[(pos & 0x3fff) >> 8];
+    const pixel *const row = px_at<pixel>(rp.src[pl], 0, y);
+    const int last = rp.src_w[pl] - 1;
+    int sum = 0;
+#pragma unroll
+    for (int k = 0; k < 8; k++) sum += F[k] * row[iclip(src_x - 3 + k, 0, last)];
+    *px_at<pixel>(rp.dst[pl], x, y) = (pixel)iclip((-sum + 64) >> 7, 0, rp.bitdepth_max);
+}
+
 // ------------------------------------------------------------------------------- loop restoration
 // Behaviour: wiener_c (ext/dav1d/src/looprestoration_tmpl.c:250-387) and sgr_5x5_c / sgr_3x3_c /
 // sgr_mix_c (:679-1384) with sgr_calc_row_ab (:505-523) and the finish filters (:555-626).

@@ -128,6 +128,8 @@ void eav1rec_frame_end(Eav1Rec *r, const Dav1dFrameContext *f, int retval);
 
 /* locate a pixel pointer inside the current picture: returns plane or -1 */
 int eav1rec_locate_cur(const Eav1Walk *w, const void *p, int *x, int *y);
+/* same inside the super-resolved picture f->sr_cur (== f->cur without super-resolution) */
+int eav1rec_locate_sr(const Eav1Walk *w, const void *p, int *x, int *y);
 /* locate a pixel pointer inside a reference (0..6) or the current picture (7) */
 int eav1rec_locate_ref(const Eav1Walk *w, const void *p, int *plane, int *x, int *y);
 

@@ -217,6 +217,13 @@ int eav1rec_locate_cur(const Eav1Walk *w, const void *p, int *x, int *y)
     return -1;
 }
 
+int eav1rec_locate_sr(const Eav1Walk *w, const void *p, int *x, int *y)
+{
+    int pl;
+    if (w->f && locate(&w->f->sr_cur.p, p, &pl, x, y)) return pl;
+    return -1;
+}
+
 int eav1rec_locate_ref(const Eav1Walk *w, const void *p, int *plane, int *x, int *y)
 {
     const Dav1dFrameContext *f = w->f;
@@ -405,6 +412,7 @@ struct Eav1Job {
     uint8_t *lf_level; size_t cap_level;
     uint8_t *lf_mask; size_t cap_mask;
     Eav1PicData *cur, *ref[7];
+    Eav1PicData *coded;                 /* super-resolution: the coded-width picture (cur is the upscaled one) */
     void *cur_data[3]; ptrdiff_t cur_stride[2];
 };
 
@@ -415,7 +423,7 @@ static Eav1Job *job_get(Eav1Rec *r)
     if (j) r->job_free = j->next;
     pthread_mutex_unlock(&r->q_mu);
     if (!j) { j = calloc(1, sizeof(*j)); if (!j) abort(); }
-    j->next = NULL; j->skip = 0; j->cur = NULL;
+    j->next = NULL; j->skip = 0; j->cur = NULL; j->coded = NULL;
     memset(j->ref, 0, sizeof(j->ref));
     j->n_cmds = j->n_payload = j->n_lf = j->n_lr = 0;
     return j;
@@ -476,9 +484,13 @@ void eav1rec_frame_end(Eav1Rec *r, const Dav1dFrameContext *f, int retval)
     Eav1Job *j = job_get(r);
     j->seq = seq;
     const Dav1dFrameHeader *const hdr = f->frame_hdr;
-    Eav1PicData *cur = pd_of(&f->cur);
+    /* `cur` is the picture that is shown and referenced: f->sr_cur, which is f->cur itself unless the frame is
+     * super-resolved (decode.c:3524-3529); `coded` is where reconstruction, deblocking and CDEF happen */
+    const int superres = hdr && hdr->width[0] != hdr->width[1];
+    Eav1PicData *coded = pd_of(&f->cur);
+    Eav1PicData *cur = superres ? pd_of(&f->sr_cur.p) : coded;
+    if (!coded) cur = NULL;
     int unsupported = atomic_load(&r->unsupported) || atomic_load(&fr->unsupported);
-    if (!retval && hdr && hdr->width[0] != hdr->width[1]) unsupported = 1;   /* super-res: not yet */
     j->skip = retval != 0 || !cur || !hdr || unsupported;
     if (!retval && unsupported && cur) {
         fprintf(stderr, "easyav1_b200: unsupported coding tool in stream (no CPU fallback)\n");
@@ -494,18 +506,26 @@ void eav1rec_frame_end(Eav1Rec *r, const Dav1dFrameContext *f, int retval)
         fd->layout = f->cur.p.layout;
         fd->bw4 = f->bw; fd->bh4 = f->bh;
         fd->sb128 = f->seq_hdr->sb128;
-        fd->cur = cur->dev_id;
+        fd->cur = coded->dev_id;
         j->cur = cur;
         atomic_fetch_add(&cur->refs, 1);
         atomic_store(&cur->fence, FENCE_PENDING);
+        if (superres) {
+            j->coded = coded;
+            atomic_fetch_add(&coded->refs, 1);
+            fd->superres = 1;
+            fd->sr_pic = cur->dev_id;
+            fd->sr_w = f->sr_cur.p.p.w;
+            for (int i = 0; i < 2; i++) { fd->resize_step[i] = f->resize_step[i]; fd->resize_start[i] = f->resize_start[i]; }
+        }
         for (int i = 0; i < 7; i++) {
             Eav1PicData *rp = IS_INTER_OR_SWITCH(hdr) ? pd_of(&f->refp[i].p) : NULL;
             fd->ref[i] = rp ? rp->dev_id : -1;
             j->ref[i] = rp;
             if (rp) atomic_fetch_add(&rp->refs, 1);
         }
-        for (int i = 0; i < 3; i++) j->cur_data[i] = f->cur.data[i];
-        j->cur_stride[0] = f->cur.stride[0]; j->cur_stride[1] = f->cur.stride[1];
+        for (int i = 0; i < 3; i++) j->cur_data[i] = f->sr_cur.p.data[i];
+        j->cur_stride[0] = f->sr_cur.p.stride[0]; j->cur_stride[1] = f->sr_cur.p.stride[1];
         /* output_image (lib.c:311-330) hands out a grain-synthesised copy, never this picture */
         j->no_download = f->c->apply_grain && has_grain(hdr);
         /* command lists: tiles are independent in reconstruction, so any tile order is legal */
@@ -620,7 +640,8 @@ static void *submit_main(void *arg)
             if (!res)
                 res = eav1cu_frame_submit(r->cu, &j->fd, j->cmds, j->n_cmds, j->payload, j->n_payload, j->arena_bytes);
             unsigned long long ticket = 0;
-            if (!res && !j->no_download) res = eav1cu_pic_download_async(r->cu, j->fd.cur, j->cur_data, j->cur_stride);
+            if (!res && !j->no_download)
+                res = eav1cu_pic_download_async(r->cu, j->fd.superres ? j->fd.sr_pic : j->fd.cur, j->cur_data, j->cur_stride);
             if (!res) res = eav1cu_fence(r->cu, &ticket);
             if (!res && sync_each) res = eav1cu_sync(r->cu);
             pthread_mutex_unlock(&r->cu_mu);
@@ -647,6 +668,7 @@ static void *submit_main(void *arg)
             const unsigned long long t = atomic_load(&cur->fence);
             if (atomic_load(&cur->refs) == 1 && t) eav1cu_fence_wait(r->cu, t);
             pd_unref(cur);
+            if (j->coded) pd_unref(j->coded);
             for (int i = 0; i < 7; i++) if (j->ref[i]) pd_unref(j->ref[i]);
         }
         if (timing) {

@@ -264,11 +264,14 @@ static void rec_blend_dir(int op, pixel *dst, int w, int h)
 static void rec_blend_v(pixel *dst, ptrdiff_t ds, const pixel *tmp, int w, int h) { (void)ds; (void)tmp; rec_blend_dir(EAV1_OP_BLEND_V, dst, w, h); }
 static void rec_blend_h(pixel *dst, ptrdiff_t ds, const pixel *tmp, int w, int h) { (void)ds; (void)tmp; rec_blend_dir(EAV1_OP_BLEND_H, dst, w, h); }
 
+/* mc.resize has two callers: dav1d_filter_sbrow_resize (recon_tmpl.c:2053), replaced below, and backup_lpf inside
+ * dav1d_copy_lpf (lf_apply_tmpl.c:76-88), replaced by a no-op. Both upscales run on the device as whole-frame
+ * launches (Eav1FrameDesc.superres), so nothing may arrive here. */
 static void rec_resize(pixel *dst, ptrdiff_t ds, const pixel *src, ptrdiff_t ss, int dst_w, int h, int src_w, int dx, int mx HIGHBD_DECL_SUFFIX)
 {
     REC();
     (void)dst; (void)ds; (void)src; (void)ss; (void)dst_w; (void)h; (void)src_w; (void)dx; (void)mx;
-    UNSUPPORTED(r); /* super-resolution: not yet on the device */
+    UNSUPPORTED(r);
 }
 
 void bitfn(eav1rec_mc_dsp_init)(Dav1dMCDSPContext *const c)
@@ -456,7 +459,9 @@ static void rec_lr_any(const int kind, pixel *dst, int w, int h, const Loopresto
 {
     REC();
     int x, y;
-    const int pl = eav1rec_locate_cur(r, dst, &x, &y);
+    /* loop restoration works on the super-resolved picture (lr_apply_tmpl.c: f->sr_cur), which is f->cur itself
+     * unless the frame uses super-resolution */
+    const int pl = eav1rec_locate_sr(r, dst, &x, &y);
     if (pl < 0) { UNSUPPORTED(r); return; }
     Eav1LrRec v, *lr = &v;
     memset(&v, 0, sizeof(v));
@@ -520,7 +525,7 @@ void bitfn(eav1rec_copy_lpf)(Dav1dFrameContext *const f, pixel *const src[3], co
 
 /* The post-filter stages as dav1d's task scheduler calls them one by one (thread_task.c:809-864).
  * Deblocking and loop-restoration drivers of the reference run against the recording tables;
- * CDEF is driven on the device from the frame's Av1Filter array; super-res is not run yet. */
+ * CDEF and the super-resolution upscale are driven on the device as whole-frame stages. */
 void bitfn(eav1rec_filter_sbrow_deblock_cols)(Dav1dFrameContext *const f, const int sby)
 {
     eav1rec_enter(f, NULL);
@@ -532,12 +537,8 @@ void bitfn(eav1rec_filter_sbrow_deblock_rows)(Dav1dFrameContext *const f, const 
     bitfn(eav1ref_filter_sbrow_deblock_rows)(f, sby);
 }
 void bitfn(eav1rec_filter_sbrow_cdef)(Dav1dTaskContext *const tc, const int sby) { (void)tc; (void)sby; }
-void bitfn(eav1rec_filter_sbrow_resize)(Dav1dFrameContext *const f, const int sby)
-{
-    (void)sby;
-    Eav1Walk *w = eav1rec_enter(f, NULL);
-    atomic_store(&w->fr->unsupported, 1);
-}
+/* super-resolution is one whole-frame stage of the engine (Eav1FrameDesc.superres, filled in eav1rec_frame_end) */
+void bitfn(eav1rec_filter_sbrow_resize)(Dav1dFrameContext *const f, const int sby) { (void)f; (void)sby; }
 void bitfn(eav1rec_filter_sbrow_lr)(Dav1dFrameContext *const f, const int sby)
 {
     eav1rec_enter(f, NULL);
@@ -551,7 +552,6 @@ void bitfn(eav1rec_filter_sbrow)(Dav1dFrameContext *const f, const int sby)
     Eav1Walk *w = eav1rec_enter(f, NULL);
     bitfn(eav1ref_filter_sbrow_deblock_cols)(f, sby);
     bitfn(eav1ref_filter_sbrow_deblock_rows)(f, sby);
-    if (f->frame_hdr->width[0] != f->frame_hdr->width[1]) atomic_store(&w->fr->unsupported, 1);
     if (f->lf.restore_planes) bitfn(eav1ref_filter_sbrow_lr)(f, sby);
     if (sby == f->sbh - 1) eav1rec_frame_end(w->r, f, 0);
 }

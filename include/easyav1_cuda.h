@@ -194,6 +194,14 @@ typedef struct Eav1FrameDesc {
     int sb128w, sb128h;
     /* loop restoration */
     const Eav1LrRec *lr_recs; size_t n_lr_recs;
+    /* super-resolution (frame_hdr->super_res.enabled, width[0] != width[1]): reconstruction, deblocking and
+     * CDEF run at the coded width in picture `cur`; mc.resize (mc_tmpl.c:918-955, driven by
+     * dav1d_filter_sbrow_resize, recon_tmpl.c:2053-2086) then upscales every row into picture `sr_pic`
+     * (sr_w luma samples wide), where loop restoration runs (its records are in sr_pic coordinates; the
+     * stripe-border rows are the resized deblocked rows, lf_apply_tmpl.c:76-88). sr_pic receives the final
+     * frame and is what later frames reference. superres == 0: everything happens in `cur`. */
+    int superres, sr_pic, sr_w;
+    int resize_step[2], resize_start[2];   /* f->resize_step / f->resize_start (decode.c:3532-3539): luma, chroma */
 } Eav1FrameDesc;
 
 /* ---- lifecycle ------------------------------------------------------------------------ */
@@ -273,6 +281,32 @@ int  eav1cu_plan_tickets(const Eav1Cmd *cmds, size_t n_cmds, const int plane_w[3
 /* out[0] kernel launches, out[1] host->device bytes, out[2] device->host bytes, out[3] frames */
 int  eav1cu_counters(Eav1cuCtx *ctx, long long out[4]);
 int  eav1cu_set_capture(Eav1cuCtx *ctx, int on);
+/* Test support: which coding tools the frames submitted by this process exercised. Counting is on only when
+ * EAV1_COVERAGE is set in the environment when the library is first used (eav1cu_coverage then returns 1,
+ * else 0 and zeros). Indices: bit depth 0/1/2 = 8/10/12 bits, `hbd` 0/1 = 8-bit / high bit depth;
+ * tx = enum RectTxfmSize, txtp = enum TxfmType (16 = WHT_WHT), mode = the implementation intra mode
+ * (ext/dav1d/src/levels.h); w / h as floor(log2). */
+typedef struct Eav1Coverage {
+    uint64_t frames[3], layout[4];
+    uint64_t itx[3][19][17];            /* [bit depth][tx][txtp] */
+    uint64_t itx_eob[3][3];             /* [bit depth][dc-only shortcut / eob < 10 / larger] */
+    uint64_t mc[2][2][2][4][4][4];      /* [hbd][scaled][prep][filt_h][filt_v][bit0 mx != 0, bit1 my != 0; scaled: 3] */
+    uint64_t mc_wh[2][8][8];            /* [scaled][w][h] */
+    uint64_t intrabc;
+    uint64_t warp[2][2];                /* [hbd][put / prep] */
+    uint64_t comp[2][4];                /* [hbd][avg, w_avg, mask, w_mask] */
+    uint64_t w_mask_ss[3];              /* 4:4:4, 4:2:2, 4:2:0 */
+    uint64_t blend[2][3];               /* [hbd][blend, blend_v, blend_h] */
+    uint64_t ipred[3][14];              /* [bit depth][mode] */
+    uint64_t ipred_wh[8][8];
+    uint64_t cfl[2][14];                /* [hbd][mode] */
+    uint64_t pal[2];
+    uint64_t lf[2][2][2][3];            /* [hbd][chroma][dir][filter size class]: 4-sample edge units */
+    uint64_t lr[2][5];                  /* [hbd][EAV1_LR_*] recorded calls */
+    uint64_t cdef_frames[2], superres_frames[2];
+    uint64_t grain[2][2];               /* [hbd][chroma scaled from luma] eav1cu_apply_grain calls */
+} Eav1Coverage;
+int  eav1cu_coverage(Eav1Coverage *out, int reset);
 /* Per-stage device time (CUDA events on the context's stream around each stage of every
  * frame): index 0 dataflow reconstruction (intra, residual, compound/blend), 1 deblock, 2 CDEF,
  * 3 loop restoration, 4 motion compensation, 5 film grain, 6 inverse-transform residuals. Each array has EAV1CU_N_STAGES entries: accumulated

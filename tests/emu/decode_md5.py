@@ -9,8 +9,13 @@ from easyav1_b200.lib import load_host, EngineError
 from easyav1_b200.decoder import Decoder
 from tests.golden.gen_fixtures import read_ivf
 
-man = json.load(open(os.path.join(ROOT, "tests/golden/manifest.json")))[sys.argv[1]]
-obu = b"".join(read_ivf(os.path.join(ROOT, "tests/golden", man["file"])))
+if sys.argv[1].startswith("syn_"):     # synthetic stream, rebuilt from its seed (tests/golden/synth_streams.py)
+    from tests.golden import synth_streams
+    obu, _ = synth_streams.build(sys.argv[1])
+    man = {"w": 3840, "h": 2160}
+else:
+    man = json.load(open(os.path.join(ROOT, "tests/golden/manifest.json")))[sys.argv[1]]
+    obu = b"".join(read_ivf(os.path.join(ROOT, "tests/golden", man["file"])))
 if len(sys.argv) > 2:
     obu = obu[: int(len(obu) * float(sys.argv[2]))]
 host = load_host(os.path.join(ROOT, "tests/emu/libdav1d_b200_emu.so"))

@@ -20,6 +20,7 @@
 #include "../../easyav1_b200/csrc/sched.h"
 #include "../../easyav1_b200/csrc/postfilter.cuh"
 #include "../../easyav1_b200/csrc/filmgrain.cuh"
+#include "../../easyav1_b200/csrc/coverage.h"
 
 using namespace eav1;
 
@@ -36,7 +37,7 @@ struct Eav1cuCtx {
     std::vector<uint8_t> masks;
     std::vector<Picture> pics;
     std::vector<uint8_t> arena;
-    Picture work[2];
+    Picture work[4];
     long long launches = 0;
     int err = 0;
 };
@@ -133,6 +134,7 @@ int eav1cu_frame_submit(Eav1cuCtx *c, const Eav1FrameDesc *fd, const Eav1Cmd *cm
                         const void *payload, size_t, size_t arena_bytes)
 {
     if (!c->have_tab) return EAV1CU_ERR_NOTABLES;
+    coverage_count(fd, cmds, n);
     if (getenv("EAV1_EMU_NULL")) {  // host-cost profiling: record only
         static size_t tot_cmds, tot_lf, tot_lr, frames;
         tot_cmds += n; tot_lf += fd->n_lf_recs; tot_lr += fd->n_lr_recs; frames++;
@@ -184,7 +186,11 @@ int eav1cu_frame_submit(Eav1cuCtx *c, const Eav1FrameDesc *fd, const Eav1Cmd *cm
     Picture &cur = c->pics[fd->cur];
     const bool has_cdef = fd->cdef_enable != 0, has_lr = fd->n_lr_recs > 0;
     Picture *A = &cur;
-    if (has_cdef || has_lr) {
+    if (fd->superres) {
+        const Picture &sr = c->pics[fd->sr_pic];
+        if (has_cdef) pic_setup(c->work[1], cur.w, cur.h, cur.layout, cur.bpc);
+        if (has_lr) { pic_setup(c->work[2], sr.w, sr.h, sr.layout, sr.bpc); if (has_cdef) pic_setup(c->work[3], sr.w, sr.h, sr.layout, sr.bpc); }
+    } else if (has_cdef || has_lr) {
         pic_setup(c->work[0], cur.w, cur.h, cur.layout, cur.bpc);
         if (has_cdef && has_lr) pic_setup(c->work[1], cur.w, cur.h, cur.layout, cur.bpc);
         A = &c->work[0];
@@ -234,9 +240,12 @@ int eav1cu_frame_submit(Eav1cuCtx *c, const Eav1FrameDesc *fd, const Eav1Cmd *cm
     return emu_postfilter(c, fd, *A, cur);
 }
 
+int eav1cu_coverage(Eav1Coverage *out, int reset) { return coverage_read(out, reset); }
+
 int eav1cu_apply_grain(Eav1cuCtx *c, int src_pic, int dst_pic, const Eav1GrainParams *g)
 {
     const Picture &src = c->pics[src_pic], &dst = c->pics[dst_pic];
+    coverage_count_grain(src.bpc, g);
     static std::vector<uint8_t> buf(36864 + 3 * 4096 + 65536);
     static FgSmem sm;
     FgParams P;

@@ -25,6 +25,53 @@ using namespace eav1;
 // Launch epochs are unique across every context of the process: a done-flag array that lands on
 // memory a destroyed context used can then never hold a value that looks current.
 static std::atomic<uint32_t> g_epoch{0};
+// process-wide totals over every context (eav1cu_global_counters): launches, host->device bytes, device->host bytes, frames
+static std::atomic<long long> g_total[4];
+
+// Many decoders of one process submit frames from their own threads. The CUDA calls of one frame (a copy, about ten
+// launches, a few event records) are short; issued from many threads at once they queue up inside the driver and
+// every call becomes slow for everybody. One process-wide lock around each frame's burst of calls keeps them
+// back to back (measured with 16 streams on one B200: see DESIGN.md); the CPU work of plan_build stays outside.
+// EAV1_TIMING=1: per call-site totals of the CUDA runtime calls on the frame path, printed when the process exits
+// (development aid for the multi-stream host path).
+enum { TC_SETDEV, TC_H2D_PACK, TC_PIC_COPY, TC_EVREC, TC_EVSYNC_SLOT, TC_EVSYNC_FENCE, TC_WAITEV, TC_D2D, TC_ALLOC, TC_LAUNCHES, TC_N };
+struct CallStats {
+    std::atomic<long long> n[TC_N], ns[TC_N], mx[TC_N];
+    const bool on = getenv("EAV1_TIMING") != nullptr;
+    ~CallStats() {
+        if (!on) return;
+        static const char *nm[TC_N] = { "cudaSetDevice", "cudaMemcpyAsync (packed lists)", "picture copy", "cudaEventRecord", "cudaEventSynchronize (slot)",
+                                        "cudaEventSynchronize (fence)", "cudaStreamWaitEvent", "cudaMemcpyAsync D2D", "cudaMalloc/Free/HostAlloc", "kernel launches of a frame" };
+        for (int i = 0; i < TC_N; i++)
+            if (n[i]) fprintf(stderr, "EAV1 TIMING: %-34s %9lld calls, mean %8.1f us, max %9.1f us, total %8.1f ms\n", nm[i], (long long)n[i],
+                              1e-3 * ns[i] / n[i], 1e-3 * mx[i], 1e-6 * ns[i]);
+    }
+    void add(int i, long long d) {
+        n[i]++; ns[i] += d;
+        long long m = mx[i];
+        while (d > m && !mx[i].compare_exchange_weak(m, d)) {}
+    }
+};
+static CallStats g_calls;
+struct CallTimer {
+    int i; std::chrono::steady_clock::time_point t0;
+    explicit CallTimer(int idx) : i(idx) { if (g_calls.on) t0 = std::chrono::steady_clock::now(); }
+    ~CallTimer() { if (g_calls.on) g_calls.add(i, std::chrono::duration_cast<std::chrono::nanoseconds>(std::chrono::steady_clock::now() - t0).count()); }
+};
+#define TCK(idx, call) do { CallTimer ct_(idx); CK(call); } while (0)
+
+// Host threads that wait for a frame (dav1d_get_picture -> eav1cu_fence_wait) sleep instead of spinning inside the
+// driver: with many decoders per process the spinning waiters slow every CUDA call of the submitting threads down.
+// EAV1_SPIN_WAIT=1 restores the default (lowest wake-up latency, single stream).
+static const unsigned g_event_flags = cudaEventDisableTiming | (getenv("EAV1_SPIN_WAIT") ? 0 : cudaEventBlockingSync);
+
+struct SubmitMutex {      // EAV1_NO_SUBMIT_LOCK=1 turns it off (A/B measurements)
+    std::mutex m;
+    const bool on = getenv("EAV1_NO_SUBMIT_LOCK") == nullptr;
+    void lock() { if (on) m.lock(); }
+    void unlock() { if (on) m.unlock(); }
+};
+static SubmitMutex g_submit_mu;
 
 // ------------------------------------------------------------------ kernels
 
@@ -209,6 +256,38 @@ recon_frame_kernel(FrameCtx fc, ReconArgs ra)
     }
 }
 
+// Phase 2a: dataflow units without any producer inside the frame (on inter frames nearly all of them: the residual
+// add on top of a finished motion-compensated block, the average / mask of two prep blocks, ...). They need no
+// tickets and no flags: one warp per unit of at most 32x32 samples, one CTA per larger one, a plain grid.
+// units[i] = (first command, number of commands); the large units lead the grid.
+template <typename BD>
+__global__ void __launch_bounds__(128, EAV1_RECON_MIN_CTAS)
+flat_units_kernel(FrameCtx fc, const Eav1Cmd *__restrict__ cmds, const uint2 *__restrict__ units, uint32_t n_big, uint32_t n_small)
+{
+    __shared__ alignas(16) unsigned char scratch[4 * EAV1_WARP_SCRATCH > sizeof(CtaScratch) ? 4 * EAV1_WARP_SCRATCH : sizeof(CtaScratch)];
+    __shared__ Eav1Cmd cmd[4][2];
+    int tid, nthr, w;
+    uint2 u;
+    if (blockIdx.x < n_big) {
+        tid = threadIdx.x; nthr = 128; w = 0;
+        u = units[blockIdx.x];
+    } else {
+        w = threadIdx.x >> 5; tid = threadIdx.x & 31; nthr = 32;
+        const uint32_t it = (blockIdx.x - n_big) * 4 + w;
+        if (it >= n_small) return;
+        u = units[n_big + it];
+    }
+    CtaScratch &sm = *reinterpret_cast<CtaScratch *>(scratch + (nthr == 32 ? w * EAV1_WARP_SCRATCH : 0));
+    for (uint32_t c = 0; c < u.y;) {
+        const uint32_t n = min(u.y - c, 2u);
+        for (uint32_t i = tid; i < n * (sizeof(Eav1Cmd) / 4); i += nthr)
+            reinterpret_cast<uint32_t *>(&cmd[w][0])[i] = reinterpret_cast<const uint32_t *>(&cmds[u.x + c])[i];
+        CTA_SYNC();
+        c += exec_cmd<BD>(fc, cmd[w][0], sm, tid, nthr, n > 1 ? &cmd[w][1] : nullptr);
+        CTA_SYNC();
+    }
+}
+
 // Phase 1: motion compensation from reference pictures. One warp per work item (a block or a
 // 32x32 tile of it); items are independent, so this is a plain grid with no flags or tickets.
 template <typename BD>
@@ -364,6 +443,8 @@ struct FramePlan {
     uint32_t n_ritems = 0, n_ritems_small = 0;   // two-step transform blocks (phase 1b)
     long long resid_px = 0;
     const ChainRec *d_recs = nullptr;
+    const uint2 *d_flat = nullptr;               // producer-free units: (first command, count), large ones first
+    uint32_t n_flat_big = 0, n_flat_small = 0;
     uint32_t n_items = 0;
     long long mc_px = 0, unit_px = 0;
     uint32_t n_chains = 0, n_deps = 0, n_levels = 0, n_big = 0, n_small = 0;
@@ -381,7 +462,7 @@ struct FramePlan {
 // Per-frame upload buffers exist twice: while the kernels of frame k still read slot k&1, the
 // host already fills the other slot for frame k+1 (the `done` event guards reuse two frames later).
 struct Slot {
-    DevBuf cmds, payload, lfrec, lflvl, lrrec, lfmask, deps, recs, items, ritems;
+    DevBuf stage;   // every list of the frame, packed (one host->device copy)
     cudaEvent_t done = nullptr;
     bool used = false;
 };
@@ -407,7 +488,10 @@ struct Eav1cuCtx {
     Scheduler sched;
     DepGraph graph;
     Schedule plan;
-    UnitGraph units;
+    UnitGraph units, units2;      // all phase-2 units / those that wait for or feed another unit
+    std::vector<uint2> flat_tmp;
+    std::vector<uint8_t> stage_tmp;
+    std::vector<uint32_t> remap_tmp;
     std::vector<ChainRec> rec_tmp;
     std::vector<uint8_t> fed_tmp;
     uint32_t *d_done = nullptr; size_t done_cap = 0;
@@ -417,6 +501,7 @@ struct Eav1cuCtx {
     int recon_grid = 148 * 4;
     int debug_check = 0;
     double t_build = 0, t_launch = 0, t_wait = 0;   // host seconds spent in frame_submit (EAV1_TIMING)
+    double t_sched = 0, t_pack = 0, t_lock = 0, t_copycall = 0;   // inside plan_build: dependency graph, memcpy into staging, wait for the submit lock, the copy call
     unsigned long long *d_sums = nullptr;   // [frame & 63][2]: device checksums of payload / cmds
     unsigned long long h_sums[64][2] = {};  // host checksums of the same uploads
     long long sum_frame[64] = {};
@@ -425,11 +510,14 @@ struct Eav1cuCtx {
     std::vector<uint32_t> ritem_tmp2;
     unsigned long long *d_trace = nullptr;   // set only inside eav1cu_staged_trace
     int est_weight = 8;           // ticket key = est_weight * est - tail (EAV1_EST_WEIGHT; any weight >= 1 keeps the order topological)
+    bool no_flat = true;          // unless EAV1_FLAT is set every phase-2 unit goes through the dataflow kernel: the separate flat launch
+                                  // for producer-free units measured slower on one stream (recon 8.7 -> 10.4 ms per 120 frames, one more
+                                  // launch per frame, same critical chain) and no faster with several streams
     bool serial_phase1 = false;   // EAV1_SERIAL_PHASE1: residuals on the main stream (profiling, debugging)
     int warp_mode = 0;   // 0: every chain on a CTA, 1: independent small chains on warps, 2: all small chains on warps
     int err = 0;
     std::string errmsg;
-    std::mutex mu;
+    std::mutex mu, err_mu;      // mu: picture pool; err_mu: err / errmsg (fail() is reached from any thread)
     long long n_launches = 0, h2d_bytes = 0, d2h_bytes = 0, n_frames = 0;
     bool own_stream = true;
     cudaStream_t stream2 = nullptr;            // phase 1b (residuals) runs beside phase 1 (motion compensation)
@@ -448,6 +536,8 @@ struct Eav1cuCtx {
 
 static int fail(Eav1cuCtx *c, int code, const char *what, cudaError_t e = cudaSuccess)
 {
+    std::unique_lock<std::mutex> g;
+    if (c) g = std::unique_lock<std::mutex>(c->err_mu);
     if (c && !c->err) {
         c->err = code;
         c->errmsg = what;
@@ -459,6 +549,8 @@ static int fail(Eav1cuCtx *c, int code, const char *what, cudaError_t e = cudaSu
 
 static int ensure(Eav1cuCtx *ctx, DevBuf &b, size_t bytes, bool pinned_too)
 {
+    if (bytes <= b.cap && (!pinned_too || bytes <= b.hcap)) return 0;
+    CallTimer ct_(TC_ALLOC);
     if (bytes > b.cap) {
         if (b.d) cudaFree(b.d);
         size_t cap = bytes + bytes / 2 + 4096;
@@ -481,17 +573,6 @@ static void free_buf(DevBuf &b)
     b = DevBuf();
 }
 
-static int upload(Eav1cuCtx *ctx, DevBuf &b, const void *src, size_t bytes)
-{
-    if (!bytes) return 0;
-    int r = ensure(ctx, b, bytes, true);
-    if (r) return r;
-    memcpy(b.h, src, bytes);
-    CK(cudaMemcpyAsync(b.d, b.h, bytes, cudaMemcpyHostToDevice, ctx->stream));
-    ctx->h2d_bytes += (long long)bytes;
-    return 0;
-}
-
 static int pic_setup(Eav1cuCtx *ctx, Picture &p, int w, int h, int layout, int bpc)
 {
     const int hbd = bpc > 8;
@@ -502,8 +583,8 @@ static int pic_setup(Eav1cuCtx *ctx, Picture &p, int w, int h, int layout, int b
     const size_t ystride = (size_t)aw << hbd, cstride = (size_t)cw << hbd;
     const size_t ybytes = ystride * ah, cbytes = cstride * chh;
     const size_t total = ybytes + 2 * cbytes + 256;
-    if (p.base && p.bytes < total) { cudaFree(p.base); p.base = nullptr; }
-    if (!p.base) { CK(cudaMalloc(&p.base, total)); p.bytes = total; }
+    if (p.base && p.bytes < total) { CallTimer ct_(TC_ALLOC); cudaFree(p.base); p.base = nullptr; }
+    if (!p.base) { CallTimer ct_(TC_ALLOC); CK(cudaMalloc(&p.base, total)); p.bytes = total; }
     p.w = w; p.h = h; p.layout = layout; p.bpc = bpc;
     p.pl[0].p = p.base; p.pl[0].stride = (int)ystride; p.pl[0].w = aw; p.pl[0].h = ah;
     p.pl[1].p = p.base + ybytes; p.pl[1].stride = (int)cstride; p.pl[1].w = cw; p.pl[1].h = chh;
@@ -527,7 +608,7 @@ int eav1cu_device_count(void)
 // stream, staging buffers and device pictures already allocated.
 static std::mutex g_cache_mu;
 static std::vector<Eav1cuCtx *> g_cache;
-static const size_t MAX_CACHED_CTX = 4;
+static const size_t MAX_CACHED_CTX = 96;   // a 64-stream server re-opening its decoders finds all of them (bench config C5)
 
 int eav1cu_ctx_create(Eav1cuCtx **out, int device)
 {
@@ -568,6 +649,7 @@ int eav1cu_ctx_create(Eav1cuCtx **out, int device)
     }
     if (const char *e = getenv("EAV1_WARP_MODE")) ctx->warp_mode = atoi(e);
     ctx->serial_phase1 = getenv("EAV1_SERIAL_PHASE1") != nullptr;
+    ctx->no_flat = getenv("EAV1_FLAT") == nullptr;
     if (const char *e = getenv("EAV1_EST_WEIGHT")) ctx->est_weight = std::max(1, std::min(16, atoi(e)));
     if (!ctx->stream2) {
         if (cudaStreamCreateWithFlags(&ctx->stream2, cudaStreamNonBlocking) != cudaSuccess ||
@@ -594,8 +676,7 @@ static void ctx_free(Eav1cuCtx *ctx)
     for (auto &p : ctx->work) if (p.base) cudaFree(p.base);
     free_buf(ctx->arena);
     for (Slot &sl : ctx->slot) {
-        free_buf(sl.cmds); free_buf(sl.payload); free_buf(sl.lfrec); free_buf(sl.lflvl); free_buf(sl.lrrec);
-        free_buf(sl.lfmask); free_buf(sl.deps); free_buf(sl.recs); free_buf(sl.items); free_buf(sl.ritems);
+        free_buf(sl.stage);
         if (sl.done) cudaEventDestroy(sl.done);
     }
     for (cudaEvent_t e : ctx->fence_ev) if (e) cudaEventDestroy(e);
@@ -622,7 +703,10 @@ void eav1cu_ctx_destroy(Eav1cuCtx *ctx)
     bool keep = ctx->own_stream && !ctx->err && !getenv("EAV1_NO_CTX_CACHE");
     if (keep) {
         // back to a just-created state, keeping every allocation
-        if (getenv("EAV1_TIMING")) { ctx_free(ctx); return; }
+        if (getenv("EAV1_TIMING") && ctx->n_frames)
+            fprintf(stderr, "EAV1 TIMING: %lld frames; per frame on the submitting thread: slot wait %.3f ms, plan build + uploads %.3f ms (graph %.3f, pack %.3f, lock wait %.3f, copy call %.3f), launches %.3f ms\n",
+                    ctx->n_frames, 1e3 * ctx->t_wait / ctx->n_frames, 1e3 * ctx->t_build / ctx->n_frames, 1e3 * ctx->t_sched / ctx->n_frames,
+                    1e3 * ctx->t_pack / ctx->n_frames, 1e3 * ctx->t_lock / ctx->n_frames, 1e3 * ctx->t_copycall / ctx->n_frames, 1e3 * ctx->t_launch / ctx->n_frames);
         for (FramePlan *sp : ctx->staged) { for (void *d : sp->owned) cudaFree(d); delete sp; }
         ctx->staged.clear();
         for (auto &p : ctx->pics) p.used = false;
@@ -633,6 +717,7 @@ void eav1cu_ctx_destroy(Eav1cuCtx *ctx)
         for (int i = 0; i < EAV1CU_N_STAGES; i++) { ctx->stage_ms[i] = 0; ctx->stage_launches[i] = 0; ctx->stage_calls[i] = 0; }
         ctx->n_launches = ctx->h2d_bytes = ctx->d2h_bytes = ctx->n_frames = 0;
         ctx->t_build = ctx->t_launch = ctx->t_wait = 0;
+        ctx->t_sched = ctx->t_pack = ctx->t_lock = ctx->t_copycall = 0;
         std::lock_guard<std::mutex> g(g_cache_mu);
         if (g_cache.size() < MAX_CACHED_CTX) { g_cache.push_back(ctx); return; }
     }
@@ -642,13 +727,23 @@ void eav1cu_ctx_destroy(Eav1cuCtx *ctx)
 int eav1cu_last_error(Eav1cuCtx *ctx, char *msg, size_t cap)
 {
     if (!ctx) return EAV1CU_ERR_INVAL;
+    std::lock_guard<std::mutex> g(ctx->err_mu);
     if (msg && cap) snprintf(msg, cap, "%s", ctx->errmsg.c_str());
+    return ctx->err;
+}
+
+int eav1cu_clear_error(Eav1cuCtx *ctx)
+{
+    if (!ctx) return EAV1CU_ERR_INVAL;
+    std::lock_guard<std::mutex> g(ctx->err_mu);
+    if (ctx->err == EAV1CU_ERR_INVAL) { ctx->err = 0; ctx->errmsg.clear(); }
     return ctx->err;
 }
 
 int eav1cu_host_alloc(void **p, size_t bytes)
 {
     if (!p) return EAV1CU_ERR_INVAL;
+    CallTimer ct_(TC_ALLOC);
     return cudaHostAlloc(p, bytes, cudaHostAllocPortable) == cudaSuccess ? 0 : EAV1CU_ERR_NOMEM;
 }
 
@@ -718,10 +813,23 @@ static int pic_copy(Eav1cuCtx *ctx, int id, void *const data[3], const ptrdiff_t
     Picture &p = ctx->pics[id];
     const int hbd = p.bpc > 8;
     const int ss_hor = p.layout != 3, ss_ver = p.layout == 1;
-    for (int pl = 0; pl < (p.layout ? 3 : 1); pl++) {
+    std::unique_lock<SubmitMutex> g(g_submit_mu);
+    // The host picture usually has the device picture's geometry (same strides, planes the same distance apart:
+    // both follow dav1d's allocation rule): then the whole picture is one contiguous copy instead of three 2-D ones.
+    const int np = p.layout ? 3 : 1;
+    bool same = stride[0] == p.pl[0].stride && (np == 1 || stride[1] == p.pl[1].stride);
+    for (int pl = 1; pl < np && same; pl++)
+        same = (const uint8_t *)data[pl] - (const uint8_t *)data[0] == p.pl[pl].p - p.pl[0].p;
+    if (same) {
+        const int lw = np == 1 ? p.w : (p.w + ss_hor) >> ss_hor, lh = np == 1 ? p.h : (p.h + ss_ver) >> ss_ver;
+        const size_t bytes = (size_t)(p.pl[np - 1].p - p.pl[0].p) + (size_t)p.pl[np - 1].stride * (lh - 1) + ((size_t)lw << hbd);
+        if (to_device) { ctx->h2d_bytes += (long long)bytes; TCK(TC_PIC_COPY, cudaMemcpyAsync(p.pl[0].p, data[0], bytes, cudaMemcpyHostToDevice, ctx->stream)); }
+        else { ctx->d2h_bytes += (long long)bytes; g_total[2] += (long long)bytes; TCK(TC_PIC_COPY, cudaMemcpyAsync(data[0], p.pl[0].p, bytes, cudaMemcpyDeviceToHost, ctx->stream)); }
+    } else
+    for (int pl = 0; pl < np; pl++) {
         const int w = pl ? (p.w + ss_hor) >> ss_hor : p.w;
         const int h = pl ? (p.h + ss_ver) >> ss_ver : p.h;
-        if (to_device) ctx->h2d_bytes += ((long long)w << hbd) * h; else ctx->d2h_bytes += ((long long)w << hbd) * h;
+        if (to_device) ctx->h2d_bytes += ((long long)w << hbd) * h; else { ctx->d2h_bytes += ((long long)w << hbd) * h; g_total[2] += ((long long)w << hbd) * h; }
         if (to_device)
             CK(cudaMemcpy2DAsync(p.pl[pl].p, p.pl[pl].stride, data[pl], stride[!!pl], (size_t)w << hbd, h,
                                  cudaMemcpyHostToDevice, ctx->stream));
@@ -729,6 +837,7 @@ static int pic_copy(Eav1cuCtx *ctx, int id, void *const data[3], const ptrdiff_t
             CK(cudaMemcpy2DAsync(data[pl], stride[!!pl], p.pl[pl].p, p.pl[pl].stride, (size_t)w << hbd, h,
                                  cudaMemcpyDeviceToHost, ctx->stream));
     }
+    g.unlock();
     if (wait) CK(cudaStreamSynchronize(ctx->stream));
     return ctx->err;
 }
@@ -745,9 +854,12 @@ int eav1cu_fence(Eav1cuCtx *ctx, unsigned long long *ticket)
     std::lock_guard<std::mutex> g(ctx->fence_mu);
     const unsigned long long t = ctx->fence_next++;
     cudaEvent_t &e = ctx->fence_ev[t % Eav1cuCtx::N_FENCE];
-    if (!e) CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
-    else CK(cudaEventSynchronize(e));   // the ticket issued N_FENCE fences ago
-    CK(cudaEventRecord(e, ctx->stream));
+    if (!e) CK(cudaEventCreateWithFlags(&e, g_event_flags));
+    else TCK(TC_EVSYNC_FENCE, cudaEventSynchronize(e));   // the ticket issued N_FENCE fences ago
+    {
+        std::lock_guard<SubmitMutex> gs(g_submit_mu);
+        TCK(TC_EVREC, cudaEventRecord(e, ctx->stream));
+    }
     *ticket = t;
     return 0;
 }
@@ -763,7 +875,7 @@ int eav1cu_fence_wait(Eav1cuCtx *ctx, unsigned long long ticket)
         if (ticket + Eav1cuCtx::N_FENCE <= ctx->fence_next) return ctx->err;   // recycled: it completed long ago
         e = ctx->fence_ev[ticket % Eav1cuCtx::N_FENCE];
     }
-    CK(cudaEventSynchronize(e));
+    TCK(TC_EVSYNC_FENCE, cudaEventSynchronize(e));
     return ctx->err;
 }
 
@@ -824,23 +936,57 @@ struct StageTimer {
     }
 };
 
+// Everything a frame's kernels read from the host travels in ONE packed buffer and one host->device copy:
+// put() only notes (source, size, where the device pointer goes); flush() lays the pieces out 256 bytes apart
+// in the slot's pinned staging buffer (streaming) or in a private device allocation (staged plan), fills in the
+// device pointers and queues the single copy. The sources (the context's scratch vectors, the caller's lists)
+// stay untouched until then.
 struct Uploader {
-    // either reuses a context DevBuf (streaming) or allocates a private device copy (staged)
     Eav1cuCtx *ctx; FramePlan *own;
-    int put(DevBuf &b, const void *src, size_t bytes, const uint8_t **out) {
+    struct Piece { const void *src; size_t bytes; const void **out; };
+    std::vector<Piece> pieces;
+    void put(const void *src, size_t bytes, const void **out) {
         *out = nullptr;
-        if (!bytes) return 0;
+        if (bytes) pieces.push_back({src, bytes, out});
+    }
+    template <typename T> void put(const void *src, size_t bytes, const T **out) { put(src, bytes, reinterpret_cast<const void **>(out)); }
+    int flush(DevBuf &stage) {
+        size_t total = 0;
+        for (const Piece &p : pieces) total += (p.bytes + 255) & ~(size_t)255;
+        if (!total) return 0;
+        uint8_t *dev = nullptr, *hst = nullptr;
         if (!own) {
-            int r = upload(ctx, b, src, bytes);
-            *out = b.d;
-            return r;
+            int r = ensure(ctx, stage, total, true);
+            if (r) return r;
+            dev = stage.d; hst = stage.h;
+        } else {
+            void *d = nullptr;
+            CK(cudaMalloc(&d, total));
+            own->owned.push_back(d);
+            dev = (uint8_t *)d;
+            ctx->stage_tmp.resize(total);
+            hst = ctx->stage_tmp.data();
         }
-        void *d = nullptr;
-        CK(cudaMalloc(&d, bytes));
-        own->owned.push_back(d);
-        CK(cudaMemcpyAsync(d, src, bytes, cudaMemcpyHostToDevice, ctx->stream));
-        CK(cudaStreamSynchronize(ctx->stream));
-        *out = (const uint8_t *)d;
+        size_t off = 0;
+        auto ta = std::chrono::steady_clock::now();
+        for (const Piece &p : pieces) {
+            memcpy(hst + off, p.src, p.bytes);
+            *p.out = dev + off;
+            off += (p.bytes + 255) & ~(size_t)255;
+        }
+        auto tb = std::chrono::steady_clock::now();
+        {
+            std::lock_guard<SubmitMutex> g(g_submit_mu);
+            auto tc = std::chrono::steady_clock::now();
+            TCK(TC_H2D_PACK, cudaMemcpyAsync(dev, hst, total, cudaMemcpyHostToDevice, ctx->stream));
+            auto td = std::chrono::steady_clock::now();
+            ctx->t_lock += std::chrono::duration<double>(tc - tb).count();
+            ctx->t_copycall += std::chrono::duration<double>(td - tc).count();
+        }
+        ctx->t_pack += std::chrono::duration<double>(tb - ta).count();
+        if (own) CK(cudaStreamSynchronize(ctx->stream));
+        else { ctx->h2d_bytes += (long long)total; g_total[1] += (long long)total; }
+        pieces.clear();
         return 0;
     }
 };
@@ -874,15 +1020,16 @@ static int plan_build(Eav1cuCtx *ctx, FramePlan &pl, bool staged, const Eav1Fram
         if (has_cdef && has_lr && (r = pic_setup(ctx, ctx->work[1], cur.w, cur.h, cur.layout, cur.bpc))) return r;
     }
     Uploader up{ctx, staged ? &pl : nullptr};
-    const uint8_t *d;
     pl.n_chains = pl.n_deps = pl.n_levels = 0;
     pl.arena_bytes = arena_bytes; pl.payload_bytes = payload_bytes; pl.n_cmds = n_cmds;
     if (n_cmds) {
         int pw[3] = { cur.pl[0].w, cur.pl[1].w, cur.pl[2].w };
         int ph[3] = { cur.pl[0].h, cur.pl[1].h, cur.pl[2].h };
+        auto ts0 = std::chrono::steady_clock::now();
         ctx->sched.reset(pw, ph);
         ctx->sched.build_units(cmds, n_cmds, ctx->units);
-        const UnitGraph &g = ctx->units;
+        ctx->t_sched += std::chrono::duration<double>(std::chrono::steady_clock::now() - ts0).count();
+        const UnitGraph &gall = ctx->units;
         // Two-step transform blocks: give each a residual block behind the arena and list it for
         // phase 1b, sorted by (transform size, type). The engine works on its own copy of the list.
         {
@@ -923,27 +1070,21 @@ static int plan_build(Eav1cuCtx *ctx, FramePlan &pl, bool staged, const Eav1Fram
             pl.arena_bytes = arena_bytes;
             cmds = cc.data();
             if (n_two) {
-                if ((r = up.put(ctx->S().ritems, ri.data(), ri.size() * 4, &d))) return r;
-                pl.d_ritems = reinterpret_cast<const uint32_t *>(d);
+                up.put(ri.data(), ri.size() * 4, &pl.d_ritems);
             }
         }
-        if ((r = up.put(ctx->S().cmds, cmds, n_cmds * sizeof(Eav1Cmd), &d))) return r;
-        pl.d_cmds = reinterpret_cast<const Eav1Cmd *>(d);
-        // never hand the kernel a null list, even when nothing has a producer
-        static const uint32_t zero = 0;
-        if ((r = up.put(ctx->S().deps, g.deps.empty() ? &zero : g.deps.data(), std::max<size_t>(g.deps.size(), 1) * 4, &d))) return r;
-        pl.d_deps = reinterpret_cast<const uint32_t *>(d);
-        pl.n_items = (uint32_t)g.mc_items.size();
+        up.put(cmds, n_cmds * sizeof(Eav1Cmd), &pl.d_cmds);
+        pl.n_items = (uint32_t)gall.mc_items.size();
         if (staged) {
             pl.mc_px = pl.unit_px = 0;
-            for (uint32_t it : g.mc_items) {
+            for (uint32_t it : gall.mc_items) {
                 const Eav1Cmd &c = cmds[it & 0xffffff];
                 const int x0 = (int)((it >> 24) & 3) * 32, y0 = (int)((it >> 26) & 3) * 32;
                 pl.mc_px += (c.op == EAV1_OP_MC && !c.u.mc.dx) ? (long long)std::min(32, c.w - x0) * std::min(32, c.h - y0) : (long long)c.w * c.h;
             }
-            for (size_t u = 0; u < g.unit_cmd.size(); u++)
-                for (uint32_t k = 0; k < g.unit_cnt[u]; k++)
-                    pl.unit_px += (long long)cmds[g.unit_cmd[u] + k].w * cmds[g.unit_cmd[u] + k].h;
+            for (size_t u = 0; u < gall.unit_cmd.size(); u++)
+                for (uint32_t k = 0; k < gall.unit_cnt[u]; k++)
+                    pl.unit_px += (long long)cmds[gall.unit_cmd[u] + k].w * cmds[gall.unit_cmd[u] + k].h;
         }
         if (pl.n_items) {
             // Largest items first (they are independent, any order is legal): the four warps of a CTA
@@ -958,13 +1099,53 @@ static int plan_build(Eav1cuCtx *ctx, FramePlan &pl, bool staged, const Eav1Fram
                 return 15 - std::min(lg, 15);   // bucket 0 = largest
             };
             bk.assign(17, 0);
-            for (uint32_t it : g.mc_items) bk[weight(it) + 1]++;
+            for (uint32_t it : gall.mc_items) bk[weight(it) + 1]++;
             for (size_t b = 1; b < bk.size(); b++) bk[b] += bk[b - 1];
-            sorted.resize(g.mc_items.size());
-            for (uint32_t it : g.mc_items) sorted[bk[weight(it)]++] = it;
-            if ((r = up.put(ctx->S().items, sorted.data(), sorted.size() * 4, &d))) return r;
-            pl.d_items = reinterpret_cast<const uint32_t *>(d);
+            sorted.resize(gall.mc_items.size());
+            for (uint32_t it : gall.mc_items) sorted[bk[weight(it)]++] = it;
+            up.put(sorted.data(), sorted.size() * 4, &pl.d_items);
         }
+        // Units that wait for nothing inside the frame run in a flat launch of their own (phase 2a); only the
+        // units with a producer among the phase-2 units go through the dataflow kernel, and a producer that
+        // already ran in phase 2a is no longer a dependency. On inter frames that leaves a few dozen units.
+        {
+            const UnitGraph &ga = ctx->units;
+            UnitGraph &g2 = ctx->units2;
+            g2.mc_items.clear(); g2.unit_cmd.clear(); g2.unit_cnt.clear(); g2.dep_start.clear(); g2.deps.clear();
+            std::vector<uint2> &flat = ctx->flat_tmp;
+            std::vector<uint32_t> &remap = ctx->remap_tmp;
+            const size_t nu = ga.unit_cmd.size();
+            remap.assign(nu, UINT32_MAX);
+            flat.clear();
+            size_t n_flat_big = 0;
+            for (int pass = 0; pass < 2; pass++)        // large units lead the list
+                for (size_t u = 0; u < nu; u++) {
+                    if (ga.dep_start[u + 1] != ga.dep_start[u] || ctx->no_flat) continue;
+                    const Eav1Cmd &c = cmds[ga.unit_cmd[u]];
+                    const bool big = c.w > 32 || c.h > 32;
+                    if (big != (pass == 0)) continue;
+                    flat.push_back(make_uint2(ga.unit_cmd[u], ga.unit_cnt[u]));
+                    n_flat_big += big;
+                }
+            for (size_t u = 0; u < nu; u++) {
+                if (ga.dep_start[u + 1] == ga.dep_start[u] && !ctx->no_flat) continue;
+                remap[u] = (uint32_t)g2.unit_cmd.size();
+                g2.unit_cmd.push_back(ga.unit_cmd[u]);
+                g2.unit_cnt.push_back(ga.unit_cnt[u]);
+                g2.dep_start.push_back((uint32_t)g2.deps.size());
+                for (uint32_t k = ga.dep_start[u]; k < ga.dep_start[u + 1]; k++)
+                    if (remap[ga.deps[k]] != UINT32_MAX) g2.deps.push_back(remap[ga.deps[k]]);
+            }
+            g2.dep_start.push_back((uint32_t)g2.deps.size());
+            pl.n_flat_big = (uint32_t)n_flat_big; pl.n_flat_small = (uint32_t)(flat.size() - n_flat_big);
+            if (!flat.empty()) {
+                up.put(flat.data(), flat.size() * sizeof(uint2), &pl.d_flat);
+            }
+        }
+        const UnitGraph &g = ctx->units2;
+        // never hand the kernel a null list, even when nothing has a producer
+        static const uint32_t zero = 0;
+        up.put(g.deps.empty() ? &zero : g.deps.data(), std::max<size_t>(g.deps.size(), 1) * 4, &pl.d_deps);
         pl.n_chains = (uint32_t)g.unit_cmd.size(); pl.n_deps = (uint32_t)g.deps.size();
         if (staged) pl.n_levels = Scheduler::unit_levels(g);
         if (pl.n_chains) {
@@ -1001,10 +1182,9 @@ static int plan_build(Eav1cuCtx *ctx, FramePlan &pl, bool staged, const Eav1Fram
             }
             pl.n_big = (uint32_t)nb; pl.n_small = (uint32_t)(nc - nb);
             pl.big_share = px_big + px_small > 0 ? px_big / (px_big + px_small) : 0;
-            if ((r = up.put(ctx->S().recs, rt.data(), rt.size() * sizeof(ChainRec), &d))) return r;
-            pl.d_recs = reinterpret_cast<const ChainRec *>(d);
+            up.put(rt.data(), rt.size() * sizeof(ChainRec), &pl.d_recs);
         } else { pl.n_big = pl.n_small = 0; }
-        if ((r = up.put(ctx->S().payload, payload, payload_bytes, &pl.d_payload))) return r;
+        up.put(payload, payload_bytes, &pl.d_payload);
         if ((r = ensure(ctx, ctx->arena, arena_bytes + 16, false))) return r;
         if (g.unit_cmd.size() > ctx->done_cap) {
             if (ctx->d_done) { CK(cudaStreamSynchronize(ctx->stream)); cudaFree(ctx->d_done); ctx->d_done = nullptr; }
@@ -1022,19 +1202,15 @@ static int plan_build(Eav1cuCtx *ctx, FramePlan &pl, bool staged, const Eav1Fram
         for (size_t i = 0; i < fd->n_lf_recs; i++) if (fd->lf_recs[i].dir == 0) v[n0++] = fd->lf_recs[i];
         size_t n1 = n0;
         for (size_t i = 0; i < fd->n_lf_recs; i++) if (fd->lf_recs[i].dir != 0) v[n1++] = fd->lf_recs[i];
-        if ((r = up.put(ctx->S().lfrec, v.data(), v.size() * sizeof(Eav1LfRec), &d))) return r;
-        pl.d_lf = reinterpret_cast<const Eav1LfRec *>(d);
+        up.put(v.data(), v.size() * sizeof(Eav1LfRec), &pl.d_lf);
         pl.n_lf0 = n0; pl.n_lf1 = n1 - n0;
-        if ((r = up.put(ctx->S().lflvl, fd->lf_level, fd->lf_level_bytes, &pl.d_lflvl))) return r;
+        up.put(fd->lf_level, fd->lf_level_bytes, &pl.d_lflvl);
     } else { pl.n_lf0 = pl.n_lf1 = 0; }
     if (has_cdef)
-        if ((r = up.put(ctx->S().lfmask, fd->lf_mask, (size_t)fd->sb128w * fd->sb128h * 1348, &pl.d_lfmask))) return r;
+        up.put(fd->lf_mask, (size_t)fd->sb128w * fd->sb128h * 1348, &pl.d_lfmask);
     pl.n_lr = fd->n_lr_recs;
-    if (has_lr) {
-        if ((r = up.put(ctx->S().lrrec, fd->lr_recs, fd->n_lr_recs * sizeof(Eav1LrRec), &d))) return r;
-        pl.d_lr = reinterpret_cast<const Eav1LrRec *>(d);
-    }
-    return 0;
+    if (has_lr) up.put(fd->lr_recs, fd->n_lr_recs * sizeof(Eav1LrRec), &pl.d_lr);
+    return up.flush(ctx->S().stage);
 }
 
 static int plan_launch(Eav1cuCtx *ctx, FramePlan &pl)
@@ -1070,7 +1246,7 @@ static int plan_launch(Eav1cuCtx *ctx, FramePlan &pl)
     // on a second stream (they share nothing); the dataflow kernel waits for both.
     const bool fork = pl.n_ritems && ctx->stream2 && !ctx->serial_phase1;
     cudaStream_t rs = fork ? ctx->stream2 : st;
-    if (fork) { CK(cudaEventRecord(ctx->ev_fork, st)); CK(cudaStreamWaitEvent(rs, ctx->ev_fork, 0)); }
+    if (fork) { TCK(TC_EVREC, cudaEventRecord(ctx->ev_fork, st)); TCK(TC_WAITEV, cudaStreamWaitEvent(rs, ctx->ev_fork, 0)); }
     if (pl.n_ritems) {
         StageTimer tm(ctx, 6, rs);
         const unsigned small_ctas = (pl.n_ritems_small + 3) / 4;
@@ -1079,7 +1255,7 @@ static int plan_launch(Eav1cuCtx *ctx, FramePlan &pl)
         else     resid_kernel<BD8><<<grid, 128, 0, rs>>>(fc, pl.d_cmds, pl.d_ritems, pl.n_ritems_small, small_ctas, pl.n_ritems);
         ctx->n_launches++;
     }
-    if (fork) CK(cudaEventRecord(ctx->ev_join, rs));
+    if (fork) TCK(TC_EVREC, cudaEventRecord(ctx->ev_join, rs));
     if (pl.n_items) {
         StageTimer tm(ctx, 4);
         const unsigned grid = (pl.n_items + 3) / 4;
@@ -1087,13 +1263,27 @@ static int plan_launch(Eav1cuCtx *ctx, FramePlan &pl)
         else     mc_kernel<BD8><<<grid, 128, 0, st>>>(fc, pl.d_cmds, pl.d_items, pl.n_items);
         ctx->n_launches++;
     }
-    if (fork) CK(cudaStreamWaitEvent(st, ctx->ev_join, 0));
+    if (fork) TCK(TC_WAITEV, cudaStreamWaitEvent(st, ctx->ev_join, 0));
+    if (pl.n_flat_big + pl.n_flat_small) {
+        StageTimer tm(ctx, 0);
+        const unsigned grid = pl.n_flat_big + (pl.n_flat_small + 3) / 4;
+        if (hbd) flat_units_kernel<BD16><<<grid, 128, 0, st>>>(fc, pl.d_cmds, pl.d_flat, pl.n_flat_big, pl.n_flat_small);
+        else     flat_units_kernel<BD8><<<grid, 128, 0, st>>>(fc, pl.d_cmds, pl.d_flat, pl.n_flat_big, pl.n_flat_small);
+        ctx->n_launches++;
+    }
     if (pl.n_chains) {
         StageTimer tm(ctx, 0);
         if (pl.n_chains > ctx->done_cap) return fail(ctx, EAV1CU_ERR_INVAL, "done-flag array smaller than the staged frame");
         ReconArgs ra;
         ra.cmds = pl.d_cmds; ra.deps = pl.d_deps;
-        ra.done = ctx->d_done; ra.ctrl = ctx->d_ctrl; ra.epoch = ctx->epoch = ++g_epoch;
+        uint32_t ep = ++g_epoch;
+        if (ep == 0 || ep < ctx->epoch) {
+            // the 32-bit launch epoch wrapped (about a week of launches): never-written flags hold 0 and stale flags
+            // could match again, so clear this context's flags (stream-ordered) and never hand out epoch 0
+            CK(cudaMemsetAsync(ctx->d_done, 0, ctx->done_cap * 4, st));
+            while (ep == 0) ep = ++g_epoch;
+        }
+        ra.done = ctx->d_done; ra.ctrl = ctx->d_ctrl; ra.epoch = ctx->epoch = ep;
         ra.big = pl.d_recs; ra.small = pl.d_recs + pl.n_big;
         ra.n_big = pl.n_big; ra.n_small = pl.n_small;
         // CTAs are split between the two kinds in proportion to their pixel work
@@ -1101,7 +1291,7 @@ static int plan_launch(Eav1cuCtx *ctx, FramePlan &pl)
         unsigned big_ctas = pl.n_big ? std::max(1u, (unsigned)(grid * pl.big_share + 0.5)) : 0;
         big_ctas = std::min(big_ctas, pl.n_big);
         unsigned small_ctas = pl.n_small ? std::min<unsigned>((pl.n_small + 3) / 4, std::max(1u, grid - std::min(grid - 1, big_ctas))) : 0;
-        if (!pl.n_small) big_ctas = std::min<unsigned>(pl.n_big, grid);
+        if (!pl.n_small) big_ctas = std::min<unsigned>(pl.n_big, grid);   // never more CTAs than units: the rest of the GPU stays free for other streams
         grid = big_ctas + small_ctas;
         ra.n_big_ctas = big_ctas; ra.n_workers = big_ctas + 4 * small_ctas;
         ra.debug = (uint32_t)ctx->debug_check;
@@ -1118,11 +1308,11 @@ static int plan_launch(Eav1cuCtx *ctx, FramePlan &pl)
             }
             cudaMemsetAsync(ctx->d_sums + slot * 2, 0, 16, st);
             unsigned long long hs = 0;
-            const uint32_t *hp = reinterpret_cast<const uint32_t *>(ctx->S().payload.h);
+            const uint32_t *hp = reinterpret_cast<const uint32_t *>(ctx->S().stage.h + ((const uint8_t *)pl.d_payload - ctx->S().stage.d));
             for (size_t i = 0; i < pl.payload_bytes / 4; i++) hs += hp[i];
             ctx->h_sums[slot][0] = hs;
             hs = 0;
-            hp = reinterpret_cast<const uint32_t *>(ctx->S().cmds.h);
+            hp = reinterpret_cast<const uint32_t *>(ctx->S().stage.h + ((const uint8_t *)pl.d_cmds - ctx->S().stage.d));
             for (size_t i = 0; i < pl.n_cmds * sizeof(Eav1Cmd) / 4; i++) hs += hp[i];
             ctx->h_sums[slot][1] = hs;
             ctx->sum_frame[slot] = ctx->n_frames + 1;
@@ -1221,7 +1411,7 @@ static int plan_launch(Eav1cuCtx *ctx, FramePlan &pl)
         StageTimer tm(ctx, 3);
         Picture &src = *lr_src, &cur = *lr_out;
         for (int i = 0; i < 3; i++) { pp.b[i] = src.pl[i]; pp.p[i] = cur.pl[i]; }
-        CK(cudaMemcpyAsync(cur.base, src.base, std::min(cur.bytes, src.bytes), cudaMemcpyDeviceToDevice, st));
+        TCK(TC_D2D, cudaMemcpyAsync(cur.base, src.base, std::min(cur.bytes, src.bytes), cudaMemcpyDeviceToDevice, st));
         dim3 grid(384 / LR_TW, (unsigned)pl.n_lr);
         if (hbd) lr_kernel<uint16_t><<<grid, 128, 0, st>>>(pp, pl.d_lr);
         else     lr_kernel<uint8_t><<<grid, 128, 0, st>>>(pp, pl.d_lr);
@@ -1245,21 +1435,25 @@ int eav1cu_frame_submit(Eav1cuCtx *ctx, const Eav1FrameDesc *fd,
     CK(cudaSetDevice(ctx->device));
     ctx->cur_slot ^= 1;
     Slot &sl = ctx->S();
-    if (!sl.done) CK(cudaEventCreateWithFlags(&sl.done, cudaEventDisableTiming));
+    if (!sl.done) CK(cudaEventCreateWithFlags(&sl.done, g_event_flags));
     auto t0 = std::chrono::steady_clock::now();
-    if (sl.used) CK(cudaEventSynchronize(sl.done));   // the frame two submits ago has finished with this slot
+    if (sl.used) TCK(TC_EVSYNC_SLOT, cudaEventSynchronize(sl.done));   // the frame two submits ago has finished with this slot
     auto t1 = std::chrono::steady_clock::now();
     int r = plan_build(ctx, ctx->live, false, fd, cmds, n_cmds, payload, payload_bytes, arena_bytes);
     if (r) return r;
     auto t2 = std::chrono::steady_clock::now();
-    if ((r = plan_launch(ctx, ctx->live))) return r;
+    {
+        std::lock_guard<SubmitMutex> g(g_submit_mu);
+        { CallTimer ct_(TC_LAUNCHES); if ((r = plan_launch(ctx, ctx->live))) return r; }
+        TCK(TC_EVREC, cudaEventRecord(sl.done, ctx->stream));
+    }
     auto t3 = std::chrono::steady_clock::now();
     ctx->t_wait += std::chrono::duration<double>(t1 - t0).count();
     ctx->t_build += std::chrono::duration<double>(t2 - t1).count();
     ctx->t_launch += std::chrono::duration<double>(t3 - t2).count();
-    CK(cudaEventRecord(sl.done, ctx->stream));
     sl.used = true;
     ctx->n_frames++;
+    g_total[0] += ctx->live.launches; g_total[3]++;
     if (ctx->capture) {
         // keep a replayable copy of this frame (bench.py's device-resident leg)
         FramePlan *sp = new FramePlan();
@@ -1346,6 +1540,13 @@ int eav1cu_plan_tickets(const Eav1Cmd *cmds, size_t n_cmds, const int plane_w[3]
     return (int)n;
 }
 
+int eav1cu_global_counters(long long out[4])
+{
+    if (!out) return EAV1CU_ERR_INVAL;
+    for (int i = 0; i < 4; i++) out[i] = g_total[i];
+    return 0;
+}
+
 int eav1cu_counters(Eav1cuCtx *ctx, long long out[4])
 {
     if (!ctx || !out) return EAV1CU_ERR_INVAL;
@@ -1397,7 +1598,24 @@ int eav1cu_staged_replay(Eav1cuCtx *ctx, int idx)
 {
     if (!ctx || idx < 0 || idx >= (int)ctx->staged.size()) return EAV1CU_ERR_INVAL;
     if (ctx->err) return ctx->err;
+    std::lock_guard<SubmitMutex> g(g_submit_mu);
     return plan_launch(ctx, *ctx->staged[idx]);
+}
+
+/* Replays every staged frame in submit order, `passes` times, from one C loop (bench.py runs one host thread per
+ * staged decoder so that several streams keep the GPU busy at once). Returns 0 or the first error. */
+int eav1cu_staged_replay_all(Eav1cuCtx *ctx, int passes)
+{
+    if (!ctx || passes < 0) return EAV1CU_ERR_INVAL;
+    if (ctx->err) return ctx->err;
+    CK(cudaSetDevice(ctx->device));
+    for (int p = 0; p < passes; p++)
+        for (FramePlan *pl : ctx->staged) {
+            std::lock_guard<SubmitMutex> g(g_submit_mu);
+            const int r = plan_launch(ctx, *pl);
+            if (r) return r;
+        }
+    return 0;
 }
 
 /* Development aid: replay staged frame idx once with per-unit timestamps. out receives 6 words per
@@ -1492,6 +1710,7 @@ int eav1cu_apply_grain(Eav1cuCtx *ctx, int src_pic, int dst_pic, const Eav1Grain
     P.grain = (int16_t *)ctx->d_fg;
     P.scaling = ctx->d_fg + FG_GRAIN_BYTES;
     P.offsets = ctx->d_fg + FG_GRAIN_BYTES + FG_SCALE_BYTES;
+    std::lock_guard<SubmitMutex> gs(g_submit_mu);
     StageTimer tm(ctx, 5);
     fg_prepare_kernel<<<1, 256, 0, ctx->stream>>>(P);
     const dim3 grid((P.cols + FG_STRIP - 1) / FG_STRIP, P.rows);

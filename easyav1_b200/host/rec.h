@@ -73,6 +73,7 @@ typedef struct Eav1Rec {
     Eav1cuCtx *cu;
     Eav1Frame *frames; int n_frames;
     int threaded;                       /* dav1d runs frame threads: frames end in the exit hook */
+    int inline_submit;                  /* single-threaded walk: the walking thread hands frames to the engine itself */
     /* job queue (decode order) */
     pthread_mutex_t q_mu; pthread_cond_t q_cv, q_idle;
     pthread_mutex_t cu_mu;              /* engine calls: the submit thread vs. film grain at output time */
@@ -81,8 +82,7 @@ typedef struct Eav1Rec {
     int q_stop, q_busy;
     pthread_t submit_thread; int have_thread;
     void *alloc_state;
-    atomic_int unsupported;             /* sticky: a tool we do not run yet was seen */
-    atomic_int error;
+    atomic_int error;                   /* engine failure (latched until dav1d_flush / the next shown key frame) */
     atomic_llong frames_submitted;
 } Eav1Rec;
 
@@ -116,6 +116,7 @@ extern __thread Eav1Walk eav1_walk;
 Eav1Rec *eav1rec_for_ctx(const Dav1dContext *c);
 /* bind the calling thread to frame f (and tile state ts, may be NULL for filter tasks) */
 Eav1Walk *eav1rec_enter(const Dav1dFrameContext *f, const Dav1dTaskContext *t);
+void eav1rec_unsupported(Eav1Walk *w);   /* the frame being walked cannot be recorded: it alone fails */
 Eav1Cmd *eav1rec_push(Eav1Walk *w);
 uint32_t eav1rec_payload(Eav1Walk *w, const void *src, size_t bytes, size_t align);
 uint32_t eav1rec_region(Eav1Walk *w, int reg, size_t elem_bytes);

@@ -21,6 +21,7 @@
 int  eav1ref_dav1d_open(Dav1dContext **c_out, const Dav1dSettings *s);
 void eav1ref_dav1d_close(Dav1dContext **c_out);
 int  eav1ref_dav1d_get_picture(Dav1dContext *c, Dav1dPicture *out);
+void eav1ref_dav1d_flush(Dav1dContext *c);
 
 /* pinned host memory comes from the engine so this library needs no CUDA headers */
 int  eav1cu_host_alloc(void **p, size_t bytes);
@@ -60,6 +61,11 @@ static void *grow(void *p, size_t *cap, size_t need, size_t elem)
     return p;
 }
 
+void eav1rec_unsupported(Eav1Walk *w)
+{
+    if (w && w->fr) atomic_store(&w->fr->unsupported, 1);
+}
+
 Eav1Cmd *eav1rec_push(Eav1Walk *w)
 {
     Eav1List *l = w->list;
@@ -77,7 +83,7 @@ uint32_t eav1rec_payload(Eav1Walk *w, const void *src, size_t bytes, size_t alig
     Eav1Frame *fr = w->fr;
     const size_t take = (bytes + align - 1) & ~(align - 1);
     const size_t off = atomic_fetch_add(&fr->n_payload, take);
-    if (off + bytes > fr->cap_payload) { atomic_store(&w->r->unsupported, 1); return 0; }
+    if (off + bytes > fr->cap_payload) { atomic_store(&fr->unsupported, 1); return 0; }
     memcpy(fr->payload + off, src, bytes);
     return (uint32_t)off;
 }
@@ -251,7 +257,7 @@ typedef struct AllocState {
 static void destroy_rec(Eav1Rec *r, AllocState *as);
 
 /* pinned buffers outlive a decoder: the next one opened in this process takes them over */
-#define PIN_POOL 64
+#define PIN_POOL 2048   /* 64 concurrent streams x (8 references + frames in flight + output queue) */
 static HostBuf g_pin_pool[PIN_POOL];
 
 static int pin_pool_get(size_t total, HostBuf *out)
@@ -416,6 +422,9 @@ struct Eav1Job {
     void *cur_data[3]; ptrdiff_t cur_stride[2];
 };
 
+static void job_submit(Eav1Rec *r, Eav1Job *j, int digest, int sync_each);
+static void job_release(Eav1Rec *r, Eav1Job *j);
+
 static Eav1Job *job_get(Eav1Rec *r)
 {
     pthread_mutex_lock(&r->q_mu);
@@ -490,12 +499,26 @@ void eav1rec_frame_end(Eav1Rec *r, const Dav1dFrameContext *f, int retval)
     Eav1PicData *coded = pd_of(&f->cur);
     Eav1PicData *cur = superres ? pd_of(&f->sr_cur.p) : coded;
     if (!coded) cur = NULL;
-    int unsupported = atomic_load(&r->unsupported) || atomic_load(&fr->unsupported);
-    j->skip = retval != 0 || !cur || !hdr || unsupported;
-    if (!retval && unsupported && cur) {
-        fprintf(stderr, "easyav1_b200: unsupported coding tool in stream (no CPU fallback)\n");
+    /* A frame fails on its own: a construct the recorder could not express, or (test hook) EAV1_TEST_FAIL_FRAME.
+     * A frame that references a failed picture fails too, as in dav1d (FRAME_ERROR progress, thread_task.c), so the
+     * damage ends at the next key frame instead of being handed out as good pictures. */
+    int unsupported = atomic_load(&fr->unsupported);
+    {
+        static int fail_at = -2;
+        if (fail_at == -2) { const char *e = getenv("EAV1_TEST_FAIL_FRAME"); fail_at = e ? atoi(e) : -1; }
+        if (fail_at >= 0 && (long long)seq == fail_at) unsupported = 1;
+    }
+    int bad_ref = 0;
+    if (hdr && IS_INTER_OR_SWITCH(hdr))
+        for (int i = 0; i < 7; i++) {
+            Eav1PicData *rp = pd_of(&f->refp[i].p);
+            if (rp && atomic_load(&rp->failed)) bad_ref = 1;
+        }
+    j->skip = retval != 0 || !cur || !hdr || unsupported || bad_ref;
+    if (!retval && (unsupported || bad_ref) && cur) {
+        if (unsupported)
+            fprintf(stderr, "easyav1_b200: frame %llu uses a construct the recorder cannot express (no CPU fallback): dropped\n", seq);
         atomic_store(&cur->failed, 1);
-        atomic_store(&r->error, EAV1CU_ERR_INVAL);
     }
     if (!j->skip) {
         if (!fr->open) frame_begin(fr, f);
@@ -573,6 +596,22 @@ void eav1rec_frame_end(Eav1Rec *r, const Dav1dFrameContext *f, int retval)
         fd->lf_mask = j->lf_mask;
     }
     fr->open = 0;
+    if (r->inline_submit) {
+        /* single-threaded walk: frames end here in decode order on the caller's thread, so the frame goes to the
+         * engine right away (no hand-over to the submit thread, no wake-up); everything stays asynchronous on the
+         * GPU side and dav1d_get_picture / eav1rec_picture_wait wait for the fence as usual */
+        job_submit(r, j, 0, 0);
+        pthread_mutex_lock(&r->q_mu);
+        r->seq_submit = j->seq + 1;
+        pthread_cond_broadcast(&r->q_idle);
+        pthread_mutex_unlock(&r->q_mu);
+        job_release(r, j);
+        pthread_mutex_lock(&r->q_mu);
+        j->next = r->job_free;
+        r->job_free = j;
+        pthread_mutex_unlock(&r->q_mu);
+        return;
+    }
     enqueue(r, j);
 }
 
@@ -606,6 +645,46 @@ static void job_digest(const Eav1Job *j)
             j->fd.ref[0], j->fd.ref[1], j->fd.ref[2], j->fd.ref[3], j->fd.ref[4], j->fd.ref[5], j->fd.ref[6], j->arena_bytes);
 }
 
+/* hand one finished frame to the engine: reconstruction, download of the planes, fence */
+static void job_submit(Eav1Rec *r, Eav1Job *j, int digest, int sync_each)
+{
+    if (j->skip) return;
+    if (digest) job_digest(j);
+    int res = atomic_load(&r->error);
+    pthread_mutex_lock(&r->cu_mu);
+    if (!res)
+        res = eav1cu_frame_submit(r->cu, &j->fd, j->cmds, j->n_cmds, j->payload, j->n_payload, j->arena_bytes);
+    unsigned long long ticket = 0;
+    if (!res && !j->no_download)
+        res = eav1cu_pic_download_async(r->cu, j->fd.superres ? j->fd.sr_pic : j->fd.cur, j->cur_data, j->cur_stride);
+    if (!res) res = eav1cu_fence(r->cu, &ticket);
+    if (!res && sync_each) res = eav1cu_sync(r->cu);
+    pthread_mutex_unlock(&r->cu_mu);
+    if (res) {
+        char msg[256] = "";
+        eav1cu_last_error(r->cu, msg, sizeof(msg));
+        fprintf(stderr, "easyav1_b200: frame reconstruction failed (%d) %s\n", res, msg);
+        atomic_store(&r->error, res);
+        atomic_store(&j->cur->failed, 1);
+    }
+    atomic_store(&j->cur->fence, ticket);
+    atomic_fetch_add(&r->frames_submitted, 1);
+}
+
+/* The pictures may go once the engine has the launches queued: device slots are reused in stream order, and the
+ * host buffer of `cur` stays referenced by its Dav1dPicture or, for a frame nobody keeps, is only recycled after
+ * its fence. */
+static void job_release(Eav1Rec *r, Eav1Job *j)
+{
+    if (j->skip) return;
+    Eav1PicData *cur = j->cur;
+    const unsigned long long t = atomic_load(&cur->fence);
+    if (atomic_load(&cur->refs) == 1 && t) eav1cu_fence_wait(r->cu, t);
+    pd_unref(cur);
+    if (j->coded) pd_unref(j->coded);
+    for (int i = 0; i < 7; i++) if (j->ref[i]) pd_unref(j->ref[i]);
+}
+
 static void *submit_main(void *arg)
 {
     Eav1Rec *r = arg;
@@ -633,44 +712,13 @@ static void *submit_main(void *arg)
         r->q_busy = 1;
         pthread_mutex_unlock(&r->q_mu);
 
-        if (!j->skip) {
-            if (digest) job_digest(j);
-            int res = atomic_load(&r->error);
-            pthread_mutex_lock(&r->cu_mu);
-            if (!res)
-                res = eav1cu_frame_submit(r->cu, &j->fd, j->cmds, j->n_cmds, j->payload, j->n_payload, j->arena_bytes);
-            unsigned long long ticket = 0;
-            if (!res && !j->no_download)
-                res = eav1cu_pic_download_async(r->cu, j->fd.superres ? j->fd.sr_pic : j->fd.cur, j->cur_data, j->cur_stride);
-            if (!res) res = eav1cu_fence(r->cu, &ticket);
-            if (!res && sync_each) res = eav1cu_sync(r->cu);
-            pthread_mutex_unlock(&r->cu_mu);
-            if (res) {
-                char msg[256] = "";
-                eav1cu_last_error(r->cu, msg, sizeof(msg));
-                fprintf(stderr, "easyav1_b200: frame reconstruction failed (%d) %s\n", res, msg);
-                atomic_store(&r->error, res);
-                atomic_store(&j->cur->failed, 1);
-            }
-            atomic_store(&j->cur->fence, ticket);
-            atomic_fetch_add(&r->frames_submitted, 1);
-        }
+        job_submit(r, j, digest, sync_each);
         pthread_mutex_lock(&r->q_mu);
         r->seq_submit++;
         r->q_busy = 0;
         pthread_cond_broadcast(&r->q_idle);
         pthread_mutex_unlock(&r->q_mu);
-        /* the pictures may go once the engine has the launches queued: device slots are reused
-         * in stream order, and the host buffer of `cur` stays referenced by its Dav1dPicture or,
-         * for a frame nobody keeps, is only recycled after the fence below */
-        if (!j->skip) {
-            Eav1PicData *cur = j->cur;
-            const unsigned long long t = atomic_load(&cur->fence);
-            if (atomic_load(&cur->refs) == 1 && t) eav1cu_fence_wait(r->cu, t);
-            pd_unref(cur);
-            if (j->coded) pd_unref(j->coded);
-            for (int i = 0; i < 7; i++) if (j->ref[i]) pd_unref(j->ref[i]);
-        }
+        job_release(r, j);
         if (timing) {
             clock_gettime(CLOCK_MONOTONIC, &ts0);
             t_busy += (ts0.tv_sec - ts1.tv_sec) + 1e-9 * (ts0.tv_nsec - ts1.tv_nsec);
@@ -802,10 +850,17 @@ int eav1hook_submit_frame(Dav1dContext *const c)
     pthread_mutex_unlock(&r->q_mu);
     if (orphan) {
         fr->open = 0;
-        Eav1Job *j = job_get(r);
-        j->seq = seq;
-        j->skip = 1;
-        enqueue(r, j);
+        if (r->inline_submit) {
+            pthread_mutex_lock(&r->q_mu);
+            r->seq_submit = seq + 1;
+            pthread_cond_broadcast(&r->q_idle);
+            pthread_mutex_unlock(&r->q_mu);
+        } else {
+            Eav1Job *j = job_get(r);
+            j->seq = seq;
+            j->skip = 1;
+            enqueue(r, j);
+        }
     }
     return res;
 }
@@ -916,6 +971,7 @@ int dav1d_open(Dav1dContext **c_out, const Dav1dSettings *s)
     }
     r->c = c;
     r->threaded = c->n_fc > 1;
+    r->inline_submit = !r->threaded && !getenv("EASYAV1_NO_INLINE_SUBMIT");
     r->n_frames = (int)c->n_fc;
     r->frames = calloc((size_t)r->n_frames, sizeof(Eav1Frame));
     if (!r->frames) { eav1ref_dav1d_close(c_out); destroy_rec(r, as); return DAV1D_ERR(ENOMEM); }
@@ -960,6 +1016,20 @@ void dav1d_close(Dav1dContext **c_out)
     if (!busy) destroy_rec(r, as);
 }
 
+/* Drop-in for dav1d_flush (ext/dav1d/src/lib.c:526; easyAV1 calls it on every seek, src/easyav1.c:3059). The
+ * reference's flush ends the frames in flight (they arrive as skipped jobs); afterwards the queue is drained and an
+ * engine error that was not a CUDA failure is forgotten, so that decoding can restart at the next key frame. */
+void dav1d_flush(Dav1dContext *c)
+{
+    eav1ref_dav1d_flush(c);
+    Eav1Rec *r = eav1rec_for_ctx(c);
+    if (!r) return;
+    pthread_mutex_lock(&r->q_mu);
+    while ((r->q_head || r->q_busy) && !r->q_stop) pthread_cond_wait(&r->q_idle, &r->q_mu);
+    pthread_mutex_unlock(&r->q_mu);
+    if (atomic_load(&r->error) == EAV1CU_ERR_INVAL && eav1cu_clear_error(r->cu) == 0) atomic_store(&r->error, 0);
+}
+
 /* for tools / tests: how many frames went through the engine and whether it failed */
 long long eav1rec_frames_submitted(const Dav1dContext *c) { Eav1Rec *r = eav1rec_for_ctx(c); return r ? atomic_load(&r->frames_submitted) : -1; }
 int eav1rec_error(const Dav1dContext *c) { Eav1Rec *r = eav1rec_for_ctx(c); return r ? atomic_load(&r->error) : -1; }
@@ -975,6 +1045,24 @@ void eav1rec_drain(const Dav1dContext *c)
     while ((r->q_head || r->q_busy) && !r->q_stop) pthread_cond_wait(&r->q_idle, &r->q_mu);
     pthread_mutex_unlock(&r->q_mu);
     eav1cu_sync(r->cu);
+}
+
+/* For a caller that multiplexes many decoders on few threads (host/pump.c): dav1d_get_picture without the wait for
+ * the planes, and the wait as a call of its own. The picture may be passed on, referenced and released as usual;
+ * only its sample data must not be read before eav1rec_picture_wait returned 0. */
+int eav1rec_get_picture_async(Dav1dContext *c, Dav1dPicture *out)
+{
+    const int res = eav1ref_dav1d_get_picture(c, out);
+    Eav1Rec *r = eav1rec_for_ctx(c);
+    if (r && res == 0 && atomic_load(&r->error)) { dav1d_picture_unref(out); return DAV1D_ERR(EIO); }
+    return res;
+}
+
+int eav1rec_picture_wait(Dav1dPicture *p)
+{
+    Eav1PicData *pd = p && p->data[0] ? p->allocator_data : NULL;
+    if (!pd) return 0;
+    return pd_wait(pd->rec, pd);
 }
 
 /* Drop-in for dav1d_get_picture (ext/dav1d/src/lib.c:458): the picture dav1d hands out was

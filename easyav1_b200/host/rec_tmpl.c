@@ -21,7 +21,9 @@
 #include "src/ipred_prepare.h"
 
 #define REC() Eav1Walk *const r = &eav1_walk
-#define UNSUPPORTED(r) atomic_store(&(r)->r->unsupported, 1)
+/* a construct the recorder cannot express: only the frame being walked fails (its picture and whatever references it
+ * come back as DAV1D_ERR(EIO)); the decoder recovers at the next key frame like dav1d does after a damaged frame */
+#define UNSUPPORTED(r) eav1rec_unsupported(r)
 
 #if BITDEPTH == 8
 #define BDMAX_ARG
@@ -488,11 +490,11 @@ void bitfn(eav1rec_loop_restoration_dsp_init)(Dav1dLoopRestorationDSPContext *co
 /* CDEF is driven on the device (needs pixel-derived direction/variance): the host table
  * must never be reached because filter_sbrow below skips dav1d_filter_sbrow_cdef. */
 static int rec_cdef_dir(const pixel *dst, ptrdiff_t s, unsigned *var HIGHBD_DECL_SUFFIX)
-{ (void)dst; (void)s; *var = 0; if (eav1_walk.r) atomic_store(&eav1_walk.r->unsupported, 1); return 0; }
+{ (void)dst; (void)s; *var = 0; eav1rec_unsupported(&eav1_walk); return 0; }
 static void rec_cdef_fb(pixel *dst, ptrdiff_t stride, const_left_pixel_row_2px left, const pixel *top, const pixel *bottom,
                         int pri, int sec, int dir, int damping, enum CdefEdgeFlags edges HIGHBD_DECL_SUFFIX)
 { (void)dst; (void)stride; (void)left; (void)top; (void)bottom; (void)pri; (void)sec; (void)dir; (void)damping; (void)edges;
-  if (eav1_walk.r) atomic_store(&eav1_walk.r->unsupported, 1); }
+  eav1rec_unsupported(&eav1_walk); }
 void bitfn(eav1rec_cdef_dsp_init)(Dav1dCdefDSPContext *const c)
 {
     c->dir = rec_cdef_dir; c->fb[0] = c->fb[1] = c->fb[2] = rec_cdef_fb;

@@ -86,4 +86,24 @@ def _bind_host(L):
     L.eav1rec_engine.argtypes = [C.c_void_p]
     L.eav1rec_drain.restype = None
     L.eav1rec_drain.argtypes = [C.c_void_p]
+    L.eav1_pump_run.argtypes = [C.POINTER(C.c_char_p), C.POINTER(C.c_size_t), C.c_int, C.c_int, C.c_int, C.c_int,
+                                C.POINTER(C.c_void_p), C.c_size_t, C.POINTER(C.c_int), C.POINTER(C.c_size_t),
+                                C.c_void_p, C.c_void_p]
     return L
+
+
+def pump_run(host, obus, n_workers, cap, apply_grain=1, inloop_filters=7, bufs=None):
+    """host/pump.c: decode len(obus) streams to the end on n_workers threads (every decoder single-threaded, the
+    workers multiplex them). Returns (frames per stream, packed planes of each stream's last picture)."""
+    n = len(obus)
+    keep = [C.create_string_buffer(o, len(o)) if isinstance(o, (bytes, bytearray)) else o for o in obus]
+    ptrs = (C.c_char_p * n)(*[C.cast(k, C.c_char_p) for k in keep])
+    sizes = (C.c_size_t * n)(*[len(o) for o in obus])
+    bufs = bufs or [C.create_string_buffer(cap) for _ in range(n)]
+    outs = (C.c_void_p * n)(*[C.addressof(b) for b in bufs])
+    frames = (C.c_int * n)()
+    used = (C.c_size_t * n)()
+    r = host.eav1_pump_run(ptrs, sizes, n, n_workers, apply_grain, inloop_filters, outs, cap, frames, used, None, None)
+    if r < 0:
+        raise EngineError("eav1_pump_run failed: %d" % r)
+    return list(frames), [bufs[i].raw[:used[i]] for i in range(n)]

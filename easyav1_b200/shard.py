@@ -1,8 +1,8 @@
 """Multi-GPU scaling of the decode path: independent units only.
 
-A unit is one stream, or one closed-GOP segment of a stream (from a temporal unit that carries
-a sequence header up to the next one: every such segment re-initialises all eight reference
-slots, so nothing crosses, src/easyav1.c:1979,2929-2959 seeks on the same boundaries). Units are
+A unit is one stream, or one closed-GOP segment of a stream (from a temporal unit whose first frame
+is a shown key frame behind a sequence header up to the next such unit: a shown key frame refreshes
+all eight reference slots, so nothing crosses; src/easyav1.c:1979,2929-2959 seeks on key frames too). Units are
 dealt round-robin to ranks, each rank owns one GPU, and NOTHING is exchanged on the data path:
 the only collective is the MAX over ranks of the elapsed time (and, in tests, a gather of
 digests). One process per GPU, torch.distributed only as plumbing."""
@@ -38,11 +38,27 @@ def _obus(tu: bytes):
         pos += size
 
 
+def _starts_closed_gop(tu: bytes) -> bool:
+    """True if the temporal unit carries a sequence header AND its first frame header is a shown key frame
+    (show_existing_frame = 0, frame_type = KEY_FRAME, show_frame = 1: only then are all eight reference slots
+    refreshed, AV1 spec 5.9.2 / ext/dav1d/src/obu.c:409-470). Encoders also repeat the sequence header in front of
+    forward key frames and intra-only frames of open GOPs, whose leading frames still reference the previous GOP."""
+    has_seq = False
+    for typ, payload in _obus(tu):
+        if typ == 1:
+            has_seq = True
+        elif typ in (3, 6) and payload:                # OBU_FRAME_HEADER / OBU_FRAME: the first three header fields
+            b = payload[0]
+            show_existing, frame_type, show_frame = b >> 7, (b >> 5) & 3, (b >> 4) & 1
+            return has_seq and not show_existing and frame_type == 0 and show_frame == 1
+    return False
+
+
 def closed_gop_segments(samples):
     """split a list of temporal units into independently decodable segments"""
     segs, cur = [], []
     for tu in samples:
-        starts = any(t == 1 for t, _ in _obus(tu))     # OBU_SEQUENCE_HEADER
+        starts = _starts_closed_gop(tu)
         if starts and cur:
             segs.append(cur)
             cur = []

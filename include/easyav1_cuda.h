@@ -209,6 +209,10 @@ int  eav1cu_device_count(void);
 int  eav1cu_ctx_create(Eav1cuCtx **out, int device);
 void eav1cu_ctx_destroy(Eav1cuCtx *ctx);
 int  eav1cu_last_error(Eav1cuCtx *ctx, char *msg, size_t cap);
+/* Forget a latched EAV1CU_ERR_INVAL (a bad argument of some earlier call); CUDA failures stay latched because the
+ * device context is unusable after them. Returns 0 if the context is usable afterwards. Called by the host side
+ * from dav1d_flush, so that a decoder can restart at the next key frame (ext/dav1d/src/lib.c:526). */
+int  eav1cu_clear_error(Eav1cuCtx *ctx);
 int  eav1cu_set_tables(Eav1cuCtx *ctx, const Eav1Tables *t);
 int  eav1cu_set_masks(Eav1cuCtx *ctx, const uint8_t *blob, size_t bytes);
 int  eav1cu_sync(Eav1cuCtx *ctx);
@@ -280,6 +284,9 @@ int  eav1cu_plan_tickets(const Eav1Cmd *cmds, size_t n_cmds, const int plane_w[3
                          uint32_t *deps, size_t cap_deps, size_t *n_deps);
 /* out[0] kernel launches, out[1] host->device bytes, out[2] device->host bytes, out[3] frames */
 int  eav1cu_counters(Eav1cuCtx *ctx, long long out[4]);
+/* the same four totals over every context of the process since it started (frames submitted through
+ * eav1cu_frame_submit only; staged replays are not counted) */
+int  eav1cu_global_counters(long long out[4]);
 int  eav1cu_set_capture(Eav1cuCtx *ctx, int on);
 /* Test support: which coding tools the frames submitted by this process exercised. Counting is on only when
  * EAV1_COVERAGE is set in the environment when the library is first used (eav1cu_coverage then returns 1,
@@ -317,6 +324,9 @@ int  eav1cu_stage_times(Eav1cuCtx *ctx, double *ms, long long *launches, long lo
 int  eav1cu_staged_count(Eav1cuCtx *ctx);
 int  eav1cu_staged_replay(Eav1cuCtx *ctx, int idx);
 int  eav1cu_staged_info(Eav1cuCtx *ctx, int idx, Eav1StagedInfo *out);
+/* all staged frames in submit order, `passes` times, queued from one C loop (one host thread per context lets
+ * several staged streams share the GPU: bench.py's multi-stream device-resident leg) */
+int  eav1cu_staged_replay_all(Eav1cuCtx *ctx, int passes);
 /* Development aid: replay staged frame idx once with per-unit device timestamps. out gets 6 words
  * per dataflow unit (index = unit id): ticket drawn, producers ready, done (ns), id of the producer
  * that finished last (~0: none), first command << 32 | count, ticket << 32 | CTA << 8 | warp. */

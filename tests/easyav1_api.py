@@ -72,3 +72,39 @@ def decode_webm(L, webm, bpc=8, layout=1):
         hp = C.c_void_p(h)
         L.easyav1_destroy(C.byref(hp))
     return out, finished
+
+
+VIDEO_CB = C.CFUNCTYPE(None, C.POINTER(VideoFrame), C.c_void_p)
+
+
+def play_file(L, path, bpc=8, layout=1, timeout_s=30.0):
+    """easyav1_init_from_filename -> easyav1_play: the library's own playback thread decodes in real time and hands
+    every frame to the video callback (src/easyav1.h:531-551). Returns (MD5s in callback order, finished)."""
+    import time
+    L.easyav1_play.argtypes = [C.c_void_p]
+    L.easyav1_stop.argtypes = [C.c_void_p]
+    L.easyav1_stop.restype = None
+    out = []
+
+    def on_video(frame, userdata):
+        out.append(frame_md5(frame.contents, bpc, layout))
+    cb = VIDEO_CB(on_video)
+    st = L.easyav1_default_settings()
+    st.enable_audio = 0
+    st.skip_unprocessed_frames = 0
+    st.log_level = 1
+    st.cb_video = C.cast(cb, C.c_void_p)
+    h = L.easyav1_init_from_filename(path.encode(), C.byref(st))
+    if not h:
+        raise RuntimeError("easyav1_init_from_filename failed")
+    try:
+        assert L.easyav1_play(h) == 1, "easyav1_play failed"
+        t0 = time.time()
+        while L.easyav1_is_finished(h) != 1 and time.time() - t0 < timeout_s:
+            time.sleep(0.02)
+        finished = L.easyav1_is_finished(h) == 1
+        L.easyav1_stop(h)
+    finally:
+        hp = C.c_void_p(h)
+        L.easyav1_destroy(C.byref(hp))
+    return out, finished

@@ -86,6 +86,7 @@ int eav1cu_device_count(void) { return 1; }
 int eav1cu_ctx_create(Eav1cuCtx **out, int) { if (getenv("EAV1_EMU_BT")) { struct sigaction sa; memset(&sa, 0, sizeof(sa)); sa.sa_sigaction = segv_bt; sa.sa_flags = SA_SIGINFO; sigaction(SIGSEGV, &sa, NULL); } *out = new Eav1cuCtx(); (*out)->pics.reserve(512); return 0; }
 void eav1cu_ctx_destroy(Eav1cuCtx *c) { delete c; }
 int eav1cu_last_error(Eav1cuCtx *c, char *msg, size_t cap) { if (msg && cap) msg[0] = 0; return c->err; }
+int eav1cu_clear_error(Eav1cuCtx *c) { if (c->err == EAV1CU_ERR_INVAL) c->err = 0; return c->err; }
 int eav1cu_set_tables(Eav1cuCtx *c, const Eav1Tables *t) { c->tab = *t; c->have_tab = true; return 0; }
 int eav1cu_set_masks(Eav1cuCtx *c, const uint8_t *b, size_t n) { c->masks.assign(b, b + n); return 0; }
 int eav1cu_sync(Eav1cuCtx *c) { return c->err; }
@@ -209,7 +210,7 @@ int eav1cu_frame_submit(Eav1cuCtx *c, const Eav1FrameDesc *fd, const Eav1Cmd *cm
     fc.masks = c->masks.data();
     // same two-step split as the engine's planner: residual blocks behind the arena (phase 1b),
     // the ITX command itself then only adds (EAV1_F_RESID)
-    static std::vector<Eav1Cmd> patched;
+    static thread_local std::vector<Eav1Cmd> patched;
     patched.assign(cmds, cmds + n);
     size_t off = (arena_bytes + 31) & ~(size_t)31;
     for (size_t i = 0; i < n; i++) {
@@ -226,7 +227,7 @@ int eav1cu_frame_submit(Eav1cuCtx *c, const Eav1FrameDesc *fd, const Eav1Cmd *cm
     if (c->arena.size() < arena_bytes + 16) c->arena.resize(arena_bytes + 16);
     fc.arena = c->arena.data();
     fc.payload = (const uint8_t *)payload;
-    static CtaScratch sm;
+    static thread_local CtaScratch sm;
     for (size_t i = 0; i < n; i++)
         if (cmds[i].op == EAV1_OP_ITX && (cmds[i].flags & EAV1_F_RESID)) {
             if (fd->bpc > 8) exec_itx_residual<BD16>(fc, cmds[i], sm, 0, 1);
@@ -241,13 +242,14 @@ int eav1cu_frame_submit(Eav1cuCtx *c, const Eav1FrameDesc *fd, const Eav1Cmd *cm
 }
 
 int eav1cu_coverage(Eav1Coverage *out, int reset) { return coverage_read(out, reset); }
+size_t eav1cu_abi_sizeof(int which) { return which == 6 ? sizeof(Eav1Coverage) : which == 3 ? sizeof(Eav1FrameDesc) : 0; }
 
 int eav1cu_apply_grain(Eav1cuCtx *c, int src_pic, int dst_pic, const Eav1GrainParams *g)
 {
     const Picture &src = c->pics[src_pic], &dst = c->pics[dst_pic];
     coverage_count_grain(src.bpc, g);
-    static std::vector<uint8_t> buf(36864 + 3 * 4096 + 65536);
-    static FgSmem sm;
+    static thread_local std::vector<uint8_t> buf(36864 + 3 * 4096 + 65536);
+    static thread_local FgSmem sm;
     FgParams P;
     memset(&P, 0, sizeof(P));
     P.g = *g;

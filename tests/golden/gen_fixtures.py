@@ -51,6 +51,48 @@ def synth_frames(w, h, n, seed, noise=3.0, pan=(3, 2)):
     return frames
 
 
+def synth_zoom_frames(w, h, n, seed, noise=0.0):
+    """10-bit frames (uint16 RGB): a low-pass noise field that drifts, rotates and zooms slowly (so that a
+    translational model alone does not predict it), one moving square, optional per-frame noise. Config C4's
+    content recipe."""
+    import math
+    rng = np.random.default_rng(seed)
+    bw, bh = w + 256, h + 256
+    lo = rng.integers(0, 256, size=((bh + 15) // 16 + 2, (bw + 15) // 16 + 2, 3), dtype=np.uint8)
+    field = Image.fromarray(lo).resize((bw, bh), Image.BICUBIC)
+    frames = []
+    for i in range(n):
+        ang = math.radians(0.15 * i)
+        z = 1.0 + 0.003 * i
+        c, s = math.cos(ang) / z, math.sin(ang) / z
+        cx, cy = bw / 2 + 2.0 * i, bh / 2 + 1.0 * i
+        a, b, cc = c, -s, cx - c * w / 2 + s * h / 2
+        d, e, f = s, c, cy - s * w / 2 - c * h / 2
+        img = field.transform((w, h), Image.AFFINE, (a, b, cc, d, e, f), resample=Image.BILINEAR)
+        arr = np.asarray(img, dtype=np.float32).copy()
+        r = h // 10
+        x0 = int((0.2 + 0.6 * i / max(n - 1, 1)) * w)
+        y0 = int(0.3 * h)
+        arr[y0 - r:y0 + r, x0 - r:x0 + r] = (220, 40, 40)
+        arr += rng.normal(0.0, noise, size=arr.shape).astype(np.float32)
+        frames.append(np.clip(arr * 4.0, 0, 1023).astype(np.uint16))
+    return frames
+
+
+def encode_cv2_10bit(frames16, quality, speed):
+    """uint16 10-bit RGB frames through OpenCV's animated-AVIF writer (libavif/aom)"""
+    import cv2
+    anim = cv2.Animation()
+    anim.frames = [cv2.cvtColor((a << 6).astype(np.uint16), cv2.COLOR_RGB2BGR) for a in frames16]
+    anim.durations = [33] * len(frames16)
+    path = "/tmp/_eav1_fixture.avif"
+    assert cv2.imwriteanimation(path, anim, [cv2.IMWRITE_AVIF_DEPTH, 10, cv2.IMWRITE_AVIF_QUALITY, quality,
+                                             cv2.IMWRITE_AVIF_SPEED, speed])
+    buf = open(path, "rb").read()
+    os.remove(path)
+    return buf
+
+
 def boxes(buf, start, end):
     pos = start
     while pos + 8 <= end:
@@ -209,6 +251,12 @@ CLIPS = {
     # unknown (src/easyav1.c:3493-3503)
     "c1_360p_webm": (640, 360, 48, 2, {"enable-cdef": "1", "enable-restoration": "1", "chroma-sample-position": "1",
                                        "container": "webm"}, 55, 6),
+    # config C1 at its full length (BASELINE.json configs[0]: 240 frames), the bench's easyAV1-API leg
+    "c1_360p_bench": (640, 360, 240, 3, {"enable-cdef": "1", "enable-restoration": "1", "chroma-sample-position": "1",
+                                        "container": "webm"}, 55, 6),
+    # config C4 for the bench (BASELINE.json configs[3]): 3840x2160 10-bit, 30 frames of drifting / rotating /
+    # zooming content. Quality 12 keeps the file at 7.7 MB (at quality 30-40 the same content costs 1 MB per frame)
+    "c4_2160p_10bit_bench": (3840, 2160, 30, 34, {"depth": 10, "content": "zoom"}, 12, 8, 0.0),
     # the bench workload (BASELINE.json configs[1]): same recipe, 120 frames. Speed 4 because
     # speed 6 never signals loop restoration on this content (checked from the recorded frames)
     "c2_1080p_bench": (1920, 1080, 120, 7, {"enable-cdef": "1", "enable-restoration": "1"}, 60, 4, 6.0),
@@ -224,8 +272,11 @@ def main():
         noise = spec[7] if len(spec) > 7 else 3.0
         if only and name not in only:
             continue
-        frames = synth_frames(w, h, n, seed, noise=noise)
-        avif = encode_cv2(frames, adv["depth"], q, spd) if "depth" in adv else encode(frames, adv, q, spd)
+        if adv.get("content") == "zoom":
+            avif = encode_cv2_10bit(synth_zoom_frames(w, h, n, seed, noise=noise), q, spd)
+        else:
+            frames = synth_frames(w, h, n, seed, noise=noise)
+            avif = encode_cv2(frames, adv["depth"], q, spd) if "depth" in adv else encode(frames, adv, q, spd)
         samples = avif_samples(avif)
         ivf = os.path.join(HERE, name + ".ivf")
         write_ivf(ivf, samples, w, h)

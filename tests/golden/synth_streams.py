@@ -49,6 +49,7 @@ def _scaled(seed, bpc=8, layout=1):
         st.frame(1, offset=2, qidx=100, refresh=2, size=(136, 104), refidx=(0, 0, 0, 1, 1, 1, 2))
         st.frame(1, offset=3, qidx=100, refresh=4, size=(256, 192), refidx=(0, 1, 2, 0, 1, 2, 0))  # larger than them
         st.frame(1, offset=4, qidx=100, refresh=8, size_from_ref=1, refidx=(2, 1, 0, 2, 1, 0, 2))
+        st.frame(1, offset=5, qidx=100, refresh=16, size=(200, 144), refidx=(0, 1, 2, 3, 0, 1, 2), filter=3)  # bilinear, scaled
         return st
     return b
 
@@ -65,6 +66,7 @@ def _gmv(seed, bpc=8):
         st.frame(1, offset=3, qidx=100, refresh=4, gmv=g, filter=3, switchable_motion_mode=0, ref_select=0)
         st.frame(1, offset=4, qidx=100, refresh=8, filter=1)
         st.frame(1, offset=5, qidx=100, refresh=16, filter=2, warp_motion=0)
+        st.frame(1, offset=6, qidx=100, refresh=32, filter=3)                        # bilinear with compound references
         return st
     return b
 
@@ -128,8 +130,8 @@ def _superres(seed, bpc=8, layout=1, w=264, h=136, cdef=1, lr=1, sb128=0):
 # name -> (builder, in the quick CPU subset?)
 STREAMS = {
     "syn_420_8":        (_plain(352, 288), True),
-    "syn_420_10":       (_plain(200, 136, 10, seed=2), False),
-    "syn_420_12":       (_plain(200, 136, 12, seed=3), True),
+    "syn_420_10":       (_plain(352, 288, 10, seed=2), False),
+    "syn_420_12":       (_plain(352, 288, 12, seed=3), True),
     "syn_444_8":        (_plain(136, 120, 8, 3, seed=4), False),
     "syn_444_12":       (_plain(136, 120, 12, 3, seed=5), False),
     "syn_422_10":       (_plain(128, 128, 10, 2, seed=140, n_inter=2), False),

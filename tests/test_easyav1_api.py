@@ -1,7 +1,8 @@
 """Drop-in at the top boundary: the reference's src/easyav1.c + nestegg,
 compiled unmodified and linked against libdav1d_b200.so, play a WebM file through the public
-easyAV1 API (easyav1_init_from_memory / easyav1_decode_next / easyav1_get_video_frame) and every
-frame handed out must carry the MD5 the reference decoder gave (tests/golden/manifest.json)."""
+easyAV1 API (easyav1_init_from_memory / easyav1_decode_next / easyav1_get_video_frame, and
+easyav1_init_from_filename / easyav1_play with the video callback) and every frame handed out must carry the
+MD5 the reference decoder gave (tests/golden/manifest.json)."""
 import json
 import os
 import subprocess
@@ -32,6 +33,45 @@ def run(lib, name, manifest):
     res = json.loads(out.stdout.strip().splitlines()[-1])
     assert res["finished"]
     assert res["md5"] == [f["md5"] for f in man["frames"]]
+
+
+PLAY_SCRIPT = """
+import json, sys
+sys.path.insert(0, %r)
+from tests import easyav1_api as ea
+L = ea.bind(sys.argv[1])
+md5s, finished = ea.play_file(L, sys.argv[2])
+print(json.dumps({'md5': md5s, 'finished': finished}))
+""" % ROOT
+
+
+def run_play(lib, name, manifest):
+    """easyav1_init_from_filename + easyav1_play: real-time playback on the library's own thread; every frame the
+    video callback receives must be one of the golden frames, in stream order, and playback must reach the end."""
+    want = [f["md5"] for f in manifest[name]["frames"]]
+    path = os.path.join(GOLDEN, name + ".webm")
+    out = subprocess.run([sys.executable, "-c", PLAY_SCRIPT, lib, path], capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0, out.stderr[-2000:]
+    res = json.loads(out.stdout.strip().splitlines()[-1])
+    assert res["finished"]
+    got = res["md5"]
+    assert len(got) >= len(want) // 2, "playback delivered %d of %d frames" % (len(got), len(want))
+    pos = -1
+    for m in got:          # in order, each a golden frame (late frames may be dropped by the player, never altered)
+        assert m in want[pos + 1:], "callback frame is not the next golden frame"
+        pos = want.index(m, pos + 1)
+
+
+def test_easyav1_play_over_emulated_engine(manifest):
+    lib = os.path.join(ROOT, "tests", "emu", "libeasyav1_b200_emu.so")
+    if not os.path.exists(lib):
+        pytest.skip("tests/emu not built")
+    run_play(lib, "c1_360p_webm", manifest)
+
+
+@pytest.mark.gpu
+def test_easyav1_play_cuda(manifest):
+    run_play(os.path.join(ROOT, "easyav1_b200", "libeasyav1_b200.so"), "c1_360p_webm", manifest)
 
 
 def test_easyav1_api_over_emulated_engine(manifest):

@@ -63,3 +63,45 @@ def test_fastdiv_is_exact_over_its_documented_range():
     L.eav1emu_fastdiv_mismatches.restype = C.c_longlong
     L.eav1emu_fastdiv_mismatches.argtypes = [C.c_int, C.c_int]
     assert L.eav1emu_fastdiv_mismatches(1024, 1 << 22) == 0
+
+
+def test_failed_frame_does_not_poison_the_decoder(manifest):
+    """One frame the recorder cannot express (forced with EAV1_TEST_FAIL_FRAME) fails alone, the frames that
+    reference it fail with it (DAV1D_ERR(EIO), as after a damaged frame in dav1d), and the SAME decoder is
+    bit-exact again from the next key frame on."""
+    import ctypes as C
+    import hashlib
+    code = r"""
+import sys, json, hashlib, ctypes as C
+sys.path.insert(0, %r)
+from easyav1_b200.lib import load_host, StreamFrame
+from tests.golden.gen_fixtures import read_ivf
+man = json.load(open(%r))["cif_inter"]
+tus = read_ivf(%r)
+obu = b"".join(tus + tus)
+host = load_host(%r)
+keep = C.create_string_buffer(obu, len(obu))
+h = host.eav1_stream_open(keep, len(obu), 1, 7, 1)
+buf = C.create_string_buffer(1 << 20); info = StreamFrame(); used = C.c_size_t()
+res = []
+while len(res) < 64:
+    r = host.eav1_stream_next(h, C.byref(info), buf, 1 << 20, C.byref(used))
+    if r == 1: break
+    res.append(r if r < 0 else hashlib.md5(buf.raw[:used.value]).hexdigest())
+host.eav1_stream_close(h)
+print(json.dumps(res))
+""" % (ROOT, os.path.join(ROOT, "tests", "golden", "manifest.json"),
+       os.path.join(ROOT, "tests", "golden", "cif_inter.ivf"), EMU_HOST)
+    if not os.path.exists(EMU_HOST):
+        pytest.skip("tests/emu not built (needs the reference sources)")
+    want = [f["md5"] for f in manifest["cif_inter"]["frames"]]
+    for threads in ("1", "3"):
+        env = dict(os.environ, EAV1_TEST_FAIL_FRAME="2", EASYAV1_THREADS=threads)
+        r = subprocess.run([sys.executable, "-c", code], env=env, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, timeout=300)
+        assert r.returncode == 0, r.stderr[-2000:]
+        got = json.loads(r.stdout.strip().splitlines()[-1])
+        assert len(got) == 2 * len(want)
+        assert got[0] == want[0]
+        assert any(isinstance(x, int) and x < 0 for x in got[:len(want)])          # the damaged GOP reports errors ...
+        assert all(isinstance(x, int) or x == want[i] for i, x in enumerate(got[:len(want)]))   # ... never wrong pictures
+        assert got[len(want):] == want                                               # and the next GOP is exact again

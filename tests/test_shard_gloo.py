@@ -84,3 +84,21 @@ def test_two_ranks_equal_one(manifest):
         p.join(timeout=60)
         assert p.exitcode == 0
     assert merged == single and total == len(names) and dt > 0
+
+
+def test_open_gop_is_not_split():
+    """A sequence header in front of a hidden (forward) key frame or an intra-only frame does not start an
+    independently decodable segment: only a shown key frame refreshes all eight reference slots."""
+    from tests.golden.obu_synth import Seq, Stream
+    st = Stream(Seq(64, 64), 5)
+    st.frame(0, qidx=100)                                                  # shown key frame: segment 1
+    st.frame(1, offset=1, qidx=100, refresh=1)
+    st.frame(0, show_frame=0, showable=1, refresh=2, offset=4, qidx=100)   # forward key frame behind a sequence header
+    st.frame(1, offset=2, qidx=100, refresh=4)                             # still references the first GOP
+    st.frame(0, qidx=100)                                                  # shown key frame: segment 2
+    st.frame(1, offset=1, qidx=100, refresh=1)
+    tus = st.samples()
+    assert sum(1 for tu in tus if any(t == 1 for t, _ in shard._obus(tu))) == 3
+    segs = shard.closed_gop_segments(tus)
+    assert [len(s) for s in segs] == [4, 2]
+    assert b"".join(sum(segs, [])) == b"".join(tus)

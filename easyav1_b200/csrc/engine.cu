@@ -894,9 +894,13 @@ int eav1cu_arena_upload(Eav1cuCtx *ctx, size_t off, const void *src, size_t byte
     if (!ctx) return EAV1CU_ERR_INVAL;
     CK(cudaSetDevice(ctx->device));
     if (off + bytes > ctx->arena.cap) {
-        // grow, preserving nothing (tests upload before the first submit)
-        int r = ensure(ctx, ctx->arena, off + bytes, false);
+        // grow, keeping what earlier uploads put there
+        CK(cudaStreamSynchronize(ctx->stream));
+        DevBuf bigger;
+        int r = ensure(ctx, bigger, (off + bytes) * 2, false);
         if (r) return r;
+        if (ctx->arena.d) { CK(cudaMemcpy(bigger.d, ctx->arena.d, ctx->arena.cap, cudaMemcpyDeviceToDevice)); cudaFree(ctx->arena.d); }
+        ctx->arena.d = bigger.d; ctx->arena.cap = bigger.cap;
     }
     CK(cudaMemcpy(ctx->arena.d + off, src, bytes, cudaMemcpyHostToDevice));
     return 0;
@@ -1020,7 +1024,12 @@ static int plan_build(Eav1cuCtx *ctx, FramePlan &pl, bool staged, const Eav1Fram
         if (has_cdef && has_lr && (r = pic_setup(ctx, ctx->work[1], cur.w, cur.h, cur.layout, cur.bpc))) return r;
     }
     Uploader up{ctx, staged ? &pl : nullptr};
+    // `pl` may be the context's reused live plan: nothing of the previous frame may survive (a submission without
+    // commands skips the block below)
     pl.n_chains = pl.n_deps = pl.n_levels = 0;
+    pl.n_items = pl.n_ritems = pl.n_ritems_small = pl.n_flat_big = pl.n_flat_small = pl.n_big = pl.n_small = 0;
+    pl.d_cmds = nullptr; pl.d_deps = nullptr; pl.d_items = nullptr; pl.d_ritems = nullptr; pl.d_recs = nullptr; pl.d_flat = nullptr;
+    pl.d_payload = nullptr; pl.resid_px = 0;
     pl.arena_bytes = arena_bytes; pl.payload_bytes = payload_bytes; pl.n_cmds = n_cmds;
     if (n_cmds) {
         int pw[3] = { cur.pl[0].w, cur.pl[1].w, cur.pl[2].w };
@@ -1185,7 +1194,14 @@ static int plan_build(Eav1cuCtx *ctx, FramePlan &pl, bool staged, const Eav1Fram
             up.put(rt.data(), rt.size() * sizeof(ChainRec), &pl.d_recs);
         } else { pl.n_big = pl.n_small = 0; }
         up.put(payload, payload_bytes, &pl.d_payload);
-        if ((r = ensure(ctx, ctx->arena, arena_bytes + 16, false))) return r;
+        if (arena_bytes + 16 > ctx->arena.cap) {
+            // grow; the old contents are kept (operator-level callers upload prep blocks before they submit)
+            CK(cudaStreamSynchronize(ctx->stream));
+            DevBuf bigger;
+            if ((r = ensure(ctx, bigger, arena_bytes + 16, false))) return r;
+            if (ctx->arena.d) { CK(cudaMemcpy(bigger.d, ctx->arena.d, ctx->arena.cap, cudaMemcpyDeviceToDevice)); cudaFree(ctx->arena.d); }
+            ctx->arena.d = bigger.d; ctx->arena.cap = bigger.cap;
+        }
         if (g.unit_cmd.size() > ctx->done_cap) {
             if (ctx->d_done) { CK(cudaStreamSynchronize(ctx->stream)); cudaFree(ctx->d_done); ctx->d_done = nullptr; }
             const size_t cap = g.unit_cmd.size() * 2 + 4096;
@@ -1242,6 +1258,10 @@ static int plan_launch(Eav1cuCtx *ctx, FramePlan &pl)
     fc.masks = ctx->d_masks;
     fc.arena = ctx->arena.d;
     fc.payload = pl.d_payload;
+    // A submission without commands is a post-filter call on its own (operator-level use): fd->cur then holds the
+    // reconstructed, unfiltered frame, which the filters expect in A.
+    if (!pl.n_cmds && A.base != cur.base)
+        CK(cudaMemcpyAsync(A.base, cur.base, std::min(A.bytes, cur.bytes), cudaMemcpyDeviceToDevice, st));
     // Phase 1: motion compensation on the main stream, the residuals of the same frame beside it
     // on a second stream (they share nothing); the dataflow kernel waits for both.
     const bool fork = pl.n_ritems && ctx->stream2 && !ctx->serial_phase1;

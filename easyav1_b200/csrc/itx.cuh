@@ -497,6 +497,11 @@ EAV1_DEV TxDim tx_dim(int tx) {
 // consecutive addresses), the only shared-memory traffic is the transpose between the passes,
 // and the second pass adds into the destination directly. One group barrier per transform.
 
+// A residual travels as int16. The only value that does not fit is +32768: a 12-bit 32-point identity column whose
+// input sits at the inter-pass clip limit (131071 * 4 + 8 >> 4). Saturating it to 32767 cannot change the
+// reconstructed sample, which is clipped to bitdepth_max <= 4095 after the add (found by tests/test_ops.py).
+EAV1_DEV int16_t res16(int v) { return (int16_t)(v > 32767 ? 32767 : v); }
+
 // N-point 1-D transform of kind `type` (T1D_FLIPADST is computed as ADST; the caller mirrors
 // the output index), in place on a register array.
 template <typename W, int N>
@@ -561,7 +566,7 @@ EAV1_DEV void itx_col_reg(const int32_t *s, int P, int x, int type, int col_min,
     if (res) {   // residual only (phase 1): row-major int16 block, added to the prediction later
         itx_1d_reg<W, N>(type, v, col_min, col_max);
 #pragma unroll
-        for (int y = 0; y < N; y++) res[(flip ? N - 1 - y : y) * res_stride + x] = (int16_t)((v[y] + 8) >> 4);
+        for (int y = 0; y < N; y++) res[(flip ? N - 1 - y : y) * res_stride + x] = res16((v[y] + 8) >> 4);
         return;
     }
     pixel *d = dst + x;
@@ -701,7 +706,7 @@ EAV1_DEVH void itx_add(typename BD::pixel *dst, int dst_stride /*pixels*/, const
     if (res) {
         for (int i = tid; i < w * h; i += nthr) {
             const int y = i / w, x = i - y * w;
-            res[i] = (int16_t)((s[x * P + y] + 8) >> 4);
+            res[i] = res16((s[x * P + y] + 8) >> 4);
         }
         CTA_SYNC();
         return;

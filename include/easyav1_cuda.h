@@ -239,6 +239,9 @@ int  eav1cu_fence_wait(Eav1cuCtx *ctx, unsigned long long ticket);
 /* Reconstruct one frame from its recorded commands (in host walk order) and run the in-loop
  * post filters; the result stays resident as picture fd->cur. Asynchronous on the context's
  * stream; eav1cu_pic_download / eav1cu_sync order after it. */
+/* Per-call (operator-level) use, as tests/test_ops.py drives it: a command list of independent commands with no
+ * post-filter side data runs exactly those DSP operators on picture fd->cur; a submission with n_cmds == 0 runs only
+ * the post filters described by fd on the samples fd->cur already holds. */
 int  eav1cu_frame_submit(Eav1cuCtx *ctx, const Eav1FrameDesc *fd,
                          const Eav1Cmd *cmds, size_t n_cmds,
                          const void *payload, size_t payload_bytes, size_t arena_bytes);

@@ -196,6 +196,7 @@ int eav1cu_frame_submit(Eav1cuCtx *c, const Eav1FrameDesc *fd, const Eav1Cmd *cm
         if (has_cdef && has_lr) pic_setup(c->work[1], cur.w, cur.h, cur.layout, cur.bpc);
         A = &c->work[0];
     }
+    if (!n && A != &cur) memcpy(A->mem.data(), cur.mem.data(), std::min(A->mem.size(), cur.mem.size()));   // post-filter call on its own
     FrameCtx fc;
     memset(&fc, 0, sizeof(fc));
     for (int i = 0; i < 3; i++) fc.cur[i] = A->pl[i];

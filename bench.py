@@ -396,6 +396,16 @@ class Staged:
         if r:
             raise RuntimeError("replay failed: %d" % r)
 
+    def graph_build(self):
+        r = self.E.eav1cu_staged_graph_build(self.eng)
+        if r:
+            raise RuntimeError("graph capture failed: %d" % r)
+
+    def graph_replay(self, passes=1):
+        r = self.E.eav1cu_staged_graph_launch(self.eng, passes)
+        if r:
+            raise RuntimeError("graph replay failed: %d" % r)
+
     def last_frame_md5(self):
         si = self.infos[-1]
         w, hh, bps = si.w, si.h, 2 if si.bpc > 8 else 1
@@ -523,7 +533,7 @@ def roofline_of(dev, names=STAGE_NAMES):
             "stages": stages}
 
 
-def multi_stream_device(E, host, man, obu, n_streams, passes, torch):
+def multi_stream_device(E, host, man, obu, n_streams, passes, torch, graph=True, sampler=None):
     """S staged decoders, each on its own CUDA stream and host thread, replayed together: aggregate frames/s and
     GB/s of the device alone (inputs resident in HBM). One start event, one end event per stream; the elapsed time
     is the latest end."""
@@ -531,8 +541,15 @@ def multi_stream_device(E, host, man, obu, n_streams, passes, torch):
     streams = [torch.cuda.Stream() for _ in range(n_streams)]
     for st, s in zip(sts, streams):
         st.set_stream(s)
+        if graph:
+            st.graph_build()
 
     def run(p):
+        if graph:               # one cudaGraphLaunch per stream and pass: a single host thread keeps all streams fed
+            for _ in range(p):
+                for st in sts:
+                    st.graph_replay(1)
+            return
         ts = [threading.Thread(target=st.replay, args=(p,)) for st in sts]
         for t in ts:
             t.start()
@@ -549,11 +566,14 @@ def multi_stream_device(E, host, man, obu, n_streams, passes, torch):
     a = torch.cuda.Event(enable_timing=True)
     ends = [torch.cuda.Event(enable_timing=True) for _ in sts]
     torch.cuda.synchronize()
+    if sampler:
+        sampler.start()
     a.record(streams[0])
     run(passes)
     for e, s in zip(ends, streams):
         e.record(s)
     torch.cuda.synchronize()
+    clk = sampler.stop() if sampler else None
     ms = max(a.elapsed_time(e) for e in ends)
     launches = 0
     for st, c in zip(sts, cnt0):
@@ -568,7 +588,9 @@ def multi_stream_device(E, host, man, obu, n_streams, passes, torch):
         st.close()
     frames = n_streams * passes * len(man["frames"])
     return {"streams": n_streams, "passes": passes, "value": frames / (ms / 1e3), "unit": UNIT, "ms": round(ms, 3),
-            "whole_frame_gbs": round(alg / 1e9 / (ms / 1e3), 1), "gpu_launches": launches}
+            "whole_frame_gbs": round(alg / 1e9 / (ms / 1e3), 1), "gpu_launches": launches,
+            "replay": "one CUDA graph per stream (all frames captured once)" if graph else "direct launches, one host thread per stream",
+            **({"gpu_util_mean": clk.get("gpu_util_mean"), "sm_mhz": clk.get("sm_mhz")} if clk else {})}
 
 
 def pump_e2e(host, man, obu, n_streams, passes, workers):
@@ -887,10 +909,9 @@ def run_ours(args):
     # ---- configs[4] (C5) on one GPU: device-resident S-stream replay, 64 streams end to end
     if want("c5"):
         peak, _ = measured_peak()
-        clocks = ClockSampler(local)
-        clocks.start()
-        devs = [multi_stream_device(E, host, man, obu, s, 3, torch) for s in (1, 4, 16)]
-        clk5 = clocks.stop()
+        devs = [multi_stream_device(E, host, man, obu, s, max(8, 96 // s), torch, sampler=ClockSampler(local)) for s in (1, 4, 16)]
+        devs.append(multi_stream_device(E, host, man, obu, 4, 24, torch, graph=False))
+        clk5 = {"gpu_util_mean": max((d.get("gpu_util_mean") or 0) for d in devs)}
         workers = cores + cores // 4
         pump_e2e(host, man, obu, N_STREAMS_C5, 1, workers)          # warm
         last, n5, t5, st5 = pump_e2e(host, man, obu, N_STREAMS_C5, 1, workers)
@@ -903,7 +924,7 @@ def run_ours(args):
             "roofline": {"bound": "hbm", "kernel": "whole frame, %d staged streams replayed together" % best["streams"],
                          "achieved": best["whole_frame_gbs"], "peak": peak, "unit": "GB/s",
                          "frac": round(best["whole_frame_gbs"] / peak, 5), "traffic": None},
-            "gpu_util_mean_during_device_legs": clk5.get("gpu_util_mean"),
+            "gpu_util_mean_best_device_leg": clk5.get("gpu_util_mean"),
             "e2e": {"value": n5 / t5, "unit": UNIT, "streams": N_STREAMS_C5,
                     "host_pipeline": "host/pump.c: 64 single-threaded decoders on %d worker threads" % workers,
                     "h2d_bytes_per_step": st5["h2d"], "d2h_bytes_per_step": st5["d2h"], "gpu_launches": st5["launches"]},

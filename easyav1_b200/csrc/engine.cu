@@ -522,6 +522,8 @@ struct Eav1cuCtx {
     bool own_stream = true;
     cudaStream_t stream2 = nullptr;            // phase 1b (residuals) runs beside phase 1 (motion compensation)
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+    cudaEvent_t ev_fg_ready = nullptr, ev_fg_free = nullptr;   // film grain: templates built on stream2, applied on the main stream
+    bool fg_busy = false;
     // optional per-stage device timing (bench.py's roofline leg)
     bool stage_timing = false;
     struct Span { cudaEvent_t a, b; int stage; int launches; };
@@ -530,6 +532,8 @@ struct Eav1cuCtx {
     double stage_ms[EAV1CU_N_STAGES] = {};
     long long stage_launches[EAV1CU_N_STAGES] = {}, stage_calls[EAV1CU_N_STAGES] = {};
     bool capture = false;
+    cudaGraph_t staged_graph = nullptr;          // every staged frame in submit order, captured once (eav1cu_staged_graph_build)
+    cudaGraphExec_t staged_exec = nullptr;
     FramePlan live;
     std::vector<FramePlan *> staged;
 };
@@ -688,10 +692,14 @@ static void ctx_free(Eav1cuCtx *ctx)
     for (auto &sp : ctx->spans) { cudaEventDestroy(sp.a); cudaEventDestroy(sp.b); }
     for (cudaEvent_t e : ctx->ev_pool) cudaEventDestroy(e);
     for (FramePlan *sp : ctx->staged) { for (void *d : sp->owned) cudaFree(d); delete sp; }
+    if (ctx->staged_exec) cudaGraphExecDestroy(ctx->staged_exec);
+    if (ctx->staged_graph) cudaGraphDestroy(ctx->staged_graph);
     if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
     if (ctx->stream2) cudaStreamDestroy(ctx->stream2);
     if (ctx->ev_fork) cudaEventDestroy(ctx->ev_fork);
     if (ctx->ev_join) cudaEventDestroy(ctx->ev_join);
+    if (ctx->ev_fg_ready) cudaEventDestroy(ctx->ev_fg_ready);
+    if (ctx->ev_fg_free) cudaEventDestroy(ctx->ev_fg_free);
     delete ctx;
 }
 
@@ -709,6 +717,8 @@ void eav1cu_ctx_destroy(Eav1cuCtx *ctx)
                     1e3 * ctx->t_pack / ctx->n_frames, 1e3 * ctx->t_lock / ctx->n_frames, 1e3 * ctx->t_copycall / ctx->n_frames, 1e3 * ctx->t_launch / ctx->n_frames);
         for (FramePlan *sp : ctx->staged) { for (void *d : sp->owned) cudaFree(d); delete sp; }
         ctx->staged.clear();
+        if (ctx->staged_exec) { cudaGraphExecDestroy(ctx->staged_exec); ctx->staged_exec = nullptr; }
+        if (ctx->staged_graph) { cudaGraphDestroy(ctx->staged_graph); ctx->staged_graph = nullptr; }
         for (auto &p : ctx->pics) p.used = false;
         ctx->have_tab = false;
         ctx->capture = false; ctx->stage_timing = false;
@@ -1638,6 +1648,55 @@ int eav1cu_staged_replay_all(Eav1cuCtx *ctx, int passes)
     return 0;
 }
 
+/* The staged frames of a context as ONE CUDA graph: the launches of all frames (both streams of phase 1, the
+ * device-to-device copy of loop restoration) are captured once, a replay is a single cudaGraphLaunch. The dataflow
+ * kernel's done flags carry launch epochs that are baked into the captured arguments, so the graph starts by clearing
+ * this context's flags (an epoch can then never be met again from an earlier replay). Launch-bound replays (several
+ * staged streams sharing the GPU) then run at the device's pace instead of the host's. */
+int eav1cu_staged_graph_build(Eav1cuCtx *ctx)
+{
+    if (!ctx || ctx->staged.empty()) return EAV1CU_ERR_INVAL;
+    if (ctx->err) return ctx->err;
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaStreamSynchronize(ctx->stream));
+    if (ctx->staged_exec) { cudaGraphExecDestroy(ctx->staged_exec); ctx->staged_exec = nullptr; }
+    if (ctx->staged_graph) { cudaGraphDestroy(ctx->staged_graph); ctx->staged_graph = nullptr; }
+    const bool timing = ctx->stage_timing;
+    ctx->stage_timing = false;
+    std::lock_guard<SubmitMutex> g(g_submit_mu);
+    CK(cudaStreamBeginCapture(ctx->stream, cudaStreamCaptureModeThreadLocal));
+    int r = 0;
+    if (ctx->d_done && cudaMemsetAsync(ctx->d_done, 0, ctx->done_cap * 4, ctx->stream) != cudaSuccess) r = EAV1CU_ERR_CUDA;
+    for (FramePlan *pl : ctx->staged) {
+        if (r) break;
+        r = plan_launch(ctx, *pl);
+    }
+    cudaGraph_t graph = nullptr;
+    const cudaError_t e = cudaStreamEndCapture(ctx->stream, &graph);
+    ctx->stage_timing = timing;
+    if (r || e != cudaSuccess) {
+        if (graph) cudaGraphDestroy(graph);
+        cudaGetLastError();
+        return r ? r : fail(ctx, EAV1CU_ERR_CUDA, "cudaStreamEndCapture", e);
+    }
+    ctx->staged_graph = graph;
+    CK(cudaGraphInstantiate(&ctx->staged_exec, graph, 0));
+    return 0;
+}
+
+int eav1cu_staged_graph_launch(Eav1cuCtx *ctx, int passes)
+{
+    if (!ctx || !ctx->staged_exec || passes < 0) return EAV1CU_ERR_INVAL;
+    if (ctx->err) return ctx->err;
+    CK(cudaSetDevice(ctx->device));
+    for (int p = 0; p < passes; p++) {
+        std::lock_guard<SubmitMutex> g(g_submit_mu);
+        CK(cudaGraphLaunch(ctx->staged_exec, ctx->stream));
+        ctx->n_launches += (long long)ctx->staged.size();     // counted per frame: one graph launch replaces these
+    }
+    return 0;
+}
+
 /* Development aid: replay staged frame idx once with per-unit timestamps. out receives 6 words per
  * dataflow unit, indexed by unit id (decode order): ticket drawn, producers ready, done (global
  * timer, ns), id of the producer that finished last (~0 = none), first command << 32 | count,
@@ -1732,10 +1791,23 @@ int eav1cu_apply_grain(Eav1cuCtx *ctx, int src_pic, int dst_pic, const Eav1Grain
     P.offsets = ctx->d_fg + FG_GRAIN_BYTES + FG_SCALE_BYTES;
     std::lock_guard<SubmitMutex> gs(g_submit_mu);
     StageTimer tm(ctx, 5);
-    fg_prepare_kernel<<<1, 256, 0, ctx->stream>>>(P);
+    // The templates, LUTs and offsets depend on the parameters only (one CTA, ~0.1 ms of dependent steps): they are
+    // built on the second stream while the kernels of the frame itself still run on the main one; the apply kernel
+    // waits for them, and the next call's build waits until this apply has finished with the shared scratch.
+    const bool side = ctx->stream2 && !ctx->serial_phase1 && !ctx->stage_timing;
+    if (side && !ctx->ev_fg_ready) {
+        if (cudaEventCreateWithFlags(&ctx->ev_fg_ready, cudaEventDisableTiming) != cudaSuccess ||
+            cudaEventCreateWithFlags(&ctx->ev_fg_free, cudaEventDisableTiming) != cudaSuccess)
+            return fail(ctx, EAV1CU_ERR_CUDA, "film grain events");
+    }
+    cudaStream_t ps = side ? ctx->stream2 : ctx->stream;
+    if (side && ctx->fg_busy) CK(cudaStreamWaitEvent(ps, ctx->ev_fg_free, 0));
+    fg_prepare_kernel<<<1, 256, 0, ps>>>(P);
+    if (side) { CK(cudaEventRecord(ctx->ev_fg_ready, ps)); CK(cudaStreamWaitEvent(ctx->stream, ctx->ev_fg_ready, 0)); }
     const dim3 grid((P.cols + FG_STRIP - 1) / FG_STRIP, P.rows);
     if (src.bpc > 8) fg_apply_kernel<uint16_t><<<grid, 256, 0, ctx->stream>>>(P);
     else fg_apply_kernel<uint8_t><<<grid, 256, 0, ctx->stream>>>(P);
+    if (side) { CK(cudaEventRecord(ctx->ev_fg_free, ctx->stream)); ctx->fg_busy = true; }
     ctx->n_launches += 2;
     CK(cudaGetLastError());
     return 0;

@@ -30,6 +30,9 @@ def load_engine():
         E.eav1cu_set_capture.argtypes = [C.c_void_p, C.c_int]
         E.eav1cu_staged_count.argtypes = [C.c_void_p]
         E.eav1cu_staged_replay.argtypes = [C.c_void_p, C.c_int]
+        E.eav1cu_staged_replay_all.argtypes = [C.c_void_p, C.c_int]
+        E.eav1cu_staged_graph_build.argtypes = [C.c_void_p]
+        E.eav1cu_staged_graph_launch.argtypes = [C.c_void_p, C.c_int]
         E.eav1cu_staged_info.argtypes = [C.c_void_p, C.c_int, C.POINTER(StagedInfo)]
         E.eav1cu_set_stream.argtypes = [C.c_void_p, C.c_void_p]
         E.eav1cu_set_stage_timing.argtypes = [C.c_void_p, C.c_int]

@@ -330,6 +330,11 @@ int  eav1cu_staged_info(Eav1cuCtx *ctx, int idx, Eav1StagedInfo *out);
 /* all staged frames in submit order, `passes` times, queued from one C loop (one host thread per context lets
  * several staged streams share the GPU: bench.py's multi-stream device-resident leg) */
 int  eav1cu_staged_replay_all(Eav1cuCtx *ctx, int passes);
+/* The same replay captured once as a CUDA graph (every kernel of every staged frame, both phase-1 streams, the
+ * flag reset in front): _build captures and instantiates, _launch queues `passes` replays, one cudaGraphLaunch each.
+ * The stream passed to eav1cu_set_stream (or the context's own) is the capture and launch stream. */
+int  eav1cu_staged_graph_build(Eav1cuCtx *ctx);
+int  eav1cu_staged_graph_launch(Eav1cuCtx *ctx, int passes);
 /* Development aid: replay staged frame idx once with per-unit device timestamps. out gets 6 words
  * per dataflow unit (index = unit id): ticket drawn, producers ready, done (ns), id of the producer
  * that finished last (~0: none), first command << 32 | count, ticket << 32 | CTA << 8 | warp. */

@@ -71,7 +71,7 @@ template <typename BD>
 EAV1_DEV void exec_itx_residual(const FrameCtx &fc, const Eav1Cmd &c, CtaScratch &sm, int tid, int nthr)
 {
     itx_add<BD>(nullptr, 0, (const typename BD::coef *)(fc.payload + c.u.itx.cf_off), c.u.itx.eob, c.u.itx.tx,
-                c.u.itx.txtp, fc.bitdepth_max, sm.itx, tid, nthr, reinterpret_cast<int16_t *>(fc.arena + c.dst_off));
+                c.u.itx.txtp, fc.bitdepth_max, sm.itx, tid, nthr, reinterpret_cast<int16_t *>(fc.arena + c.dst_off), c.u.itx.rows);
 }
 
 // Inlined into the worker: as a separate function it saves and restores its callee-saved registers
@@ -184,7 +184,7 @@ EAV1_EXEC_LINK int exec_cmd(const FrameCtx &fc, const Eav1Cmd &c, CtaScratch &sm
             res_add<BD>(dst8, dstride, (const int16_t *)(fc.arena + c.dst_off), c.w, c.h, bdmax, tid, nthr);
         else
             itx_add<BD>(dst8, dstride, (const typename BD::coef *)(fc.payload + c.u.itx.cf_off), c.u.itx.eob,
-                        c.u.itx.tx, c.u.itx.txtp, bdmax, sm.itx, tid, nthr);
+                        c.u.itx.tx, c.u.itx.txtp, bdmax, sm.itx, tid, nthr, nullptr, c.u.itx.rows);
         PROF_MARK(5);
         break;
     default:

@@ -537,6 +537,11 @@ EAV1_DEV void itx_row_reg(const typename BD::coef *coeff, int sh, int y, int typ
                           int row_min, int row_max, int col_min, int col_max, int32_t *s, int P)
 {
     typedef typename BD::wide W;
+    if (y >= sh) {       // a row past the last one that was shipped: all zero in, all zero out (every 1-D transform is linear)
+#pragma unroll
+        for (int x = 0; x < N; x++) s[x * P + y] = 0;
+        return;
+    }
     int v[N];
 #pragma unroll
     for (int x = 0; x < N; x++) {
@@ -591,7 +596,7 @@ EAV1_DEV void itx_col_reg(const int32_t *s, int P, int x, int type, int col_min,
 
 template <typename BD>
 EAV1_DEVH void itx_add_reg(typename BD::pixel *dst, int dst_stride, const typename BD::coef *coeff, int w, int h,
-                           int shift, int rt, int ct, int bitdepth_max, int32_t *s, int tid, int nthr, int16_t *res)
+                           int shift, int rt, int ct, int bitdepth_max, int32_t *s, int tid, int nthr, int16_t *res, int rows)
 {
     const int is_rect2 = (w * 2 == h) || (h * 2 == w);
     const int P = h + 1;
@@ -605,10 +610,10 @@ EAV1_DEVH void itx_add_reg(typename BD::pixel *dst, int dst_stride, const typena
     PROF_BEGIN();
     for (int y = tid; y < h; y += nthr) {
         switch (w) {
-        case 4:  itx_row_reg<BD, 4>(coeff, h, y, rt, is_rect2, shift, row_min, row_max, col_min, col_max, s, P); break;
-        case 8:  itx_row_reg<BD, 8>(coeff, h, y, rt, is_rect2, shift, row_min, row_max, col_min, col_max, s, P); break;
-        case 16: itx_row_reg<BD, 16>(coeff, h, y, rt, is_rect2, shift, row_min, row_max, col_min, col_max, s, P); break;
-        default: itx_row_reg<BD, 32>(coeff, h, y, rt, is_rect2, shift, row_min, row_max, col_min, col_max, s, P); break;
+        case 4:  itx_row_reg<BD, 4>(coeff, rows, y, rt, is_rect2, shift, row_min, row_max, col_min, col_max, s, P); break;
+        case 8:  itx_row_reg<BD, 8>(coeff, rows, y, rt, is_rect2, shift, row_min, row_max, col_min, col_max, s, P); break;
+        case 16: itx_row_reg<BD, 16>(coeff, rows, y, rt, is_rect2, shift, row_min, row_max, col_min, col_max, s, P); break;
+        default: itx_row_reg<BD, 32>(coeff, rows, y, rt, is_rect2, shift, row_min, row_max, col_min, col_max, s, P); break;
         }
     }
     PROF_MARK(10);
@@ -629,16 +634,20 @@ EAV1_DEVH void itx_add_reg(typename BD::pixel *dst, int dst_stride, const typena
 
 // dst += inverse_transform(coef). `s` is the CTA's shared tile (>= 64*65 int32).
 template <typename BD>
+// `rows`: how many rows of the (column-major, min(w,32) x min(h,32)) coefficient block were shipped, which is also the
+// stride between its columns; the rows behind them are zero (itx_tmpl.c:87-105 last_nonzero_col). 0 = the whole block.
 EAV1_DEVH void itx_add(typename BD::pixel *dst, int dst_stride /*pixels*/, const typename BD::coef *coeff,
-                      int eob, int tx, int txtp, int bitdepth_max, int32_t *s, int tid, int nthr, int16_t *res = nullptr)
+                      int eob, int tx, int txtp, int bitdepth_max, int32_t *s, int tid, int nthr, int16_t *res = nullptr,
+                      int rows = 0)
 {
     typedef typename BD::wide W;
     const TxDim d = tx_dim(tx);
     const int w = d.w, h = d.h;
+    if (rows <= 0 || rows > imin(h, 32)) rows = imin(h, 32);
     if (txtp == 16) { // WHT_WHT, 4x4 only
         if (tid == 0) {
             for (int y = 0; y < 4; y++)
-                for (int x = 0; x < 4; x++) s[y * 4 + x] = coeff[y + x * 4] >> 2;
+                for (int x = 0; x < 4; x++) s[y * 4 + x] = coeff[y + x * 4] >> 2;     /* lossless blocks always ship all four rows */
             for (int y = 0; y < 4; y++) wht4(&s[y * 4], 1);
             for (int x = 0; x < 4; x++) wht4(&s[x], 4);
             for (int y = 0; y < 4; y++)
@@ -669,7 +678,7 @@ EAV1_DEVH void itx_add(typename BD::pixel *dst, int dst_stride /*pixels*/, const
 #define EAV1_ITX_REG 1
 #endif
     if (EAV1_ITX_REG && w <= 32 && h <= 32) {
-        itx_add_reg<BD>(dst, dst_stride, coeff, w, h, d.shift, rt, ct, bitdepth_max, s, tid, nthr, res);
+        itx_add_reg<BD>(dst, dst_stride, coeff, w, h, d.shift, rt, ct, bitdepth_max, s, tid, nthr, res, rows);
         return;
     }
     const int sh = imin(h, 32), sw = imin(w, 32);
@@ -685,7 +694,7 @@ EAV1_DEVH void itx_add(typename BD::pixel *dst, int dst_stride /*pixels*/, const
     // load (column-major source: index i = y + x*sh)
     for (int i = tid; i < sw * sh; i += nthr) {
         const int x = i / sh, y = i - x * sh;
-        int v = coeff[i];
+        int v = y < rows ? coeff[y + x * rows] : 0;
         if (is_rect2) v = (int)(((W)v * 181 + 128) >> 8);
         s[x * P + y] = v;
     }

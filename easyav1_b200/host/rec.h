@@ -119,6 +119,8 @@ Eav1Walk *eav1rec_enter(const Dav1dFrameContext *f, const Dav1dTaskContext *t);
 void eav1rec_unsupported(Eav1Walk *w);   /* the frame being walked cannot be recorded: it alone fails */
 Eav1Cmd *eav1rec_push(Eav1Walk *w);
 uint32_t eav1rec_payload(Eav1Walk *w, const void *src, size_t bytes, size_t align);
+/* room for `bytes` in the frame's payload; *dst receives where to write them (NULL when the payload is full) */
+uint32_t eav1rec_payload_reserve(Eav1Walk *w, size_t bytes, size_t align, void **dst);
 uint32_t eav1rec_region(Eav1Walk *w, int reg, size_t elem_bytes);
 uint32_t eav1rec_region_new(Eav1Walk *w, int reg, size_t bytes);
 Eav1LfRec *eav1rec_push_lf(Eav1Walk *w, const Eav1LfRec *v);

@@ -88,6 +88,16 @@ uint32_t eav1rec_payload(Eav1Walk *w, const void *src, size_t bytes, size_t alig
     return (uint32_t)off;
 }
 
+uint32_t eav1rec_payload_reserve(Eav1Walk *w, size_t bytes, size_t align, void **dst)
+{
+    Eav1Frame *fr = w->fr;
+    const size_t take = (bytes + align - 1) & ~(align - 1);
+    const size_t off = atomic_fetch_add(&fr->n_payload, take);
+    if (off + bytes > fr->cap_payload) { atomic_store(&fr->unsupported, 1); *dst = NULL; return 0; }
+    *dst = fr->payload + off;
+    return (uint32_t)off;
+}
+
 /* A producer starts a fresh region every time (single assignment): no command ever overwrites
  * scratch that an earlier command of the frame still has to read, so the engine is free to run
  * all motion compensation of a frame before anything else. */

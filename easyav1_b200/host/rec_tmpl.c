@@ -17,6 +17,7 @@
 #include "common/intops.h"
 #include "src/recon.h"
 #include "src/tables.h"
+#include "src/scan.h"
 #include "src/wedge.h"
 #include "src/ipred_prepare.h"
 
@@ -67,9 +68,37 @@ static void rec_itx(const int tx, const int txtp, pixel *dst, const ptrdiff_t st
     c->op = EAV1_OP_ITX;
     set_dst(r, c, dst, w, h, REG_II, sizeof(pixel));
     c->u.itx.tx = (uint8_t)tx; c->u.itx.txtp = (uint8_t)txtp; c->u.itx.eob = (int16_t)eob;
-    c->u.itx.cf_off = eav1rec_payload(r, cf, (size_t)n * sizeof(coef), 16);
-    /* contract of itxfm_add: the callee clears the coefficients (itx_tmpl.c:108) */
-    memset(cf, 0, (size_t)n * sizeof(coef));
+    /* Only the rows that can hold a non-zero coefficient travel: eob bounds them exactly as the
+     * reference's own transform derives last_nonzero_col (itx_tmpl.c:58-105): a dc-only block is one coefficient, a
+     * 1-D class block follows eob directly, everything else the scan-order table. The block is column-major, so the
+     * first `rows` entries of each of its min(w,32) columns are copied and, as the contract of itxfm_add demands
+     * (itx_tmpl.c:108: the callee clears the coefficients), cleared; the rest of the block is zero already. */
+    const int sw = imin(w, 32), sh = imin(h, 32);
+    int rows;
+    if (txtp == WHT_WHT) rows = sh;
+    else if (eob < (txtp == DCT_DCT)) rows = 1;
+    else if (txtp == H_DCT || txtp == H_ADST || txtp == H_FLIPADST) rows = imin(sh - 1, eob) + 1;
+    else if (txtp == V_DCT || txtp == V_ADST || txtp == V_FLIPADST) rows = (eob >> (td->lw + 2)) + 1;
+    else rows = dav1d_last_nonzero_col_from_eob[tx][eob] + 1;
+    (void)n;
+    if (txtp != WHT_WHT && eob < (txtp == DCT_DCT)) {
+        c->u.itx.rows = 1;
+        c->u.itx.cf_off = eav1rec_payload(r, cf, sizeof(coef), 4);
+        cf[0] = 0;
+    } else if (rows >= sh) {
+        c->u.itx.rows = (uint8_t)sh;
+        c->u.itx.cf_off = eav1rec_payload(r, cf, (size_t)sw * sh * sizeof(coef), 16);
+        memset(cf, 0, (size_t)sw * sh * sizeof(coef));
+    } else {
+        c->u.itx.rows = (uint8_t)rows;
+        coef *dstp;
+        c->u.itx.cf_off = eav1rec_payload_reserve(r, (size_t)sw * rows * sizeof(coef), 16, (void **)&dstp);
+        if (dstp)
+            for (int x = 0; x < sw; x++) {
+                memcpy(dstp + x * rows, cf + x * sh, (size_t)rows * sizeof(coef));
+                memset(cf + x * sh, 0, (size_t)rows * sizeof(coef));
+            }
+    }
 }
 
 #define ITX_FN(tx, tp) \
@@ -85,6 +114,7 @@ ITX_ALL(ITX_FN)
 void bitfn(eav1rec_itx_dsp_init)(Dav1dInvTxfmDSPContext *const c, int bpc)
 {
     (void)bpc;
+    dav1d_init_last_nonzero_col_from_eob_tables();
 #define ITX_SET(tx, tp) c->itxfm_add[tx][tp] = rec_itx_##tx##_##tp;
     ITX_ALL(ITX_SET)
 }

@@ -140,9 +140,12 @@ typedef struct Eav1Cmd {
             uint32_t idx_off;   /* payload byte offset: w*h/2 packed indices */
         } pal;
         struct {                /* ITX */
-            uint32_t cf_off;    /* payload byte offset of min(w,32)*min(h,32) coefs, column-major */
+            uint32_t cf_off;    /* payload byte offset of the coefficients: min(w,32) columns of `rows` entries each */
             int16_t  eob;
             uint8_t  tx, txtp;  /* enum RectTxfmSize, enum TxfmType (table index as used by itxfm_add[tx][txtp]) */
+            uint8_t  rows;      /* rows of the column-major min(w,32) x min(h,32) block that are shipped (= the stride
+                                   between columns); the rows behind them are zero: last_nonzero_col + 1 of
+                                   itx_tmpl.c:87-105, derived from eob. 0 = the whole block (stride min(h,32)) */
         } itx;
         uint8_t raw[44];
     } u;

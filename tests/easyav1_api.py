@@ -108,3 +108,49 @@ def play_file(L, path, bpc=8, layout=1, timeout_s=30.0):
         hp = C.c_void_p(h)
         L.easyav1_destroy(C.byref(hp))
     return out, finished
+
+
+class AudioFrame(C.Structure):   # easyav1_audio_frame, src/easyav1.h:309-319
+    _fields_ = [("channels", C.c_uint), ("samples", C.c_uint), ("timestamp", C.c_uint64), ("bytes", C.c_size_t),
+                ("pcm", C.c_void_p)]
+
+
+def decode_audio(L, webm, interlace=True, seek_after=None, seek_to_ms=0, enable_video=True):
+    """The loop of easyav1.h:35-53 with audio enabled. Returns ([(timestamp, samples, float32 bytes per frame)], number
+    of video frames). With seek_after=k, easyav1_seek_to_timestamp(seek_to_ms) is called once after k audio frames."""
+    keep = C.create_string_buffer(webm, len(webm))
+    L.easyav1_get_audio_frame.restype = C.POINTER(AudioFrame)
+    L.easyav1_get_audio_frame.argtypes = [C.c_void_p]
+    L.easyav1_seek_to_timestamp.argtypes = [C.c_void_p, C.c_uint64]
+    L.easyav1_get_audio_channels.argtypes = [C.c_void_p]
+    st = L.easyav1_default_settings()
+    st.enable_audio = 1
+    st.enable_video = 1 if enable_video else 0
+    st.interlace_audio = 1 if interlace else 0
+    st.log_level = 1
+    h = L.easyav1_init_from_memory(keep, len(webm), C.byref(st))
+    if not h:
+        raise RuntimeError("easyav1_init_from_memory failed")
+    out, n_video, sought = [], 0, False
+    try:
+        while L.easyav1_decode_next(h) == 1:
+            if L.easyav1_has_video_frame(h) == 1:
+                L.easyav1_get_video_frame(h)
+                n_video += 1
+            afr = L.easyav1_get_audio_frame(h)     # NULL when no new samples (src/easyav1.h:769)
+            if afr:
+                fr = afr.contents
+                if interlace:
+                    data = C.string_at(fr.pcm, fr.samples * fr.channels * 4)
+                else:
+                    ptrs = C.cast(fr.pcm, C.POINTER(C.c_void_p))
+                    data = b"".join(C.string_at(ptrs[c], fr.samples * 4) for c in range(fr.channels))
+                out.append((int(fr.timestamp), int(fr.samples), data))
+                if seek_after is not None and not sought and len(out) >= seek_after:
+                    sought = True
+                    if L.easyav1_seek_to_timestamp(h, seek_to_ms) != 1:
+                        raise RuntimeError("easyav1_seek_to_timestamp failed")
+    finally:
+        hp = C.c_void_p(h)
+        L.easyav1_destroy(C.byref(hp))
+    return out, n_video

@@ -46,6 +46,7 @@ int eav1cu_vorbis_open(Eav1Vorbis **out, int, int channels, int bs0, int bs1, co
 void eav1cu_vorbis_close(Eav1Vorbis *v) { delete v; }
 int eav1cu_vorbis_restart(Eav1Vorbis *v) { v->state_W = -1; return 0; }
 long long eav1cu_vorbis_launch_count(Eav1Vorbis *v) { return v->launches; }
+int eav1cu_vorbis_last_error(Eav1Vorbis *, char *msg, size_t cap) { if (msg && cap) msg[0] = 0; return 0; }
 
 int eav1cu_vorbis_imdct_ola(Eav1Vorbis *v, const uint8_t *flags, int n_blocks, const float *spectra,
                             float *pcm, size_t cap_samples, int interleave, size_t *n_samples)

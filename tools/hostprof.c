@@ -15,12 +15,16 @@
 #include <ucontext.h>
 
 #define MAXS 200000
-static void *samples[MAXS];
+static void *samples[MAXS], *callers[MAXS];
 static volatile int n_samples;
 static void on_prof(int sig, siginfo_t *si, void *uc_)
 {
     ucontext_t *uc = uc_;
-    if (n_samples < MAXS) samples[n_samples++] = (void *)uc->uc_mcontext.gregs[REG_RIP];
+    if (n_samples < MAXS) {
+        /* the word at the stack pointer: the return address when the sample sits in a frameless leaf (memcpy, memset) */
+        callers[n_samples] = *(void **)uc->uc_mcontext.gregs[REG_RSP];
+        samples[n_samples++] = (void *)uc->uc_mcontext.gregs[REG_RIP];
+    }
 }
 typedef struct { int w, h, layout, bpc, frame_type, show_frame, showable; int64_t offset; } Info;
 int main(int argc, char **argv)
@@ -53,10 +57,15 @@ int main(int argc, char **argv)
     fprintf(stderr, "%d frames in %.3f s = %.1f fps, %d samples\n", frames, dt, frames / dt, n_samples);
     for (int i = 0; i < n_samples; i++) {
         Dl_info di;
+        if (dladdr(samples[i], &di) && di.dli_fname && strstr(di.dli_fname, "libc.so") && dladdr(callers[i], &di) &&
+            di.dli_fname && !strstr(di.dli_fname, "libc.so")) {
+            const char *b = strrchr(di.dli_fname, '/'); b = b ? b + 1 : di.dli_fname;
+            printf("libc<-%s +0x%lx\n", b, (unsigned long)((char *)callers[i] - (char *)di.dli_fbase));
+            continue;
+        }
         if (dladdr(samples[i], &di) && di.dli_fname) {
             const char *b = strrchr(di.dli_fname, '/'); b = b ? b + 1 : di.dli_fname;
-            if (di.dli_sname) printf("%s %s\n", b, di.dli_sname);
-            else printf("%s +0x%lx\n", b, (unsigned long)((char *)samples[i] - (char *)di.dli_fbase));
+            printf("%s +0x%lx\n", b, (unsigned long)((char *)samples[i] - (char *)di.dli_fbase));
         } else printf("? %p\n", samples[i]);
     }
     return 0;

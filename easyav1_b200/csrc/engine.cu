@@ -518,7 +518,7 @@ struct Eav1cuCtx {
     int err = 0;
     std::string errmsg;
     std::mutex mu, err_mu;      // mu: picture pool; err_mu: err / errmsg (fail() is reached from any thread)
-    long long n_launches = 0, h2d_bytes = 0, d2h_bytes = 0, n_frames = 0;
+    long long n_launches = 0, h2d_bytes = 0, d2h_bytes = 0, n_frames = 0, staged_graph_kernels = 0;
     bool own_stream = true;
     cudaStream_t stream2 = nullptr;            // phase 1b (residuals) runs beside phase 1 (motion compensation)
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
@@ -1666,11 +1666,14 @@ int eav1cu_staged_graph_build(Eav1cuCtx *ctx)
     std::lock_guard<SubmitMutex> g(g_submit_mu);
     CK(cudaStreamBeginCapture(ctx->stream, cudaStreamCaptureModeThreadLocal));
     int r = 0;
+    const long long n0 = ctx->n_launches;
     if (ctx->d_done && cudaMemsetAsync(ctx->d_done, 0, ctx->done_cap * 4, ctx->stream) != cudaSuccess) r = EAV1CU_ERR_CUDA;
     for (FramePlan *pl : ctx->staged) {
         if (r) break;
         r = plan_launch(ctx, *pl);
     }
+    ctx->staged_graph_kernels = ctx->n_launches - n0;   // kernel nodes of the graph
+    ctx->n_launches = n0;                               // capturing launched nothing
     cudaGraph_t graph = nullptr;
     const cudaError_t e = cudaStreamEndCapture(ctx->stream, &graph);
     ctx->stage_timing = timing;
@@ -1692,7 +1695,7 @@ int eav1cu_staged_graph_launch(Eav1cuCtx *ctx, int passes)
     for (int p = 0; p < passes; p++) {
         std::lock_guard<SubmitMutex> g(g_submit_mu);
         CK(cudaGraphLaunch(ctx->staged_exec, ctx->stream));
-        ctx->n_launches += (long long)ctx->staged.size();     // counted per frame: one graph launch replaces these
+        ctx->n_launches += ctx->staged_graph_kernels;         // the kernels the graph runs
     }
     return 0;
 }

@@ -4,12 +4,15 @@
 tag=${1:-r1}
 out=gpurun_out
 set -x
-python bench.py --steps 2 --warmup 3 > $out/${tag}_bench.json 2> $out/${tag}_bench.err || exit 1
+python bench.py --steps 5 --warmup 3 > $out/${tag}_bench.json 2> $out/${tag}_bench.err || exit 1
 EAV1_BENCH_PROFILE=1 ncu --profile-from-start off --metrics gpu__time_duration.sum --clock-control none --csv \
-    --log-file $out/${tag}_launches.csv python bench.py --steps 2 --warmup 3 > $out/${tag}_ncu_launches.log 2>&1
-EAV1_BENCH_PROFILE=1 ncu --profile-from-start off --set full --clock-control none --import-source on \
-    -k regex:"recon_frame_kernel|resid_kernel|mc_kernel|cdef_kernel|lr_kernel|deblock_kernel" --launch-count 18 \
-    -o $out/${tag}_full python bench.py --steps 2 --warmup 3 > $out/${tag}_ncu_full.log 2>&1
+    --log-file $out/${tag}_launches.csv python bench.py --only none --steps 2 --warmup 3 > $out/${tag}_ncu_launches.log 2>&1
+# --set full over the first 40 frames of the timed step (key frame, an ARF, ~38 inter frames: >= 10 launches of every
+# kernel, spread over the clip instead of its first three frames). Direct launches (EAV1_BENCH_NO_GRAPH) so that the
+# capture can stop after a launch count; the kernels and their arguments are those of the graph.
+EAV1_BENCH_PROFILE=1 EAV1_BENCH_NO_GRAPH=1 ncu --profile-from-start off --set full --clock-control none --import-source on \
+    -k regex:"recon_frame_kernel|resid_kernel|mc_kernel|cdef_kernel|lr_kernel|deblock_kernel" --launch-count 210 \
+    -o $out/${tag}_full python bench.py --only none --steps 2 --warmup 3 > $out/${tag}_ncu_full.log 2>&1
 python tools/vorbis_bench.py > $out/${tag}_vorbis.json 2> $out/${tag}_vorbis.err
 ncu --set full --clock-control none --import-source on -k regex:vorbis_kernel --launch-skip 6 --launch-count 1 \
     -o $out/${tag}_vorbis_full python tools/vorbis_bench.py > $out/${tag}_ncu_vorbis.log 2>&1

@@ -81,12 +81,15 @@ def ncu_traffic(kernel_name):
             continue
         for k, v in d.items():
             if kernel_name in k:
-                rd = [x for n, x in v.items() if n.startswith("dram__bytes_read.sum")]
-                wr = [x for n, x in v.items() if n.startswith("dram__bytes_write.sum")]
-                unit = [n for n in v if n.startswith("dram__bytes_read.sum")]
-                if rd and wr and unit:
-                    scale = 1e6 if "Mbyte" in unit[0] else 1e3 if "Kbyte" in unit[0] else 1e9 if "Gbyte" in unit[0] else 1.0
-                    best = {"bytes_per_launch": int((rd[0] + wr[0]) * scale), "source": os.path.basename(path)}
+                def in_bytes(prefix):     # ncu picks a unit per metric ("[Mbyte]", "[Kbyte]", ...)
+                    for n, x in v.items():
+                        if n.startswith(prefix):
+                            return x * (1e6 if "Mbyte" in n else 1e3 if "Kbyte" in n else 1e9 if "Gbyte" in n else 1.0)
+                    return None
+                rd, wr = in_bytes("dram__bytes_read.sum"), in_bytes("dram__bytes_write.sum")
+                if rd is not None and wr is not None:
+                    best = {"bytes_per_launch": int(rd + wr), "source": os.path.basename(path),
+                            "launches_captured": v.get("launches_captured")}
     return best
 
 

@@ -824,7 +824,8 @@ def test_cdef(so, bpc, layout):
             for pl in range(len(planes)):
                 want = pad[pl][4:-4, 8:-8]
                 bad = np.argwhere(got[pl] != want)
-                assert not len(bad), "cdef trial %d plane %d: %d samples differ, first at (y, x) = %s" % (trial, pl, len(bad), bad[0])
+                assert not len(bad), "cdef trial %d plane %d: %d samples differ, first at (y, x) = %s: got %s want %s" % (
+                    trial, pl, len(bad), bad[0], np.asarray(got[pl])[bad[:8, 0], bad[:8, 1]].tolist(), np.asarray(want)[bad[:8, 0], bad[:8, 1]].tolist())
     finally:
         rig.close()
 

@@ -150,7 +150,7 @@ EAV1_DEV void lf_unit(const PfParams &pp, const Eav1LfRec &r, int u, int line0 =
 // per thread group.
 
 struct CdefSmem {
-    alignas(4) int16_t tile[3][12 * 12];  // padded inputs, INT16_MIN marks "not available" (read as 32-bit pairs too)
+    alignas(4) int16_t tile[3][12 * 12];  // padded inputs, INT16_MIN marks "not available"
     int32_t part[8][16];       // per direction: sums of the samples on each of its (up to 15) lines
     int32_t cost[8];
     int32_t dir, var;
@@ -265,121 +265,6 @@ EAV1_DEV void cdef_filter(const Eav1Tables *tab, const Plane &out, int x0, int y
         int v = px + ((sum - (sum < 0) + 8) >> 4);
         if (pri && sec) v = iclip(v, mn, mx);
         *px_at<pixel>(second ? *out2 : out, x0 + x, y0 + y) = (pixel)v;
-    }
-}
-
-// ---- packed path: two horizontally adjacent samples per lane as signed 16-bit halves of one register.
-// sm_100a has native 16x2 integer add / min / max / add-then-max (VIADD.16x2, VIMNMX.S16x2, VIADDMNMX.S16x2), so the
-// constrain() of two samples costs what one costs in scalar code. Used for blocks whose whole 2-sample border
-// exists (no INT16_MIN markers in the tile: a marker minus a sample would wrap in 16 bits); every value below
-// stays inside int16: samples <= 4095, differences <= 4095, |sum| <= 12 * 240 + 12 * 64.
-#if defined(__CUDA_ARCH__)
-EAV1_DEV uint32_t pk_add(uint32_t a, uint32_t b) { return __vadd2(a, b); }
-EAV1_DEV uint32_t pk_min(uint32_t a, uint32_t b) { return __vmins2(a, b); }
-EAV1_DEV uint32_t pk_max(uint32_t a, uint32_t b) { return __vmaxs2(a, b); }
-EAV1_DEV uint32_t pk_addmax(uint32_t a, uint32_t b, uint32_t c) { return __viaddmax_s16x2(a, b, c); }   // max(a + b, c)
-// 0xffff where a half is negative: PRMT with the sign-replicate bit of the selector nibbles (prmt.b32, default mode).
-// __byte_perm() cannot express it: it keeps only three bits of every nibble.
-EAV1_DEV uint32_t pk_signmask(uint32_t a) { uint32_t d; asm("prmt.b32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(0u), "r"(0xbb99u)); return d; }
-EAV1_DEV uint32_t pk_straddle(uint32_t lo, uint32_t hi) { return __byte_perm(lo, hi, 0x5432); }       // (lo.hi, hi.lo)
-#else
-EAV1_DEV uint32_t pk_op(uint32_t a, uint32_t b, int op) {
-    int16_t r[2];
-    for (int k = 0; k < 2; k++) {
-        const int x = (int16_t)(a >> (16 * k)), y = (int16_t)(b >> (16 * k));
-        r[k] = (int16_t)(op == 0 ? x + y : op == 1 ? (x < y ? x : y) : (x > y ? x : y));
-    }
-    return (uint16_t)r[0] | ((uint32_t)(uint16_t)r[1] << 16);
-}
-EAV1_DEV uint32_t pk_add(uint32_t a, uint32_t b) { return pk_op(a, b, 0); }
-EAV1_DEV uint32_t pk_min(uint32_t a, uint32_t b) { return pk_op(a, b, 1); }
-EAV1_DEV uint32_t pk_max(uint32_t a, uint32_t b) { return pk_op(a, b, 2); }
-EAV1_DEV uint32_t pk_addmax(uint32_t a, uint32_t b, uint32_t c) { return pk_max(pk_add(a, b), c); }
-EAV1_DEV uint32_t pk_signmask(uint32_t a) { return ((a & 0x8000u) ? 0xffffu : 0u) | ((a & 0x80000000u) ? 0xffff0000u : 0u); }
-EAV1_DEV uint32_t pk_straddle(uint32_t lo, uint32_t hi) { return (lo >> 16) | (hi << 16); }
-#endif
-EAV1_DEV uint32_t pk_neg(uint32_t a) { return pk_add(~a, 0x00010001u); }
-
-// constrain() of cdef_tmpl.c:37-42 on two samples: sign(d) * min(|d|, max(0, strength - (|d| >> shift))) written as
-// clamp(d, -t, t). nx = -centre, s1 = strength + 1 (both packed), shmask = the bits a half keeps after the shift.
-EAV1_DEV uint32_t cdef_constrain2(uint32_t p, uint32_t nx, uint32_t s1, int shift, uint32_t shmask)
-{
-    const uint32_t d = pk_add(p, nx);
-    const uint32_t ad = pk_max(d, pk_neg(d));
-    const uint32_t t = pk_addmax(s1, ~((ad >> shift) & shmask), 0u);   // ~v = -v - 1
-    return pk_max(pk_min(d, t), pk_neg(t));
-}
-
-// the pair at tile index i (the tile is 4-byte aligned, i may be odd)
-EAV1_DEV uint32_t cdef_pair(const int16_t *tile, int i)
-{
-    const uint32_t *w = reinterpret_cast<const uint32_t *>(tile) + (i >> 1);
-    return (i & 1) ? pk_straddle(w[0], w[1]) : w[0];
-}
-
-EAV1_DEV uint32_t pk_times(uint32_t a, int k)   // k in 1..4
-{
-    const uint32_t a2 = pk_add(a, a);
-    return k == 1 ? a : k == 2 ? a2 : k == 3 ? pk_add(a2, a) : pk_add(a2, a2);
-}
-
-template <typename pixel>
-EAV1_DEV void cdef_filter_packed(const Eav1Tables *tab, const Plane &out, int x0, int y0, int w, int h, const int16_t *tile,
-                                 int pri, int sec, int dir, int damping, int bitdepth_max, int tid, int nthr,
-                                 const Plane *out2 = nullptr, const int16_t *tile2 = nullptr)
-{
-    const int bd8 = (32 - clz32((unsigned)bitdepth_max)) - 8;
-    const int pri_tap = 4 - ((pri >> bd8) & 1);
-    const int pri_shift = pri ? imax(0, damping - ulog2(pri)) : 0;
-    const int sec_shift = sec ? damping - ulog2(sec) : 0;
-    const uint32_t pri1 = (uint32_t)(pri + 1) * 0x10001u, sec1 = (uint32_t)(sec + 1) * 0x10001u;
-    const uint32_t pmask = (0xffffu >> pri_shift) * 0x10001u, smask = (0xffffu >> sec_shift) * 0x10001u;
-    int op[2], o2[2], o3[2];
-    for (int k = 0; k < 2; k++) {
-        op[k] = tab->cdef_directions[dir + 2][k];
-        o2[k] = tab->cdef_directions[dir + 4][k];
-        o3[k] = tab->cdef_directions[dir][k];
-    }
-    const int lpw = ulog2((unsigned)w) - 1, pairs = (w * h) >> 1;   // pairs per row = w / 2
-    for (int ii = tid; ii < (out2 ? 2 * pairs : pairs); ii += nthr) {
-        const bool second = ii >= pairs;
-        const int i = second ? ii - pairs : ii;
-        const int y = i >> lpw, x = (i & ((w >> 1) - 1)) << 1;
-        const int16_t *t = second ? tile2 : tile;
-        const int c = (y + 2) * 12 + x + 2;
-        const uint32_t px = cdef_pair(t, c), nx = pk_neg(px);
-        const bool both = pri && sec;       // only then the result is clamped to the range of the taps
-        uint32_t mx = px, mn = px, acc_p[2] = { 0, 0 }, acc_s[2] = { 0, 0 };
-#pragma unroll
-        for (int k = 0; k < 2; k++) {
-            if (pri) {
-                const uint32_t p0 = cdef_pair(t, c + op[k]), p1 = cdef_pair(t, c - op[k]);
-                acc_p[k] = pk_add(cdef_constrain2(p0, nx, pri1, pri_shift, pmask), cdef_constrain2(p1, nx, pri1, pri_shift, pmask));
-                if (both) { mx = pk_max(pk_max(p0, p1), mx); mn = pk_min(pk_min(p0, p1), mn); }
-            }
-            if (sec) {
-                const uint32_t s0 = cdef_pair(t, c + o2[k]), s1 = cdef_pair(t, c - o2[k]);
-                const uint32_t s2 = cdef_pair(t, c + o3[k]), s3 = cdef_pair(t, c - o3[k]);
-                acc_s[k] = pk_add(pk_add(cdef_constrain2(s0, nx, sec1, sec_shift, smask), cdef_constrain2(s1, nx, sec1, sec_shift, smask)),
-                                  pk_add(cdef_constrain2(s2, nx, sec1, sec_shift, smask), cdef_constrain2(s3, nx, sec1, sec_shift, smask)));
-                if (both) {
-                    mx = pk_max(pk_max(pk_max(s0, s1), pk_max(s2, s3)), mx);
-                    mn = pk_min(pk_min(pk_min(s0, s1), pk_min(s2, s3)), mn);
-                }
-            }
-        }
-        // taps: primary (pri_tap, (pri_tap & 3) | 2) = (4, 2) or (3, 3); secondary (2, 1)
-        uint32_t sum = pk_add(pk_add(pk_times(acc_p[0], pri_tap), pk_times(acc_p[1], (pri_tap & 3) | 2)),
-                              pk_add(pk_add(acc_s[0], acc_s[0]), acc_s[1]));
-        // (sum - (sum < 0) + 8) >> 4 per half: the logical shift keeps 12 bits, the xor/add pair sign-extends them
-        sum = pk_add(pk_add(sum, pk_signmask(sum)), 0x00080008u);
-        sum = pk_add(((sum >> 4) & 0x0fff0fffu) ^ 0x08000800u, 0xf800f800u);
-        uint32_t v = pk_add(px, sum);
-        if (both) v = pk_min(pk_max(v, mn), mx);
-        const Plane &o = second ? *out2 : out;
-        uint8_t *d = o.p + (ptrdiff_t)(y0 + y) * o.stride + (ptrdiff_t)(x0 + x) * (int)sizeof(pixel);
-        if (sizeof(pixel) == 1) *reinterpret_cast<uint16_t *>(d) = (uint16_t)((v & 0xffu) | ((v >> 8) & 0xff00u));
-        else *reinterpret_cast<uint32_t *>(d) = v;
     }
 }
 
@@ -525,20 +410,14 @@ EAV1_DEV void cdef_block(const PfParams &pp, int bx, int by, bool valid, CdefSme
             do_y = pri || y_sec;
         } else do_y = y_sec != 0;
     }
-    const bool packed = edges == 15;    // the whole border exists: no "not available" markers in the tiles
-    if (do_y && packed) cdef_filter_packed<pixel>(pp.tab, pp.b[0], lx, ly, 8, 8, sm.tile[0], pri, y_sec, ydir, damping, pp.bitdepth_max, tid, nthr);
-    else if (do_y) cdef_filter<pixel>(pp.tab, pp.b[0], lx, ly, 8, 8, sm.tile[0], pri, y_sec, ydir, damping, pp.bitdepth_max, tid, nthr);
+    if (do_y) cdef_filter<pixel>(pp.tab, pp.b[0], lx, ly, 8, 8, sm.tile[0], pri, y_sec, ydir, damping, pp.bitdepth_max, tid, nthr);
     else cdef_copy<pixel>(pp.a[0], pp.b[0], lx, ly, 8, 8, tid, nthr);
     if (has_chroma) {
         if (active && uv_lvl) {
             const uint8_t uvd422[8] = { 7, 0, 2, 4, 5, 6, 6, 6 };
             const int uvdir = uv_pri ? (pp.layout == 2 ? uvd422[dir] : dir) : 0;
-            if (packed)
-                cdef_filter_packed<pixel>(pp.tab, pp.b[1], cx, cy, cw, chh, sm.tile[1], uv_pri, uv_sec, uvdir, damping - 1, pp.bitdepth_max, tid, nthr,
-                                          &pp.b[2], sm.tile[2]);
-            else
-                cdef_filter<pixel>(pp.tab, pp.b[1], cx, cy, cw, chh, sm.tile[1], uv_pri, uv_sec, uvdir, damping - 1, pp.bitdepth_max, tid, nthr,
-                                   &pp.b[2], sm.tile[2]);
+            cdef_filter<pixel>(pp.tab, pp.b[1], cx, cy, cw, chh, sm.tile[1], uv_pri, uv_sec, uvdir, damping - 1, pp.bitdepth_max, tid, nthr,
+                               &pp.b[2], sm.tile[2]);
         } else {
             cdef_copy<pixel>(pp.a[1], pp.b[1], cx, cy, cw, chh, tid, nthr);
             cdef_copy<pixel>(pp.a[2], pp.b[2], cx, cy, cw, chh, tid, nthr);

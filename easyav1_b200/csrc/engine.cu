@@ -17,6 +17,7 @@
 #include "exec.cuh"
 #include "postfilter.cuh"
 #include "filmgrain.cuh"
+#include "convert.cuh"
 #include "sched.h"
 #include "coverage.h"
 
@@ -349,6 +350,15 @@ resid_kernel(FrameCtx fc, const Eav1Cmd *__restrict__ cmds, const uint32_t *__re
     }
 }
 
+// Output conversion: one thread per luma sample, rows of 128 samples per CTA row.
+template <typename pixel>
+__global__ void __launch_bounds__(128)
+convert_kernel(ConvParams P)
+{
+    const int x = blockIdx.x * 128 + threadIdx.x, y = blockIdx.y;
+    if (x < P.w) convert_sample<pixel>(P, x, y);
+}
+
 // debugging aid (EAV1_DEBUG_CHECK=2): stream-ordered checksum of an uploaded buffer
 __global__ void checksum_kernel(const uint32_t *p, size_t n_words, unsigned long long *out)
 {
@@ -519,6 +529,7 @@ struct Eav1cuCtx {
     std::string errmsg;
     std::mutex mu, err_mu;      // mu: picture pool; err_mu: err / errmsg (fail() is reached from any thread)
     long long n_launches = 0, h2d_bytes = 0, d2h_bytes = 0, n_frames = 0, staged_graph_kernels = 0;
+    DevBuf conv;                        // output of eav1cu_pic_convert before it is copied to the host
     bool own_stream = true;
     cudaStream_t stream2 = nullptr;            // phase 1b (residuals) runs beside phase 1 (motion compensation)
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
@@ -685,6 +696,7 @@ static void ctx_free(Eav1cuCtx *ctx)
     }
     for (cudaEvent_t e : ctx->fence_ev) if (e) cudaEventDestroy(e);
     if (ctx->d_done) cudaFree(ctx->d_done);
+    if (ctx->conv.d) cudaFree(ctx->conv.d);
     if (ctx->d_ctrl) cudaFree(ctx->d_ctrl);
     if (ctx->d_fg) cudaFree(ctx->d_fg);
     if (ctx->d_tab) cudaFree(ctx->d_tab);
@@ -849,6 +861,41 @@ static int pic_copy(Eav1cuCtx *ctx, int id, void *const data[3], const ptrdiff_t
     }
     g.unlock();
     if (wait) CK(cudaStreamSynchronize(ctx->stream));
+    return ctx->err;
+}
+
+int eav1cu_pic_convert(Eav1cuCtx *ctx, int id, const Eav1Convert *cv, void *dst, size_t dst_stride, size_t dst_bytes)
+{
+    if (!ctx || !cv || !dst || id < 0 || id >= (int)ctx->pics.size() || !ctx->pics[id].base) return EAV1CU_ERR_INVAL;
+    if (ctx->err) return ctx->err;
+    const Picture &p = ctx->pics[id];
+    const size_t need = conv_needed(cv->format, p.layout, p.bpc, p.w, p.h, dst_stride);
+    if (!need || need > dst_bytes) return EAV1CU_ERR_INVAL;
+    CK(cudaSetDevice(ctx->device));
+    if (need > ctx->conv.cap) {
+        if (ctx->conv.d) cudaFree(ctx->conv.d);
+        ctx->conv.d = nullptr; ctx->conv.cap = 0;
+        CK(cudaMalloc((void **)&ctx->conv.d, need));
+        ctx->conv.cap = need;
+    }
+    ConvParams P;
+    memset(&P, 0, sizeof(P));
+    for (int i = 0; i < 3; i++) P.src[i] = p.pl[i];
+    P.w = p.w; P.h = p.h; P.mono = p.layout == 0; P.ss_hor = p.layout != 3; P.ss_ver = p.layout == 1;
+    P.bpc = p.bpc; P.format = cv->format;
+    conv_coefficients(P, cv->matrix, cv->full_range);
+    P.dst = ctx->conv.d; P.dst_stride = (long long)dst_stride;
+    {
+        std::lock_guard<SubmitMutex> g(g_submit_mu);
+        const dim3 grid((unsigned)((p.w + 127) / 128), (unsigned)p.h);
+        if (p.bpc > 8) convert_kernel<uint16_t><<<grid, 128, 0, ctx->stream>>>(P);
+        else convert_kernel<uint8_t><<<grid, 128, 0, ctx->stream>>>(P);
+        CK(cudaGetLastError());
+        ctx->n_launches++; g_total[0]++;
+        CK(cudaMemcpyAsync(dst, ctx->conv.d, need, cudaMemcpyDeviceToHost, ctx->stream));
+        ctx->d2h_bytes += (long long)need; g_total[2] += (long long)need;
+    }
+    CK(cudaStreamSynchronize(ctx->stream));
     return ctx->err;
 }
 

@@ -461,9 +461,9 @@ EAV1_DEV void resize_sample(const ResizeParams &rp, const int8_t (*filt)[8], int
 // at the frame top/bottom and left/right the edge sample is replicated.
 
 #define LR_TW 32
-struct LrSmem {
+struct alignas(16) LrSmem {
     uint16_t in[(64 + 6) * (LR_TW + 6)];
-    union {
+    union alignas(16) {
         uint16_t hor[(64 + 6) * LR_TW];                 // Wiener: horizontally filtered rows
         struct {
             int32_t a3[(64 + 2) * (LR_TW + 2)]; uint16_t b3[(64 + 2) * (LR_TW + 2)];
@@ -479,6 +479,30 @@ EAV1_DEV void lr_load(const PfParams &pp, const Eav1LrRec &r, int x0, int tw, ui
     const int ss_ver = r.plane ? pp.ss_ver : 0;
     const int ph = (pp.h + ss_ver) >> ss_ver;
     const int W = tw + 6, H = r.h + 6;
+    // Full-width slices whose 3-sample halo exists on both sides (everything but the first / last slice of a picture
+    // row) are read as aligned 32-bit words: columns x0-4 .. x0+tw+3, of which the tile keeps x0-3 .. x0+tw+2.
+    if (tw == LR_TW && (x0 > 0 || (r.edges & 1)) && (x0 + tw + 4 <= r.w || (r.edges & 2))) {
+        constexpr int SPW = 4 / (int)sizeof(pixel), NW = (LR_TW + 8) / SPW;
+        for (int i = tid; i < NW * H; i += nthr) {
+            const int ty = i / NW, wi = i - ty * NW;
+            const int ry = ty - 3;
+            const Plane *src = &B;
+            int sy;
+            if (ry < 0) {
+                if (r.edges & 4) { src = &A; sy = r.y + imax(ry, -2); } else sy = r.y;
+            } else if (ry >= r.h) {
+                if (r.edges & 8) { src = &A; sy = imin(r.y + r.h + imin(ry - r.h, 1), ph - 1); } else sy = r.y + r.h - 1;
+            } else sy = r.y + ry;
+            const uint32_t v = *reinterpret_cast<const uint32_t *>(src->p + (ptrdiff_t)sy * src->stride +
+                                                                    (ptrdiff_t)(r.x + x0 - 4 + SPW * wi) * (int)sizeof(pixel));
+#pragma unroll
+            for (int b = 0; b < SPW; b++) {
+                const int tx = SPW * wi + b - 1;
+                if (tx >= 0 && tx < W) in[ty * W + tx] = (uint16_t)(sizeof(pixel) == 1 ? (v >> (8 * b)) & 0xff : (v >> (16 * b)) & 0xffff);
+            }
+        }
+        return;
+    }
     const FastDiv fdW(W);
     for (int i = tid; i < W * H; i += nthr) {
         const int ty = fdW.div(i), tx = i - ty * W;
@@ -497,6 +521,15 @@ EAV1_DEV void lr_load(const PfParams &pp, const Eav1LrRec &r, int x0, int tw, ui
         } else v = *px_at<pixel>(B, ax, r.y + ry);
         in[i] = (uint16_t)v;
     }
+}
+
+// four finished samples of one row, x a multiple of 4: one 32-bit (8-bit samples) or 64-bit store
+template <typename pixel>
+EAV1_DEV void lr_store4(const Plane &P, int x, int y, const int v[4])
+{
+    uint8_t *d = P.p + (ptrdiff_t)y * P.stride + (ptrdiff_t)x * (int)sizeof(pixel);
+    if (sizeof(pixel) == 1) *reinterpret_cast<uint32_t *>(d) = (uint32_t)v[0] | ((uint32_t)v[1] << 8) | ((uint32_t)v[2] << 16) | ((uint32_t)v[3] << 24);
+    else { uint2 q; q.x = (uint32_t)v[0] | ((uint32_t)v[1] << 16); q.y = (uint32_t)v[2] | ((uint32_t)v[3] << 16); *reinterpret_cast<uint2 *>(d) = q; }
 }
 
 template <typename pixel>
@@ -519,6 +552,25 @@ EAV1_DEV void lr_wiener_tile(const PfParams &pp, const Eav1LrRec &r, int x0, int
     }
     CTA_SYNC();
     const Plane &P = pp.p[r.plane];
+    if (tw == LR_TW) {
+        for (int i = tid; i < r.h * (LR_TW / 4); i += nthr) {
+            const int y = i / (LR_TW / 4), x = (i - y * (LR_TW / 4)) * 4;
+            int sum[4], v[4];
+#pragma unroll
+            for (int j = 0; j < 4; j++) sum[j] = -(1 << (bitdepth + (rb_v - 1)));
+            for (int k = 0; k < 7; k++) {
+                const int f = r.p.filter[1][k];
+                const uint2 h4 = *reinterpret_cast<const uint2 *>(&sm.hor[(y + k) * LR_TW + x]);
+                sum[0] += (int)(h4.x & 0xffff) * f; sum[1] += (int)(h4.x >> 16) * f;
+                sum[2] += (int)(h4.y & 0xffff) * f; sum[3] += (int)(h4.y >> 16) * f;
+            }
+#pragma unroll
+            for (int j = 0; j < 4; j++) v[j] = iclip((sum[j] + (1 << (rb_v - 1))) >> rb_v, 0, pp.bitdepth_max);
+            lr_store4<pixel>(P, r.x + x0 + x, r.y + y, v);
+        }
+        CTA_SYNC();
+        return;
+    }
     for (int i = tid; i < r.h * tw; i += nthr) {
         const int y = fdt.div(i), x = i - y * tw;
         int sum = -(1 << (bitdepth + (rb_v - 1)));
@@ -571,8 +623,8 @@ EAV1_DEV void lr_sgr_tile(const PfParams &pp, const Eav1LrRec &r, int x0, int tw
         }
     CTA_SYNC();
     const Plane &P = pp.p[r.plane];
-    for (int i = tid; i < h * tw; i += nthr) {
-        const int y = fdt.div(i), x = i - y * tw;
+    // one finished sample of the stripe slice (weighted sum of the box-filter outputs around it)
+    auto sample = [&](int x, int y) -> int {
         const int src = sm.in[(y + 3) * W + x + 3];
         int t3 = 0, t5 = 0;
         if (do3) {
@@ -601,7 +653,21 @@ EAV1_DEV void lr_sgr_tile(const PfParams &pp, const Eav1LrRec &r, int x0, int tw
         if (r.kind == EAV1_LR_SGR_MIX) v = r.p.sgr.w0 * t5 + r.p.sgr.w1 * t3;
         else if (r.kind == EAV1_LR_SGR_5X5) v = r.p.sgr.w0 * t5;
         else v = r.p.sgr.w1 * t3;
-        *px_at<pixel>(P, r.x + x0 + x, r.y + y) = (pixel)iclip(src + ((v + (1 << 10)) >> 11), 0, pp.bitdepth_max);
+        return iclip(src + ((v + (1 << 10)) >> 11), 0, pp.bitdepth_max);
+    };
+    if (tw == LR_TW) {
+        for (int i = tid; i < h * (LR_TW / 4); i += nthr) {
+            const int y = i / (LR_TW / 4), x = (i - y * (LR_TW / 4)) * 4;
+            int v4[4];
+#pragma unroll
+            for (int j = 0; j < 4; j++) v4[j] = sample(x + j, y);
+            lr_store4<pixel>(P, r.x + x0 + x, r.y + y, v4);
+        }
+    } else {
+        for (int i = tid; i < h * tw; i += nthr) {
+            const int y = fdt.div(i), x = i - y * tw;
+            *px_at<pixel>(P, r.x + x0 + x, r.y + y) = (pixel)sample(x, y);
+        }
     }
     CTA_SYNC();
 }

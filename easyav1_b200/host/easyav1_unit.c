@@ -33,3 +33,19 @@ int eav1ref_vorbis_halfrate(vorbis_dsp_state *v)
 {
     return ((codec_setup_info *)v->vi->codec_setup)->halfrate_flag;
 }
+
+/* ---- an additional getter beside easyav1_get_video_frame (src/easyav1.h:738), which stays as it is ----
+ * The frame easyav1_get_video_frame last returned (easyav1->video.picture, src/easyav1.c:3520-3568), converted on the
+ * GPU to format 1 = NV12, 2 = P010, 3 = RGBA8 (include/easyav1_cuda.h) with the stream's own matrix / range, written
+ * to dst. Returns EASYAV1_STATUS_OK or EASYAV1_STATUS_ERROR (no frame yet, format not possible for this stream,
+ * dst too small). */
+extern int eav1rec_picture_convert(const Dav1dPicture *p, int format, int matrix, int full_range, void *dst,
+                                   size_t dst_stride, size_t dst_bytes);
+
+easyav1_status easyav1_b200_get_video_frame_converted(easyav1_t *easyav1, int format, void *dst, size_t dst_stride, size_t dst_bytes)
+{
+    if (!easyav1 || !dst || easyav1->video.active != EASYAV1_TRUE || !easyav1->video.picture.data[0])
+        return EASYAV1_STATUS_ERROR;
+    return eav1rec_picture_convert(&easyav1->video.picture, format, -1, -1, dst, dst_stride, dst_bytes) == 0 ?
+           EASYAV1_STATUS_OK : EASYAV1_STATUS_ERROR;
+}

@@ -136,4 +136,6 @@ int eav1rec_locate_sr(const Eav1Walk *w, const void *p, int *x, int *y);
 /* locate a pixel pointer inside a reference (0..6) or the current picture (7) */
 int eav1rec_locate_ref(const Eav1Walk *w, const void *p, int *plane, int *x, int *y);
 
+int eav1rec_picture_convert(const Dav1dPicture *p, int format, int matrix, int full_range, void *dst, size_t dst_stride, size_t dst_bytes);
+
 #endif

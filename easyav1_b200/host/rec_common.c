@@ -1075,6 +1075,27 @@ int eav1rec_picture_wait(Dav1dPicture *p)
     return pd_wait(pd->rec, pd);
 }
 
+/* SURVEY.md N4 — an ADDITIONAL getter beside dav1d_get_picture: the picture `p` (as handed out by dav1d_get_picture,
+ * still referenced by the caller) converted on the device to NV12 / P010 / RGBA8 (include/easyav1_cuda.h,
+ * eav1cu_pic_convert) and copied to dst. matrix < 0 / full_range < 0 take the values of the picture's sequence header
+ * (what src/easyav1.c:3287-3507 reports to the application). Returns 0 or a negative DAV1D_ERR. */
+int eav1rec_picture_convert(const Dav1dPicture *p, int format, int matrix, int full_range, void *dst, size_t dst_stride, size_t dst_bytes)
+{
+    Eav1PicData *pd = p && p->data[0] ? p->allocator_data : NULL;
+    if (!pd || !dst) return DAV1D_ERR(EINVAL);
+    Eav1Rec *r = pd->rec;
+    const int w = pd_wait(r, pd);               /* its frame has been reconstructed (and it did not fail) */
+    if (w) return w;
+    Eav1Convert cv;
+    cv.format = format;
+    cv.matrix = matrix >= 0 ? matrix : (p->seq_hdr ? (int)p->seq_hdr->mtrx : 2);
+    cv.full_range = full_range >= 0 ? full_range : (p->seq_hdr ? p->seq_hdr->color_range : 0);
+    pthread_mutex_lock(&r->cu_mu);
+    const int res = eav1cu_pic_convert(r->cu, pd->dev_id, &cv, dst, dst_stride, dst_bytes);
+    pthread_mutex_unlock(&r->cu_mu);
+    return res == 0 ? 0 : res == EAV1CU_ERR_INVAL ? DAV1D_ERR(EINVAL) : DAV1D_ERR(EIO);
+}
+
 /* Drop-in for dav1d_get_picture (ext/dav1d/src/lib.c:458): the picture dav1d hands out was
  * reconstructed asynchronously; wait for its planes to arrive in (pinned) host memory. The DSP
  * surface we replace is void, so engine failures are latched and surface here as DAV1D_ERR(EIO);

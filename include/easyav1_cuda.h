@@ -226,6 +226,33 @@ int  eav1cu_pic_release(Eav1cuCtx *ctx, int id);
 int  eav1cu_pic_upload(Eav1cuCtx *ctx, int id, const void *const data[3], const ptrdiff_t stride[2]);
 int  eav1cu_pic_download(Eav1cuCtx *ctx, int id, void *const data[3], const ptrdiff_t stride[2]);
 
+/* ---- output conversion -------------------------------------------------------
+ * An ADDITIONAL getter: the planar picture easyav1_get_video_frame / dav1d_get_picture hand out is unchanged.
+ * Converts a finished picture on the device and copies the result to `dst` (host memory; pinned memory makes the
+ * copy faster), so that the format every consumer of the reference converts to anyway (the SDL player uploads
+ * Y/U/V textures and lets the GPU convert, tools/easyav1_player.c:1338; colour metadata mapping
+ * src/easyav1.c:3287-3507) crosses PCIe once. No reference code computes these formats, so parity is against a
+ * numpy restatement of the integer formulas below (tests/test_convert.py): "parity unpinned".
+ *   NV12   8-bit 4:2:0 only: Y rows, then (h+1)/2 rows of interleaved U,V; row pitch dst_stride bytes
+ *   P010   10/12-bit 4:2:0 only: the same with 16-bit samples, value << (16 - bpc)
+ *   RGBA8  any layout and bit depth: R,G,B,255 per sample, chroma taken from the co-sited (x >> ss_hor, y >> ss_ver)
+ *          sample. With y' = Y - y_off, u' = U - c_off, v' = V - c_off:
+ *            R = clip8((ky*y' + krv*v' + 4096) >> 13),  G = clip8((ky*y' - kgu*u' - kgv*v' + 4096) >> 13),
+ *            B = clip8((ky*y' + kbu*u' + 4096) >> 13)
+ *          ky = rint(8192 * 255 / (yr << (bpc-8))), k.. = rint(8192 * 255 * m / (cr << (bpc-8))) with
+ *          yr, cr = 219, 224 (limited range) or 255, 255 (full), m = 2(1-Kr), 2(1-Kb)Kb/Kg, 2(1-Kr)Kr/Kg, 2(1-Kb),
+ *          (Kr, Kb) = (0.2126, 0.0722) for matrix 1 (BT.709), (0.2627, 0.0593) for 9 (BT.2020 NCL), else (0.299, 0.114);
+ *          y_off = 16 << (bpc-8) (limited) or 0, c_off = 128 << (bpc-8). Monochrome pictures use u' = v' = 0.
+ * Returns 0, EAV1CU_ERR_INVAL for a format the picture's layout / bit depth does not allow or a dst that is too
+ * small (needed bytes: dst_stride * (h + (h+1)/2) for NV12 / P010, dst_stride * h for RGBA8). Synchronous. */
+enum { EAV1CU_FMT_NV12 = 1, EAV1CU_FMT_P010 = 2, EAV1CU_FMT_RGBA8 = 3 };
+typedef struct Eav1Convert {
+    int32_t format;        /* EAV1CU_FMT_* */
+    int32_t matrix;        /* enum Dav1dMatrixCoefficients (include/dav1d/headers.h), RGBA8 only */
+    int32_t full_range;    /* Dav1dSequenceHeader.color_range, RGBA8 only */
+} Eav1Convert;
+int  eav1cu_pic_convert(Eav1cuCtx *ctx, int id, const Eav1Convert *cv, void *dst, size_t dst_stride, size_t dst_bytes);
+
 /* Pinned host memory for output pictures (backs the Dav1dPicAllocator replacement). */
 int  eav1cu_host_alloc(void **p, size_t bytes);
 void eav1cu_host_free(void *p);

@@ -20,6 +20,7 @@
 #include "../../easyav1_b200/csrc/sched.h"
 #include "../../easyav1_b200/csrc/postfilter.cuh"
 #include "../../easyav1_b200/csrc/filmgrain.cuh"
+#include "../../easyav1_b200/csrc/convert.cuh"
 #include "../../easyav1_b200/csrc/coverage.h"
 
 using namespace eav1;
@@ -128,6 +129,26 @@ int eav1cu_arena_download(Eav1cuCtx *c, size_t off, void *dst, size_t n) { if (c
 
 int eav1cu_pic_download_async(Eav1cuCtx *c, int id, void *const data[3], const ptrdiff_t stride[2])
 { return eav1cu_pic_download(c, id, data, stride); }
+
+int eav1cu_pic_convert(Eav1cuCtx *c, int id, const Eav1Convert *cv, void *dst, size_t dst_stride, size_t dst_bytes)
+{
+    if (!c || !cv || !dst || id < 0 || id >= (int)c->pics.size()) return EAV1CU_ERR_INVAL;
+    const Picture &p = c->pics[id];
+    const size_t need = conv_needed(cv->format, p.layout, p.bpc, p.w, p.h, dst_stride);
+    if (!need || need > dst_bytes) return EAV1CU_ERR_INVAL;
+    ConvParams P;
+    memset(&P, 0, sizeof(P));
+    for (int i = 0; i < 3; i++) P.src[i] = p.pl[i];
+    P.w = p.w; P.h = p.h; P.mono = p.layout == 0; P.ss_hor = p.layout != 3; P.ss_ver = p.layout == 1;
+    P.bpc = p.bpc; P.format = cv->format;
+    conv_coefficients(P, cv->matrix, cv->full_range);
+    P.dst = (uint8_t *)dst; P.dst_stride = (long long)dst_stride;
+    for (int y = 0; y < p.h; y++)
+        for (int x = 0; x < p.w; x++) {
+            if (p.bpc > 8) convert_sample<uint16_t>(P, x, y); else convert_sample<uint8_t>(P, x, y);
+        }
+    return 0;
+}
 int eav1cu_fence(Eav1cuCtx *, unsigned long long *ticket) { static unsigned long long n; *ticket = ++n; return 0; }
 int eav1cu_fence_wait(Eav1cuCtx *, unsigned long long) { return 0; }
 

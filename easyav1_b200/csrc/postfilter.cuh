@@ -542,6 +542,30 @@ EAV1_DEV void lr_wiener_tile(const PfParams &pp, const Eav1LrRec &r, int x0, int
     lr_load<pixel>(pp, r, x0, tw, sm.in, tid, nthr);
     CTA_SYNC();
     const FastDiv fdt(tw);
+    if (tw == LR_TW) {
+        // four outputs per thread from ten inputs read as five aligned pairs (the tile row pitch, 38, is even)
+        int f[7];
+#pragma unroll
+        for (int k = 0; k < 7; k++) f[k] = r.p.filter[0][k];
+        for (int i = tid; i < H * (LR_TW / 4); i += nthr) {
+            const int ty = i / (LR_TW / 4), x = (i - ty * (LR_TW / 4)) * 4;
+            const uint32_t *row = reinterpret_cast<const uint32_t *>(sm.in + ty * W + x);
+            int sv[10];
+#pragma unroll
+            for (int q = 0; q < 5; q++) { const uint32_t w2 = row[q]; sv[2 * q] = (int)(w2 & 0xffff); sv[2 * q + 1] = (int)(w2 >> 16); }
+            uint32_t o[4];
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                int sum = 1 << (bitdepth + 6);
+                if (sizeof(pixel) == 1) sum += sv[j + 3] * 128;
+#pragma unroll
+                for (int k = 0; k < 7; k++) sum += sv[j + k] * f[k];
+                o[j] = (uint32_t)iclip((sum + (1 << (rb_h - 1))) >> rb_h, 0, clip_limit - 1);
+            }
+            uint2 q2; q2.x = o[0] | (o[1] << 16); q2.y = o[2] | (o[3] << 16);
+            *reinterpret_cast<uint2 *>(&sm.hor[ty * LR_TW + x]) = q2;
+        }
+    } else
     for (int i = tid; i < H * tw; i += nthr) {
         const int ty = fdt.div(i), x = i - ty * tw;
         const uint16_t *row = sm.in + ty * W + x;

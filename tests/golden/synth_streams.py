@@ -127,6 +127,26 @@ def _superres(seed, bpc=8, layout=1, w=264, h=136, cdef=1, lr=1, sb128=0):
     return b
 
 
+def _uhd_grain_warp(seed):
+    """BASELINE.json configs[3] as a parity case: 3840x2160 10-bit with film grain signalled in the frame headers,
+    global motion (rot-zoom and affine, i.e. warped prediction of whole blocks) and local warped motion allowed."""
+    def b():
+        st = Stream(Seq(3840, 2160, 10, 1, film_grain_present=1), seed)
+        g = dict(seed=4321, y=[(0, 24), (64, 48), (128, 80), (255, 110)],
+                 uv=[[(0, 20), (255, 60)], [(30, 50), (220, 70)]], cfl=0, scaling_shift=10, lag=3,
+                 ar_y=[((i * 5) % 21) - 10 for i in range(24)],
+                 ar_uv=[[((i * 7) % 17) - 8 for i in range(25)], [((i * 11) % 19) - 9 for i in range(25)]],
+                 ar_shift=7, grain_scale_shift=0, uv_mult=[12, -16], uv_luma_mult=[20, 8], uv_offset=[3, -7],
+                 overlap=1, clip=0)
+        gm = {0: (2, [3 << 13, -(2 << 13), (1 << 16) + 300, -200, 200, (1 << 16) + 300]),
+              3: (3, [1 << 13, 2 << 13, (1 << 16) - 150, 100, -80, (1 << 16) + 210])}
+        st.frame(0, qidx=110, cdef=(5, [(12, 5), (24, 9), (0, 0), (40, 20)]), lr=(1, 2, 3), grain=g)
+        st.frame(1, offset=1, qidx=120, refresh=1, gmv=gm, cdef=(4, [(9, 4), (0, 3)]), lr=(2, 1, 1), grain=dict(g, seed=99, cfl=1))
+        st.frame(1, offset=2, qidx=130, refresh=2, gmv=gm, cdef=(3, [(20, 7)]), lr=(3, 3, 2), lr_unit=(1, 1), grain=dict(g, seed=7, lag=2))
+        return st
+    return b
+
+
 # name -> (builder, in the quick CPU subset?)
 STREAMS = {
     "syn_420_8":        (_plain(352, 288), True),
@@ -173,6 +193,7 @@ STREAMS = {
     # larger frames: many superblock rows / columns, restoration units of every size
     "syn_720p_10":      (_plain(1280, 720, 10, 1, seed=51, n_inter=2, inf=dict(tile_cols_log2=1)), False),
     "syn_sr_1080p":     (_superres(52, 8, 1, w=1920, h=1080), False),
+    "syn_2160p_10_grain_warp": (_uhd_grain_warp(61), True),
 }
 
 

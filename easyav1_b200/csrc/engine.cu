@@ -397,7 +397,7 @@ lr_kernel(PfParams pp, const Eav1LrRec *__restrict__ recs)
     if (threadIdx.x < sizeof(Eav1LrRec) / 4)
         reinterpret_cast<uint32_t *>(&r)[threadIdx.x] = reinterpret_cast<const uint32_t *>(&recs[blockIdx.y])[threadIdx.x];
     __syncthreads();
-    lr_tile<pixel>(pp, r, blockIdx.x, sm, threadIdx.x, blockDim.x);
+    lr_tile<pixel>(pp, r, blockIdx.x, blockIdx.z, sm, threadIdx.x, blockDim.x);
 }
 
 // Super-resolution: one thread per output sample, blockIdx.z = plane, the 64-phase filter table in shared memory.
@@ -1489,7 +1489,7 @@ static int plan_launch(Eav1cuCtx *ctx, FramePlan &pl)
         Picture &src = *lr_src, &cur = *lr_out;
         for (int i = 0; i < 3; i++) { pp.b[i] = src.pl[i]; pp.p[i] = cur.pl[i]; }
         TCK(TC_D2D, cudaMemcpyAsync(cur.base, src.base, std::min(cur.bytes, src.bytes), cudaMemcpyDeviceToDevice, st));
-        dim3 grid(384 / LR_TW, (unsigned)pl.n_lr);
+        dim3 grid(384 / LR_TW, (unsigned)pl.n_lr, 64 / LR_SUB_ROWS);
         if (hbd) lr_kernel<uint16_t><<<grid, 128, 0, st>>>(pp, pl.d_lr);
         else     lr_kernel<uint8_t><<<grid, 128, 0, st>>>(pp, pl.d_lr);
         ctx->n_launches++;

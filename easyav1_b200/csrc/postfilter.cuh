@@ -461,31 +461,35 @@ EAV1_DEV void resize_sample(const ResizeParams &rp, const int8_t (*filt)[8], int
 // at the frame top/bottom and left/right the edge sample is replicated.
 
 #define LR_TW 32
+#define LR_SUB_ROWS 32     // a stripe (<= 64 rows) is filtered as two halves by two CTAs: twice the groups in flight
 struct alignas(16) LrSmem {
-    uint16_t in[(64 + 6) * (LR_TW + 6)];
+    uint16_t in[(LR_SUB_ROWS + 6) * (LR_TW + 6)];
     union alignas(16) {
-        uint16_t hor[(64 + 6) * LR_TW];                 // Wiener: horizontally filtered rows
+        uint16_t hor[(LR_SUB_ROWS + 6) * LR_TW];        // Wiener: horizontally filtered rows
         struct {
-            int32_t a3[(64 + 2) * (LR_TW + 2)]; uint16_t b3[(64 + 2) * (LR_TW + 2)];
-            int32_t a5[34 * (LR_TW + 2)];       uint16_t b5[34 * (LR_TW + 2)];
+            int32_t a3[(LR_SUB_ROWS + 2) * (LR_TW + 2)]; uint16_t b3[(LR_SUB_ROWS + 2) * (LR_TW + 2)];
+            int32_t a5[(LR_SUB_ROWS / 2 + 2) * (LR_TW + 2)]; uint16_t b5[(LR_SUB_ROWS / 2 + 2) * (LR_TW + 2)];
         } s;
     };
 };
 
+// Rows row0 .. row0+nrows-1 of the stripe (plus 3 above and below) and columns x0-3 .. x0+tw+2 of the unit. Rows that
+// lie outside the stripe follow the reference's rule (2 saved pre-CDEF rows from A, the third replicated, or the
+// stripe's own edge row at the frame border); rows inside it, also beyond the sub-range, are the CDEF output B.
 template <typename pixel>
-EAV1_DEV void lr_load(const PfParams &pp, const Eav1LrRec &r, int x0, int tw, uint16_t *in, int tid, int nthr)
+EAV1_DEV void lr_load(const PfParams &pp, const Eav1LrRec &r, int x0, int tw, int row0, int nrows, uint16_t *in, int tid, int nthr)
 {
     const Plane &B = pp.b[r.plane], &A = pp.a[r.plane];
     const int ss_ver = r.plane ? pp.ss_ver : 0;
     const int ph = (pp.h + ss_ver) >> ss_ver;
-    const int W = tw + 6, H = r.h + 6;
+    const int W = tw + 6, H = nrows + 6;
     // Full-width slices whose 3-sample halo exists on both sides (everything but the first / last slice of a picture
     // row) are read as aligned 32-bit words: columns x0-4 .. x0+tw+3, of which the tile keeps x0-3 .. x0+tw+2.
     if (tw == LR_TW && (x0 > 0 || (r.edges & 1)) && (x0 + tw + 4 <= r.w || (r.edges & 2))) {
         constexpr int SPW = 4 / (int)sizeof(pixel), NW = (LR_TW + 8) / SPW;
         for (int i = tid; i < NW * H; i += nthr) {
             const int ty = i / NW, wi = i - ty * NW;
-            const int ry = ty - 3;
+            const int ry = row0 + ty - 3;
             const Plane *src = &B;
             int sy;
             if (ry < 0) {
@@ -506,7 +510,7 @@ EAV1_DEV void lr_load(const PfParams &pp, const Eav1LrRec &r, int x0, int tw, ui
     const FastDiv fdW(W);
     for (int i = tid; i < W * H; i += nthr) {
         const int ty = fdW.div(i), tx = i - ty * W;
-        const int ry = ty - 3;
+        const int ry = row0 + ty - 3;
         int cx = x0 + tx - 3;
         if (cx < 0 && !(r.edges & 1)) cx = 0;
         if (cx >= r.w && !(r.edges & 2)) cx = r.w - 1;
@@ -533,13 +537,13 @@ EAV1_DEV void lr_store4(const Plane &P, int x, int y, const int v[4])
 }
 
 template <typename pixel>
-EAV1_DEV void lr_wiener_tile(const PfParams &pp, const Eav1LrRec &r, int x0, int tw, LrSmem &sm, int tid, int nthr)
+EAV1_DEV void lr_wiener_tile(const PfParams &pp, const Eav1LrRec &r, int x0, int tw, int row0, int nrows, LrSmem &sm, int tid, int nthr)
 {
     const int bitdepth = 32 - clz32((unsigned)pp.bitdepth_max);
     const int rb_h = 3 + (bitdepth == 12) * 2, rb_v = 11 - (bitdepth == 12) * 2;
     const int clip_limit = 1 << (bitdepth + 1 + 7 - rb_h);
-    const int W = tw + 6, H = r.h + 6;
-    lr_load<pixel>(pp, r, x0, tw, sm.in, tid, nthr);
+    const int W = tw + 6, H = nrows + 6;
+    lr_load<pixel>(pp, r, x0, tw, row0, nrows, sm.in, tid, nthr);
     CTA_SYNC();
     const FastDiv fdt(tw);
     if (tw == LR_TW) {
@@ -577,7 +581,7 @@ EAV1_DEV void lr_wiener_tile(const PfParams &pp, const Eav1LrRec &r, int x0, int
     CTA_SYNC();
     const Plane &P = pp.p[r.plane];
     if (tw == LR_TW) {
-        for (int i = tid; i < r.h * (LR_TW / 4); i += nthr) {
+        for (int i = tid; i < nrows * (LR_TW / 4); i += nthr) {
             const int y = i / (LR_TW / 4), x = (i - y * (LR_TW / 4)) * 4;
             int sum[4], v[4];
 #pragma unroll
@@ -590,16 +594,16 @@ EAV1_DEV void lr_wiener_tile(const PfParams &pp, const Eav1LrRec &r, int x0, int
             }
 #pragma unroll
             for (int j = 0; j < 4; j++) v[j] = iclip((sum[j] + (1 << (rb_v - 1))) >> rb_v, 0, pp.bitdepth_max);
-            lr_store4<pixel>(P, r.x + x0 + x, r.y + y, v);
+            lr_store4<pixel>(P, r.x + x0 + x, r.y + row0 + y, v);
         }
         CTA_SYNC();
         return;
     }
-    for (int i = tid; i < r.h * tw; i += nthr) {
+    for (int i = tid; i < nrows * tw; i += nthr) {
         const int y = fdt.div(i), x = i - y * tw;
         int sum = -(1 << (bitdepth + (rb_v - 1)));
         for (int k = 0; k < 7; k++) sum += sm.hor[(y + k) * LR_TW + x] * r.p.filter[1][k];
-        *px_at<pixel>(P, r.x + x0 + x, r.y + y) = (pixel)iclip((sum + (1 << (rb_v - 1))) >> rb_v, 0, pp.bitdepth_max);
+        *px_at<pixel>(P, r.x + x0 + x, r.y + row0 + y) = (pixel)iclip((sum + (1 << (rb_v - 1))) >> rb_v, 0, pp.bitdepth_max);
     }
     CTA_SYNC();
 }
@@ -627,11 +631,12 @@ EAV1_DEV void sgr_ab(const PfParams &pp, const uint16_t *in, int W, int cx, int 
 }
 
 template <typename pixel>
-EAV1_DEV void lr_sgr_tile(const PfParams &pp, const Eav1LrRec &r, int x0, int tw, LrSmem &sm, int tid, int nthr)
+EAV1_DEV void lr_sgr_tile(const PfParams &pp, const Eav1LrRec &r, int x0, int tw, int row0, int nrows, LrSmem &sm, int tid, int nthr)
 {
-    const int W = tw + 6, SW = tw + 2, h = r.h;
+    // row0 is even, so the 5x5 filter's row pairs (computed on rows -1, 1, 3, ... of the stripe) keep their parity
+    const int W = tw + 6, SW = tw + 2, h = nrows;
     const bool do5 = r.kind != EAV1_LR_SGR_3X3, do3 = r.kind != EAV1_LR_SGR_5X5;
-    lr_load<pixel>(pp, r, x0, tw, sm.in, tid, nthr);
+    lr_load<pixel>(pp, r, x0, tw, row0, nrows, sm.in, tid, nthr);
     CTA_SYNC();
     const FastDiv fdS(SW), fdt(tw);
     if (do3)
@@ -685,25 +690,25 @@ EAV1_DEV void lr_sgr_tile(const PfParams &pp, const Eav1LrRec &r, int x0, int tw
             int v4[4];
 #pragma unroll
             for (int j = 0; j < 4; j++) v4[j] = sample(x + j, y);
-            lr_store4<pixel>(P, r.x + x0 + x, r.y + y, v4);
+            lr_store4<pixel>(P, r.x + x0 + x, r.y + row0 + y, v4);
         }
     } else {
         for (int i = tid; i < h * tw; i += nthr) {
             const int y = fdt.div(i), x = i - y * tw;
-            *px_at<pixel>(P, r.x + x0 + x, r.y + y) = (pixel)sample(x, y);
+            *px_at<pixel>(P, r.x + x0 + x, r.y + row0 + y) = (pixel)sample(x, y);
         }
     }
     CTA_SYNC();
 }
 
 template <typename pixel>
-EAV1_DEV void lr_tile(const PfParams &pp, const Eav1LrRec &r, int slice, LrSmem &sm, int tid, int nthr)
+EAV1_DEV void lr_tile(const PfParams &pp, const Eav1LrRec &r, int slice, int sub, LrSmem &sm, int tid, int nthr)
 {
-    const int x0 = slice * LR_TW;
-    if (x0 >= r.w) return; // uniform across the CTA
-    const int tw = imin(LR_TW, r.w - x0);
-    if (r.kind <= EAV1_LR_WIENER5) lr_wiener_tile<pixel>(pp, r, x0, tw, sm, tid, nthr);
-    else lr_sgr_tile<pixel>(pp, r, x0, tw, sm, tid, nthr);
+    const int x0 = slice * LR_TW, row0 = sub * LR_SUB_ROWS;
+    if (x0 >= r.w || row0 >= r.h) return; // uniform across the CTA
+    const int tw = imin(LR_TW, r.w - x0), nrows = imin(LR_SUB_ROWS, r.h - row0);
+    if (r.kind <= EAV1_LR_WIENER5) lr_wiener_tile<pixel>(pp, r, x0, tw, row0, nrows, sm, tid, nthr);
+    else lr_sgr_tile<pixel>(pp, r, x0, tw, row0, nrows, sm, tid, nthr);
 }
 
 } // namespace eav1

@@ -1445,6 +1445,10 @@ static int plan_launch(Eav1cuCtx *ctx, FramePlan &pl)
         Picture &dst = (has_lr || superres) ? ctx->work[1] : cur;
         for (int i = 0; i < 3; i++) pp.b[i] = dst.pl[i];
         pp.lfmask = pl.d_lfmask;
+        // Most 8x8 blocks of a typical frame are left alone by CDEF (skipped, strength 0, cdef_idx -1): the whole
+        // picture is copied by the copy engine first (L2-resident, a few microseconds) and the kernel only writes
+        // the blocks it filters; a warp copying its own 96 bytes spent its life waiting for them.
+        TCK(TC_D2D, cudaMemcpyAsync(dst.base, A.base, std::min(dst.bytes, A.bytes), cudaMemcpyDeviceToDevice, st));
         dim3 grid((fd->bw4 / 2 + 8) / 8, (fd->bh4 + 1) / 2);
         if (hbd) cdef_kernel<uint16_t><<<grid, 256, 0, st>>>(pp);
         else     cdef_kernel<uint8_t><<<grid, 256, 0, st>>>(pp);

@@ -268,29 +268,6 @@ EAV1_DEV void cdef_filter(const Eav1Tables *tab, const Plane &out, int x0, int y
     }
 }
 
-// Blocks CDEF leaves alone (no coded coefficients, strength 0, cdef_idx -1: most blocks of a typical inter frame) are
-// copied a -> b: one row per lane where a row is 4, 8 or 16 bytes (block positions are multiples of the block width,
-// plane strides multiples of 64 bytes, so the vector accesses are aligned), per sample otherwise.
-template <typename pixel>
-EAV1_DEV void cdef_copy(const Plane &in, const Plane &out, int x0, int y0, int w, int h, int tid, int nthr)
-{
-    const int row_bytes = w * (int)sizeof(pixel);
-    if (row_bytes == 4 || row_bytes == 8 || row_bytes == 16) {
-        for (int y = tid; y < h; y += nthr) {
-            const uint8_t *s = in.p + (ptrdiff_t)(y0 + y) * in.stride + (ptrdiff_t)x0 * (int)sizeof(pixel);
-            uint8_t *d = out.p + (ptrdiff_t)(y0 + y) * out.stride + (ptrdiff_t)x0 * (int)sizeof(pixel);
-            if (row_bytes == 4) *reinterpret_cast<uint32_t *>(d) = *reinterpret_cast<const uint32_t *>(s);
-            else if (row_bytes == 8) *reinterpret_cast<uint2 *>(d) = *reinterpret_cast<const uint2 *>(s);
-            else *reinterpret_cast<uint4 *>(d) = *reinterpret_cast<const uint4 *>(s);
-        }
-        return;
-    }
-    for (int i = tid; i < w * h; i += nthr) {
-        const int y = i / w, x = i - y * w;
-        *px_at<pixel>(out, x0 + x, y0 + y) = *px_at<pixel>(in, x0 + x, y0 + y);
-    }
-}
-
 // Direction search on the 8x8 block held in tile[0] (interior at +2,+2), cdef_find_dir
 // (cdef_tmpl.c:220-315). Step 1: every thread adds its samples into the line sums of all eight
 // directions (shared-memory adds; 64 samples x 8 directions spread over the group). Step 2: eight
@@ -364,15 +341,9 @@ EAV1_DEV void cdef_block(const PfParams &pp, int bx, int by, bool valid, CdefSme
     int uv_sec = uv_lvl & 3; uv_sec += uv_sec == 3; uv_sec <<= bd8;
     const int damping = pp.cdef_damping + bd8;
 
-    if (!active && nthr <= 32) {
-        // a whole group (one warp, barriers are __syncwarp) has nothing to filter: copy and leave
-        cdef_copy<pixel>(pp.a[0], pp.b[0], lx, ly, 8, 8, tid, nthr);
-        if (has_chroma) {
-            cdef_copy<pixel>(pp.a[1], pp.b[1], cx, cy, cw, chh, tid, nthr);
-            cdef_copy<pixel>(pp.a[2], pp.b[2], cx, cy, cw, chh, tid, nthr);
-        }
-        return;
-    }
+    // The output picture starts as a copy of the input (made by the caller before this stage), so only filtered
+    // blocks are written. A whole group (one warp, barriers are __syncwarp) with nothing to filter leaves at once.
+    if (!active && nthr <= 32) return;
     if (active) {
         for (int i = tid; i < 8 * 16; i += nthr) (&sm.part[0][0])[i] = 0;
         cdef_load<pixel>(pp.a[0], lx, ly, 8, 8, edges, sm.tile[0], tid, nthr);
@@ -411,16 +382,12 @@ EAV1_DEV void cdef_block(const PfParams &pp, int bx, int by, bool valid, CdefSme
         } else do_y = y_sec != 0;
     }
     if (do_y) cdef_filter<pixel>(pp.tab, pp.b[0], lx, ly, 8, 8, sm.tile[0], pri, y_sec, ydir, damping, pp.bitdepth_max, tid, nthr);
-    else cdef_copy<pixel>(pp.a[0], pp.b[0], lx, ly, 8, 8, tid, nthr);
     if (has_chroma) {
         if (active && uv_lvl) {
             const uint8_t uvd422[8] = { 7, 0, 2, 4, 5, 6, 6, 6 };
             const int uvdir = uv_pri ? (pp.layout == 2 ? uvd422[dir] : dir) : 0;
             cdef_filter<pixel>(pp.tab, pp.b[1], cx, cy, cw, chh, sm.tile[1], uv_pri, uv_sec, uvdir, damping - 1, pp.bitdepth_max, tid, nthr,
                                &pp.b[2], sm.tile[2]);
-        } else {
-            cdef_copy<pixel>(pp.a[1], pp.b[1], cx, cy, cw, chh, tid, nthr);
-            cdef_copy<pixel>(pp.a[2], pp.b[2], cx, cy, cw, chh, tid, nthr);
         }
     }
 }

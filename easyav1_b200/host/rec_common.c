@@ -35,10 +35,18 @@ __thread Eav1Walk eav1_walk;
 static pthread_mutex_t g_mu = PTHREAD_MUTEX_INITIALIZER;
 static Eav1Rec *g_recs[MAX_RECS];
 
+/* Every thread caches the recorder it used last. A decoder can be torn down by another thread (the last
+ * dav1d_picture_unref), so the cached pointer is only dereferenced while no recorder has been destroyed since it was
+ * cached: destroy_rec bumps the generation. */
+static atomic_uint g_rec_generation;
+static __thread unsigned t_rec_generation;
+
 Eav1Rec *eav1rec_for_ctx(const Dav1dContext *c)
 {
     Eav1Rec *r = eav1_walk.r;
-    if (r && r->c == c) return r;
+    const unsigned gen = atomic_load_explicit(&g_rec_generation, memory_order_acquire);
+    if (r && t_rec_generation == gen && r->c == c) return r;
+    t_rec_generation = gen;
     pthread_mutex_lock(&g_mu);
     r = NULL;
     for (int i = 0; i < MAX_RECS; i++)
@@ -564,11 +572,21 @@ void eav1rec_frame_end(Eav1Rec *r, const Dav1dFrameContext *f, int retval)
         /* command lists: tiles are independent in reconstruction, so any tile order is legal */
         size_t total = 0;
         for (int i = 0; i < fr->n_tiles; i++) total += fr->tiles[i].n;
-        j->cmds = grow(j->cmds, &j->cap_cmds, total + 1, sizeof(Eav1Cmd));
-        size_t pos = 0;
-        for (int i = 0; i < fr->n_tiles; i++) {
-            memcpy(j->cmds + pos, fr->tiles[i].cmds, fr->tiles[i].n * sizeof(Eav1Cmd));
-            pos += fr->tiles[i].n;
+        if (fr->n_tiles == 1) {
+            /* one tile (the usual case): its list becomes the job's by exchanging the two buffers; this runs under
+             * dav1d's task lock, where copying a few hundred KB would stall every worker */
+            Eav1List *t0 = &fr->tiles[0];
+            t0->cmds = grow(t0->cmds, &t0->cap, total + 1, sizeof(Eav1Cmd));
+            Eav1Cmd *p = j->cmds; const size_t c = j->cap_cmds;
+            j->cmds = t0->cmds; j->cap_cmds = t0->cap;
+            t0->cmds = p; t0->cap = c; t0->n = 0;
+        } else {
+            j->cmds = grow(j->cmds, &j->cap_cmds, total + 1, sizeof(Eav1Cmd));
+            size_t pos = 0;
+            for (int i = 0; i < fr->n_tiles; i++) {
+                memcpy(j->cmds + pos, fr->tiles[i].cmds, fr->tiles[i].n * sizeof(Eav1Cmd));
+                pos += fr->tiles[i].n;
+            }
         }
         j->n_cmds = total;
         /* payload / lf / lr: swap buffers with the frame slot */
@@ -901,6 +919,7 @@ static void destroy_rec(Eav1Rec *r, AllocState *as)
     if (!r) return;
     pthread_mutex_lock(&g_mu);
     for (int i = 0; i < MAX_RECS; i++) if (g_recs[i] == r) g_recs[i] = NULL;
+    atomic_fetch_add_explicit(&g_rec_generation, 1, memory_order_release);
     pthread_mutex_unlock(&g_mu);
     if (eav1_walk.r == r) eav1_walk.r = NULL;
     if (as) {

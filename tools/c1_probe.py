@@ -25,8 +25,10 @@ clip = sys.argv[1] if len(sys.argv) > 1 else "c1_360p_bench"
 path = os.path.join(ROOT, "tests", "golden", clip + ".webm")
 for name, lib, envs in (("reference", "oracle/_ref/libeasyav1_ref.so", [{}]),
                         ("ours", "easyav1_b200/libeasyav1_b200.so",
-                         [{}, {"EASYAV1_THREADS": "1"}, {"EASYAV1_THREADS": "4"}, {"EASYAV1_THREADS": "8"}, {"EASYAV1_FRAME_DELAY": "2"},
-                          {"EASYAV1_FRAME_DELAY": "4"}, {"EAV1_TIMING": "1"}])):
+                         [{}] + [{"EASYAV1_THREADS": t} for t in os.environ.get("C1_THREADS", "1,4,8").split(",")] +
+                         [{"EASYAV1_THREADS": t, "EASYAV1_FRAME_DELAY": d} for t, d in
+                          [x.split(":") for x in os.environ.get("C1_COMBOS", "").split(",") if x]] +
+                         ([{"EAV1_TIMING": "1"}] if os.environ.get("C1_TIMING") else []))):
     for env in envs:
         e = dict(os.environ); e.update(env)
         out = subprocess.run([sys.executable, "-c", CHILD, os.path.join(ROOT, lib), path], capture_output=True, text=True, env=e, timeout=300)

@@ -155,8 +155,10 @@ EAV1_EXEC_LINK int exec_cmd(const FrameCtx &fc, const Eav1Cmd &c, CtaScratch &sm
                                next->x == c.x && next->y == c.y && next->w == c.w && next->h == c.h &&
                                !(c.flags & EAV1_F_DST_ARENA);
             const int16_t *res = fused ? (const int16_t *)(fc.arena + next->dst_off) : nullptr;
-            uint2 res_pre = uint2();
-            if (fused && tid < ((c.w * c.h) >> 2)) res_pre = *reinterpret_cast<const uint2 *>(res + (tid << 2));
+            ResPre res_pre = ResPre();
+            res_pre.tid = tid; res_pre.nthr = nthr;
+            if (fused && tid < ((c.w * c.h) >> 2)) res_pre.a = *reinterpret_cast<const uint2 *>(res + (tid << 2));
+            if (fused && tid + nthr < ((c.w * c.h) >> 2)) res_pre.b = *reinterpret_cast<const uint2 *>(res + ((tid + nthr) << 2));
             build_edge<pixel>(fc.cur[c.plane], c, bdmax, sm.ip.edge, tid, nthr);
             PROF_MARK(2);
             const bool added = ipred_block<pixel>(fc.tab, dst8, dstride, sm.ip.edge, sm.ip.edge2, c.u.ipred.mode, c.w, c.h,

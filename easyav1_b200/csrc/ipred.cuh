@@ -170,12 +170,16 @@ EAV1_DEV void store4(pixel *q, int v0, int v1, int v2, int v3) {
 }
 
 // the same with the residual of the transform block added (row-major int16, `r` points at this group)
+// Residuals fetched before the edge was gathered: the thread's first two groups of four samples (i = tid and
+// i = tid + nthr), whose latency is long gone when the prediction is ready. Two groups cover a 32x32 block on a
+// 128-thread group and a 16x16 block on a warp; further groups are loaded where they are used.
+struct ResPre { uint2 a, b; int tid, nthr; };
+
 template <typename pixel>
 EAV1_DEV void store4r(pixel *q, int v0, int v1, int v2, int v3, const int16_t *r, int bitdepth_max,
-                      bool have_pre, uint2 pre) {
+                      int i, const ResPre &pre) {
     if (r) {
-        // the thread's first group was fetched before the edge was gathered (its latency is long gone)
-        const uint2 rr = have_pre ? pre : *reinterpret_cast<const uint2 *>(r);
+        const uint2 rr = i == pre.tid ? pre.a : i == pre.tid + pre.nthr ? pre.b : *reinterpret_cast<const uint2 *>(r);
         v0 = iclip(v0 + (int16_t)(rr.x & 0xffff), 0, bitdepth_max); v1 = iclip(v1 + (int16_t)(rr.x >> 16), 0, bitdepth_max);
         v2 = iclip(v2 + (int16_t)(rr.y & 0xffff), 0, bitdepth_max); v3 = iclip(v3 + (int16_t)(rr.y >> 16), 0, bitdepth_max);
     }
@@ -221,7 +225,7 @@ template <typename pixel>
 EAV1_DEV bool ipred_block(const Eav1Tables *tab, pixel *dst, int stride, uint16_t *edge, uint16_t *edge2,
                           int mode, int w, int h, int angle_in, int max_w, int max_h,
                           int bitdepth_max, int tid, int nthr, uint16_t *tile, const int16_t *res = nullptr,
-                          uint2 res_pre = uint2())
+                          const ResPre &res_pre = ResPre())
 {
     const uint16_t *E = edge + EDGE_C;
     // w and h are powers of two >= 4: samples are handled four to a thread, i4 -> (y, x = 4*(i4 & m4))
@@ -244,19 +248,19 @@ EAV1_DEV bool ipred_block(const Eav1Tables *tab, pixel *dst, int stride, uint16_
             }
             dc = s;
         }
-        for (int i = tid; i < n4; i += nthr) store4r<pixel>(dst + (i >> lw4) * stride + ((i & m4) << 2), dc, dc, dc, dc, res ? res + (i << 2) : nullptr, bitdepth_max, i == tid, res_pre);
+        for (int i = tid; i < n4; i += nthr) store4r<pixel>(dst + (i >> lw4) * stride + ((i & m4) << 2), dc, dc, dc, dc, res ? res + (i << 2) : nullptr, bitdepth_max, i, res_pre);
         break;
     }
     case IP_VERT:
         for (int i = tid; i < n4; i += nthr) {
             const int x = (i & m4) << 2;
-            store4r<pixel>(dst + (i >> lw4) * stride + x, E[1 + x], E[2 + x], E[3 + x], E[4 + x], res ? res + (i << 2) : nullptr, bitdepth_max, i == tid, res_pre);
+            store4r<pixel>(dst + (i >> lw4) * stride + x, E[1 + x], E[2 + x], E[3 + x], E[4 + x], res ? res + (i << 2) : nullptr, bitdepth_max, i, res_pre);
         }
         break;
     case IP_HOR:
         for (int i = tid; i < n4; i += nthr) {
             const int y = i >> lw4, v = E[-(1 + y)];
-            store4r<pixel>(dst + y * stride + ((i & m4) << 2), v, v, v, v, res ? res + (i << 2) : nullptr, bitdepth_max, i == tid, res_pre);
+            store4r<pixel>(dst + y * stride + ((i & m4) << 2), v, v, v, v, res ? res + (i << 2) : nullptr, bitdepth_max, i, res_pre);
         }
         break;
     case IP_PAETH: {
@@ -272,7 +276,7 @@ EAV1_DEV bool ipred_block(const Eav1Tables *tab, pixel *dst, int stride, uint16_
                 const int ld = iabs(l - base), td = iabs(t - base), tld = iabs(tl - base);
                 v[k] = ld <= td && ld <= tld ? l : td <= tld ? t : tl;
             }
-            store4r<pixel>(dst + y * stride + x, v[0], v[1], v[2], v[3], res ? res + (i << 2) : nullptr, bitdepth_max, i == tid, res_pre);
+            store4r<pixel>(dst + y * stride + x, v[0], v[1], v[2], v[3], res ? res + (i << 2) : nullptr, bitdepth_max, i, res_pre);
         }
         break;
     }
@@ -292,7 +296,7 @@ EAV1_DEV bool ipred_block(const Eav1Tables *tab, pixel *dst, int stride, uint16_
                 else
                     v[k] = (wh_[x] * E[-(1 + y)] + (256 - wh_[x]) * right + 128) >> 8;
             }
-            store4r<pixel>(dst + y * stride + x0, v[0], v[1], v[2], v[3], res ? res + (i << 2) : nullptr, bitdepth_max, i == tid, res_pre);
+            store4r<pixel>(dst + y * stride + x0, v[0], v[1], v[2], v[3], res ? res + (i << 2) : nullptr, bitdepth_max, i, res_pre);
         }
         break;
     }
@@ -325,7 +329,7 @@ EAV1_DEV bool ipred_block(const Eav1Tables *tab, pixel *dst, int stride, uint16_
                 if (base < max_base_x) v[k] = (top[base] * (64 - frac) + top[base + 1] * frac + 32) >> 6;
                 else v[k] = top[max_base_x];
             }
-            store4r<pixel>(dst + y * stride + x0, v[0], v[1], v[2], v[3], res ? res + (i << 2) : nullptr, bitdepth_max, i == tid, res_pre);
+            store4r<pixel>(dst + y * stride + x0, v[0], v[1], v[2], v[3], res ? res + (i << 2) : nullptr, bitdepth_max, i, res_pre);
         }
         break;
     }
@@ -377,7 +381,7 @@ EAV1_DEV bool ipred_block(const Eav1Tables *tab, pixel *dst, int stride, uint16_
                 }
                 o[k] = (v + 32) >> 6;
             }
-            store4r<pixel>(dst + y * stride + x0, o[0], o[1], o[2], o[3], res ? res + (i << 2) : nullptr, bitdepth_max, i == tid, res_pre);
+            store4r<pixel>(dst + y * stride + x0, o[0], o[1], o[2], o[3], res ? res + (i << 2) : nullptr, bitdepth_max, i, res_pre);
         }
         break;
     }
@@ -410,7 +414,7 @@ EAV1_DEV bool ipred_block(const Eav1Tables *tab, pixel *dst, int stride, uint16_
                 if (base < max_base_y) v[k] = (left[-base] * (64 - frac) + left[-(base + 1)] * frac + 32) >> 6;
                 else v[k] = left[-max_base_y];
             }
-            store4r<pixel>(dst + y * stride + x0, v[0], v[1], v[2], v[3], res ? res + (i << 2) : nullptr, bitdepth_max, i == tid, res_pre);
+            store4r<pixel>(dst + y * stride + x0, v[0], v[1], v[2], v[3], res ? res + (i << 2) : nullptr, bitdepth_max, i, res_pre);
         }
         break;
     }
@@ -468,7 +472,7 @@ EAV1_DEV bool ipred_block(const Eav1Tables *tab, pixel *dst, int stride, uint16_
         for (int i = tid; i < n4; i += nthr) {
             const uint16_t *t = T + (i << 2);
             store4r<pixel>(dst + (i >> lw4) * stride + ((i & m4) << 2), t[0], t[1], t[2], t[3],
-                           res ? res + (i << 2) : nullptr, bitdepth_max, i == tid, res_pre);
+                           res ? res + (i << 2) : nullptr, bitdepth_max, i, res_pre);
         }
         break;
     }

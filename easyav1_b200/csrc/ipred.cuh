@@ -51,6 +51,24 @@ EAV1_DEV void build_edge(const Plane &pl, const Eav1Cmd &c, int bitdepth_max, ui
     const int nt = (needs & 2) ? szt : 0, ntr = ((needs & 2) && (needs & 8)) ? szt : 0;
     const int n_left = c.u.ipred.n_left, n_top = c.u.ipred.n_top;
     const int nb = (c.u.ipred.have & 8) ? c.u.ipred.n_bl : 0, nr = (c.u.ipred.have & 16) ? c.u.ipred.n_tr : 0;
+    // The usual case — no top-right / bottom-left part, every needed neighbour exists and none has to be replicated —
+    // needs none of the case analysis below: left column, top row and corner are plain loads. This code runs once per
+    // transform block on the frame's critical chain, where every instruction is a few cycles of a single warp.
+    if (!nbl && !ntr && (!nl || (have_left && n_left >= szl)) && (!nt || (have_top && n_top >= szt)) &&
+        (!(needs & 4) || (have_left && have_top && !(c.u.ipred.have & 4)))) {
+        const int nc = (needs & 4) ? 1 : 0;
+        for (int j = tid; j < nl + nt + nc; j += nthr) {
+            int px, py, slot;
+            if (j < nl) { px = ex - 1; py = ey + j; slot = -(1 + j); }
+            else if (j < nl + nt) { px = ex + (j - nl); py = ey - 1; slot = 1 + (j - nl); }
+            else { px = ex - 1; py = ey - 1; slot = 0; }
+            E[slot] = (uint16_t)*px_at<pixel>(pl, px, py);
+        }
+        PROF_MARK(22);
+        CTA_SYNC();
+        PROF_MARK(24);
+        return;
+    }
     const int fill_l = ((1 << bitdepth) >> 1) + 1, fill_t = ((1 << bitdepth) >> 1) - 1;
     const int total = nl + nbl + nt + ntr;
     // where edge sample j comes from: (px,py) in the plane, or the constant cst >= 0; slot = index into E

@@ -117,6 +117,136 @@ EAV1_DEV void lf_edge4(pixel *dst, int E, int I, int H, ptrdiff_t stridea, ptrdi
     }
 }
 
+// The same filter on one line held in registers: a[8 + k] = q_k, a[7 - k] = p_k. Returns how many samples on each side
+// of the edge it changed (0, 1, 2, 3 or 6). Arithmetic identical to lf_edge4 (loopfilter_tmpl.c:38-170).
+EAV1_DEV int lf_core(int *a, int E, int I, int H, int wd, int bitdepth_max)
+{
+    const int bd8 = (32 - clz32((unsigned)bitdepth_max)) - 8;
+    const int F = 1 << bd8;
+    E <<= bd8; I <<= bd8; H <<= bd8;
+    const int dmin = -128 * (1 << bd8), dmax = 128 * (1 << bd8) - 1;
+    const int p1 = a[6], p0 = a[7], q0 = a[8], q1 = a[9];
+    const int p2 = a[5], q2 = a[10], p3 = a[4], q3 = a[11];
+    bool fm = iabs(p1 - p0) <= I && iabs(q1 - q0) <= I && iabs(p0 - q0) * 2 + (iabs(p1 - q1) >> 1) <= E;
+    if (wd > 4) {
+        fm = fm && iabs(p2 - p1) <= I && iabs(q2 - q1) <= I;
+        if (wd > 6) fm = fm && iabs(p3 - p2) <= I && iabs(q3 - q2) <= I;
+    }
+    if (!fm) return 0;
+    bool flat8out = false, flat8in = false;
+    if (wd >= 16)
+        flat8out = iabs(a[1] - p0) <= F && iabs(a[2] - p0) <= F && iabs(a[3] - p0) <= F &&
+                   iabs(a[12] - q0) <= F && iabs(a[13] - q0) <= F && iabs(a[14] - q0) <= F;
+    if (wd >= 6) flat8in = iabs(p2 - p0) <= F && iabs(p1 - p0) <= F && iabs(q1 - q0) <= F && iabs(q2 - q0) <= F;
+    if (wd >= 8) flat8in = flat8in && iabs(p3 - p0) <= F && iabs(q3 - q0) <= F;
+    if (wd >= 16 && flat8out && flat8in) {
+        int v[14], out[12];
+#pragma unroll
+        for (int k = 0; k < 14; k++) v[k] = a[1 + k];          // p6 .. q6
+#pragma unroll
+        for (int k = 0; k < 12; k++) {
+            int sum = 8;
+#pragma unroll
+            for (int t = -6; t <= 6; t++) sum += v[iclip(k + 1 + t, 0, 13)];
+            sum += v[k + 1] + v[iclip(k, 0, 13)] + v[iclip(k + 2, 0, 13)];
+            out[k] = sum >> 4;
+        }
+#pragma unroll
+        for (int k = 0; k < 12; k++) a[2 + k] = out[k];         // p5 .. q5
+        return 6;
+    }
+    if (wd >= 8 && flat8in) {
+        a[5] = (p3 + p3 + p3 + 2 * p2 + p1 + p0 + q0 + 4) >> 3;
+        a[6] = (p3 + p3 + p2 + 2 * p1 + p0 + q0 + q1 + 4) >> 3;
+        a[7] = (p3 + p2 + p1 + 2 * p0 + q0 + q1 + q2 + 4) >> 3;
+        a[8] = (p2 + p1 + p0 + 2 * q0 + q1 + q2 + q3 + 4) >> 3;
+        a[9] = (p1 + p0 + q0 + 2 * q1 + q2 + q3 + q3 + 4) >> 3;
+        a[10] = (p0 + q0 + q1 + 2 * q2 + q3 + q3 + q3 + 4) >> 3;
+        return 3;
+    }
+    if (wd == 6 && flat8in) {
+        a[6] = (p2 + 2 * p2 + 2 * p1 + 2 * p0 + q0 + 4) >> 3;
+        a[7] = (p2 + 2 * p1 + 2 * p0 + 2 * q0 + q1 + 4) >> 3;
+        a[8] = (p1 + 2 * p0 + 2 * q0 + 2 * q1 + q2 + 4) >> 3;
+        a[9] = (p0 + 2 * q0 + 2 * q1 + 2 * q2 + q2 + 4) >> 3;
+        return 2;
+    }
+    const bool hev = iabs(p1 - p0) > H || iabs(q1 - q0) > H;
+    if (hev) {
+        int f = iclip(p1 - q1, dmin, dmax);
+        f = iclip(3 * (q0 - p0) + f, dmin, dmax);
+        const int f1 = imin(f + 4, dmax) >> 3, f2 = imin(f + 3, dmax) >> 3;
+        a[7] = iclip(p0 + f2, 0, bitdepth_max);
+        a[8] = iclip(q0 - f1, 0, bitdepth_max);
+        return 1;
+    }
+    int f = iclip(3 * (q0 - p0), dmin, dmax);
+    const int f1 = imin(f + 4, dmax) >> 3, f2 = imin(f + 3, dmax) >> 3;
+    a[7] = iclip(p0 + f2, 0, bitdepth_max);
+    a[8] = iclip(q0 - f1, 0, bitdepth_max);
+    f = (f1 + 1) >> 1;
+    a[6] = iclip(p1 + f, 0, bitdepth_max);
+    a[9] = iclip(q1 - f, 0, bitdepth_max);
+    return 2;
+}
+
+// One line of a column edge (the samples lie along the row): the 8 or 16 samples around the edge come in as aligned
+// vector loads (the edge position is a multiple of 4 samples) and go back as vector stores that cover only this edge's
+// own half blocks — [x-2, x+2) for the 4- and 6-tap filters, [x-4, x+4) for the 8-tap, [x-8, x+8) for the 16-tap — which
+// no other edge of the pass writes. The per-sample version issued 8-16 loads and up to 12 stores per line and stalled
+// on the load/store queue (ncu at 3840x2160: lg_throttle 47 per issue).
+// HALF samples on each side of e into a[8 - HALF .. 8 + HALF) / back from there; all indices are compile-time
+template <typename pixel, int HALF>
+EAV1_DEV void lf_row_load(const pixel *e, int *a)
+{
+#pragma unroll
+    for (int q = 0; q < HALF / 2; q++) {
+        if (sizeof(pixel) == 1) {
+            const uint32_t v = reinterpret_cast<const uint32_t *>(e - HALF)[q];
+#pragma unroll
+            for (int b = 0; b < 4; b++) a[8 - HALF + 4 * q + b] = (int)((v >> (8 * b)) & 0xff);
+        } else {
+            const uint2 v = reinterpret_cast<const uint2 *>(e - HALF)[q];
+            a[8 - HALF + 4 * q] = (int)(v.x & 0xffff); a[8 - HALF + 4 * q + 1] = (int)(v.x >> 16);
+            a[8 - HALF + 4 * q + 2] = (int)(v.y & 0xffff); a[8 - HALF + 4 * q + 3] = (int)(v.y >> 16);
+        }
+    }
+}
+template <typename pixel, int HALF>
+EAV1_DEV void lf_row_store(pixel *e, const int *a)
+{
+#pragma unroll
+    for (int q = 0; q < HALF / 2; q++) {
+        const int *s = &a[8 - HALF + 4 * q];
+        if (sizeof(pixel) == 1)
+            reinterpret_cast<uint32_t *>(e - HALF)[q] = (uint32_t)s[0] | ((uint32_t)s[1] << 8) | ((uint32_t)s[2] << 16) | ((uint32_t)s[3] << 24);
+        else {
+            uint2 v; v.x = (uint32_t)s[0] | ((uint32_t)s[1] << 16); v.y = (uint32_t)s[2] | ((uint32_t)s[3] << 16);
+            reinterpret_cast<uint2 *>(e - HALF)[q] = v;
+        }
+    }
+}
+
+template <typename pixel>
+EAV1_DEV void lf_line_h(pixel *e, int E, int I, int H, int wd, int bitdepth_max)
+{
+    int a[16];
+    if (wd >= 16) lf_row_load<pixel, 8>(e, a); else lf_row_load<pixel, 4>(e, a);
+    const int n = lf_core(a, E, I, H, wd, bitdepth_max);
+    if (!n) return;
+    if (n <= 2) {   // p1 p0 | q0 q1: two 2-sample stores
+        if (sizeof(pixel) == 1) {
+            *reinterpret_cast<uint16_t *>(e - 2) = (uint16_t)(a[6] | (a[7] << 8));
+            *reinterpret_cast<uint16_t *>(e) = (uint16_t)(a[8] | (a[9] << 8));
+        } else {
+            *reinterpret_cast<uint32_t *>(e - 2) = (uint32_t)a[6] | ((uint32_t)a[7] << 16);
+            *reinterpret_cast<uint32_t *>(e) = (uint32_t)a[8] | ((uint32_t)a[9] << 16);
+        }
+        return;
+    }
+    if (n == 6) lf_row_store<pixel, 8>(e, a); else lf_row_store<pixel, 4>(e, a);
+}
+
 // One 4-sample edge unit `u` (0..31) of one recorded loop_filter_sb call.
 template <typename pixel>
 EAV1_DEV void lf_unit(const PfParams &pp, const Eav1LfRec &r, int u, int line0 = 0, int line1 = 4)
@@ -136,7 +266,8 @@ EAV1_DEV void lf_unit(const PfParams &pp, const Eav1LfRec &r, int u, int line0 =
     else wd = 4 + 2 * ((r.vmask[1] & bit) ? 1 : 0);
     if (r.dir == 0) {
         pixel *dst = px_at<pixel>(pl, r.x, r.y + 4 * u);
-        lf_edge4<pixel>(dst, E, I, H, stride, 1, wd, pp.bitdepth_max, line0, line1);
+        if (r.x >= 8) for (int i = line0; i < line1; i++) lf_line_h<pixel>(dst + stride * i, E, I, H, wd, pp.bitdepth_max);
+        else lf_edge4<pixel>(dst, E, I, H, stride, 1, wd, pp.bitdepth_max, line0, line1);
     } else {
         pixel *dst = px_at<pixel>(pl, r.x + 4 * u, r.y);
         lf_edge4<pixel>(dst, E, I, H, 1, stride, wd, pp.bitdepth_max, line0, line1);

@@ -534,6 +534,7 @@ struct Eav1cuCtx {
     cudaStream_t stream2 = nullptr;            // phase 1b (residuals) runs beside phase 1 (motion compensation)
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     cudaEvent_t ev_fg_ready = nullptr, ev_fg_free = nullptr;   // film grain: templates built on stream2, applied on the main stream
+    cudaStream_t stream_fg = nullptr;   // film-grain template builds (eav1cu_apply_grain)
     bool fg_busy = false;
     // optional per-stage device timing (bench.py's roofline leg)
     bool stage_timing = false;
@@ -710,6 +711,7 @@ static void ctx_free(Eav1cuCtx *ctx)
     if (ctx->stream2) cudaStreamDestroy(ctx->stream2);
     if (ctx->ev_fork) cudaEventDestroy(ctx->ev_fork);
     if (ctx->ev_join) cudaEventDestroy(ctx->ev_join);
+    if (ctx->stream_fg) cudaStreamDestroy(ctx->stream_fg);
     if (ctx->ev_fg_ready) cudaEventDestroy(ctx->ev_fg_ready);
     if (ctx->ev_fg_free) cudaEventDestroy(ctx->ev_fg_free);
     delete ctx;
@@ -1848,13 +1850,16 @@ int eav1cu_apply_grain(Eav1cuCtx *ctx, int src_pic, int dst_pic, const Eav1Grain
     // The templates, LUTs and offsets depend on the parameters only (one CTA, ~0.1 ms of dependent steps): they are
     // built on the second stream while the kernels of the frame itself still run on the main one; the apply kernel
     // waits for them, and the next call's build waits until this apply has finished with the shared scratch.
+    // A stream of its own, not the one the residual kernels use: there the 0.2 ms template build of frame N sat in
+    // front of the residuals of frame N+1 and, through them, in front of its reconstruction.
     const bool side = ctx->stream2 && !ctx->serial_phase1 && !ctx->stage_timing;
     if (side && !ctx->ev_fg_ready) {
-        if (cudaEventCreateWithFlags(&ctx->ev_fg_ready, cudaEventDisableTiming) != cudaSuccess ||
+        if (cudaStreamCreateWithFlags(&ctx->stream_fg, cudaStreamNonBlocking) != cudaSuccess ||
+            cudaEventCreateWithFlags(&ctx->ev_fg_ready, cudaEventDisableTiming) != cudaSuccess ||
             cudaEventCreateWithFlags(&ctx->ev_fg_free, cudaEventDisableTiming) != cudaSuccess)
-            return fail(ctx, EAV1CU_ERR_CUDA, "film grain events");
+            return fail(ctx, EAV1CU_ERR_CUDA, "film grain stream / events");
     }
-    cudaStream_t ps = side ? ctx->stream2 : ctx->stream;
+    cudaStream_t ps = side ? ctx->stream_fg : ctx->stream;
     if (side && ctx->fg_busy) CK(cudaStreamWaitEvent(ps, ctx->ev_fg_free, 0));
     fg_prepare_kernel<<<1, 256, 0, ps>>>(P);
     if (side) { CK(cudaEventRecord(ctx->ev_fg_ready, ps)); CK(cudaStreamWaitEvent(ctx->stream, ctx->ev_fg_ready, 0)); }

@@ -61,10 +61,18 @@ struct CallTimer {
 };
 #define TCK(idx, call) do { CallTimer ct_(idx); CK(call); } while (0)
 
-// Host threads that wait for a frame (dav1d_get_picture -> eav1cu_fence_wait) sleep instead of spinning inside the
-// driver: with many decoders per process the spinning waiters slow every CUDA call of the submitting threads down.
-// EAV1_SPIN_WAIT=1 restores the default (lowest wake-up latency, single stream).
-static const unsigned g_event_flags = cudaEventDisableTiming | (getenv("EAV1_SPIN_WAIT") ? 0 : cudaEventBlockingSync);
+// How host threads wait for a frame (dav1d_get_picture -> eav1cu_fence_wait, and the wait for a staging slot).
+// A lone decoder spins inside the driver: waking a sleeping thread costs tens of microseconds per frame, which is a
+// quarter of the time of a 360p frame in easyAV1's one-picture-per-call loop (1,730 -> 2,200 frames/s) and 7 % at
+// 1080p. With many decoders per process the waiters must sleep (cudaEventBlockingSync): spinning waiters slow every
+// CUDA call of the submitting threads down. The mode is chosen when a context is created or taken from the cache,
+// by the number of live contexts; EAV1_SPIN_WAIT=1 / 0 forces spinning / sleeping.
+static std::atomic<int> g_live_ctx{0};
+static bool want_spin(int live_including_this)
+{
+    if (const char *e = getenv("EAV1_SPIN_WAIT")) return atoi(e) != 0;
+    return live_including_this <= 1;
+}
 
 struct SubmitMutex {      // EAV1_NO_SUBMIT_LOCK=1 turns it off (A/B measurements)
     std::mutex m;
@@ -535,6 +543,7 @@ struct Eav1cuCtx {
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     cudaEvent_t ev_fg_ready = nullptr, ev_fg_free = nullptr;   // film grain: templates built on stream2, applied on the main stream
     cudaStream_t stream_fg = nullptr;   // film-grain template builds (eav1cu_apply_grain)
+    unsigned event_flags = cudaEventDisableTiming | cudaEventBlockingSync;   // of the events host threads wait on
     bool fg_busy = false;
     // optional per-stage device timing (bench.py's roofline leg)
     bool stage_timing = false;
@@ -626,6 +635,16 @@ static std::mutex g_cache_mu;
 static std::vector<Eav1cuCtx *> g_cache;
 static const size_t MAX_CACHED_CTX = 96;   // a 64-stream server re-opening its decoders finds all of them (bench config C5)
 
+// Called with the context idle (fresh or from the cache): events of the other kind are dropped and made again on demand.
+static void ctx_set_wait_mode(Eav1cuCtx *ctx, bool spin)
+{
+    const unsigned flags = cudaEventDisableTiming | (spin ? 0u : (unsigned)cudaEventBlockingSync);
+    if (flags == ctx->event_flags) return;
+    ctx->event_flags = flags;
+    for (Slot &sl : ctx->slot) if (sl.done) { cudaEventDestroy(sl.done); sl.done = nullptr; sl.used = false; }
+    for (cudaEvent_t &e : ctx->fence_ev) if (e) { cudaEventDestroy(e); e = nullptr; }
+}
+
 int eav1cu_ctx_create(Eav1cuCtx **out, int device)
 {
     if (!out) return EAV1CU_ERR_INVAL;
@@ -638,6 +657,8 @@ int eav1cu_ctx_create(Eav1cuCtx **out, int device)
             if (g_cache[i]->device == device) {
                 *out = g_cache[i];
                 g_cache.erase(g_cache.begin() + i);
+                cudaSetDevice(device);
+                ctx_set_wait_mode(*out, want_spin(++g_live_ctx));
                 return 0;
             }
     }
@@ -676,6 +697,7 @@ int eav1cu_ctx_create(Eav1cuCtx **out, int device)
     }
     if (const char *e = getenv("EAV1_DEBUG_CHECK")) ctx->debug_check = atoi(e) ? atoi(e) : 1;
     if (ctx->debug_check == 2) { cudaMalloc(&ctx->d_sums, 64 * 2 * 8); cudaMemset(ctx->d_sums, 0, 64 * 2 * 8); cudaDeviceSynchronize(); }
+    ctx_set_wait_mode(ctx, want_spin(++g_live_ctx));
     *out = ctx;
     return 0;
 }
@@ -720,6 +742,7 @@ static void ctx_free(Eav1cuCtx *ctx)
 void eav1cu_ctx_destroy(Eav1cuCtx *ctx)
 {
     if (!ctx) return;
+    --g_live_ctx;
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
     bool keep = ctx->own_stream && !ctx->err && !getenv("EAV1_NO_CTX_CACHE");
@@ -913,7 +936,7 @@ int eav1cu_fence(Eav1cuCtx *ctx, unsigned long long *ticket)
     std::lock_guard<std::mutex> g(ctx->fence_mu);
     const unsigned long long t = ctx->fence_next++;
     cudaEvent_t &e = ctx->fence_ev[t % Eav1cuCtx::N_FENCE];
-    if (!e) CK(cudaEventCreateWithFlags(&e, g_event_flags));
+    if (!e) CK(cudaEventCreateWithFlags(&e, ctx->event_flags));
     else TCK(TC_EVSYNC_FENCE, cudaEventSynchronize(e));   // the ticket issued N_FENCE fences ago
     {
         std::lock_guard<SubmitMutex> gs(g_submit_mu);
@@ -1518,7 +1541,7 @@ int eav1cu_frame_submit(Eav1cuCtx *ctx, const Eav1FrameDesc *fd,
     CK(cudaSetDevice(ctx->device));
     ctx->cur_slot ^= 1;
     Slot &sl = ctx->S();
-    if (!sl.done) CK(cudaEventCreateWithFlags(&sl.done, g_event_flags));
+    if (!sl.done) CK(cudaEventCreateWithFlags(&sl.done, ctx->event_flags));
     auto t0 = std::chrono::steady_clock::now();
     if (sl.used) TCK(TC_EVSYNC_SLOT, cudaEventSynchronize(sl.done));   // the frame two submits ago has finished with this slot
     auto t1 = std::chrono::steady_clock::now();

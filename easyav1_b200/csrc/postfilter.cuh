@@ -559,7 +559,9 @@ EAV1_DEV void resize_sample(const ResizeParams &rp, const int8_t (*filt)[8], int
 // at the frame top/bottom and left/right the edge sample is replicated.
 
 #define LR_TW 32
+#ifndef LR_SUB_ROWS
 #define LR_SUB_ROWS 32     // a stripe (<= 64 rows) is filtered as two halves by two CTAs: twice the groups in flight
+#endif
 struct alignas(16) LrSmem {
     uint16_t in[(LR_SUB_ROWS + 6) * (LR_TW + 6)];
     union alignas(16) {

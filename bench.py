@@ -14,7 +14,7 @@ CDEF + loop restoration, one stream; one "step" = one pass of the reconstruction
   configs       the other BASELINE.json configs, each with value / e2e / roofline / cpu_baseline / parity:
                 C4 3840x2160 10-bit (+ film grain on every shown frame), C3 Vorbis IMDCT / window / overlap-add,
                 C1 the easyAV1 C99 API on a 640x360 WebM (the reference's own benchmark loop), C5 64 concurrent
-                1080p streams (device-resident replay of S = 1 / 4 / 16 staged streams, end to end with 64).
+                1080p streams (device-resident replay of S = 1 / 4 / 8 / 16 staged streams, end to end with 64).
 N > 1 (torchrun, one process per GPU, gloo for the barrier and the MAX over ranks; nothing is exchanged on the
 data path): the top-level keys are configs[4] (C5): 64 streams dealt round-robin to the ranks
 (easyav1_b200.shard.assign), 64 / N decoders per rank sharing that rank's share of the host cores.
@@ -927,7 +927,7 @@ def run_ours(args):
     # ---- configs[4] (C5) on one GPU: device-resident S-stream replay, 64 streams end to end
     if want("c5"):
         peak, _ = measured_peak()
-        devs = [multi_stream_device(E, host, man, obu, s, max(8, 96 // s), torch, sampler=ClockSampler(local)) for s in (1, 4, 16)]
+        devs = [multi_stream_device(E, host, man, obu, s, max(8, 96 // s), torch, sampler=ClockSampler(local)) for s in (1, 4, 8, 16)]
         devs.append(multi_stream_device(E, host, man, obu, 4, 24, torch, graph=False))
         clk5 = {"gpu_util_mean": max((d.get("gpu_util_mean") or 0) for d in devs)}
         workers = cores + cores // 4

@@ -9,6 +9,7 @@
 #include <atomic>
 #include <chrono>
 #include <mutex>
+#include <thread>
 #include <string>
 #include <vector>
 
@@ -71,7 +72,8 @@ static std::atomic<int> g_live_ctx{0};
 static bool want_spin(int live_including_this)
 {
     if (const char *e = getenv("EAV1_SPIN_WAIT")) return atoi(e) != 0;
-    return live_including_this <= 1;
+    static const unsigned cores = std::thread::hardware_concurrency();
+    return live_including_this <= 1 && cores >= 4;   // a polling waiter needs a core of its own
 }
 
 struct SubmitMutex {      // EAV1_NO_SUBMIT_LOCK=1 turns it off (A/B measurements)

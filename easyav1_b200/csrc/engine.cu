@@ -388,6 +388,19 @@ deblock_kernel(PfParams pp, const Eav1LfRec *__restrict__ recs, int n)
     lf_unit<pixel>(pp, recs[ri], threadIdx.x >> 2, line, line + 1);
 }
 
+// Whole-picture duplicate ahead of CDEF / loop restoration (they write only what they filter). A copy-engine node
+// between two kernels of a stream costs several microseconds of hand-over in either direction; 3 MB that sit in L2
+// take a kernel two.
+__global__ void __launch_bounds__(256)
+picture_copy_kernel(uint4 *__restrict__ dst, uint4 *__restrict__ dst2, const uint4 *__restrict__ src, size_t n16)
+{
+    for (size_t i = (size_t)blockIdx.x * 256 + threadIdx.x; i < n16; i += (size_t)gridDim.x * 256) {
+        const uint4 v = src[i];
+        dst[i] = v;
+        if (dst2) dst2[i] = v;
+    }
+}
+
 template <typename pixel>
 __global__ void __launch_bounds__(256)
 cdef_kernel(PfParams pp)
@@ -1317,6 +1330,23 @@ static int plan_build(Eav1cuCtx *ctx, FramePlan &pl, bool staged, const Eav1Fram
     return up.flush(ctx->S().stage);
 }
 
+// device-to-device duplicate of a picture on stream st (EAV1_COPY_ENGINE=1: through the copy engine, for A/B runs)
+// dst2 (optional): a second destination of the same size
+static cudaError_t picture_copy(Eav1cuCtx *ctx, void *dst, const void *src, size_t bytes, cudaStream_t st, void *dst2 = nullptr)
+{
+    static const bool engine = getenv("EAV1_COPY_ENGINE") != nullptr;
+    if (engine || (bytes & 15) || ((uintptr_t)dst & 15) || ((uintptr_t)src & 15) || ((uintptr_t)dst2 & 15)) {
+        cudaError_t e = cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToDevice, st);
+        if (e == cudaSuccess && dst2) e = cudaMemcpyAsync(dst2, src, bytes, cudaMemcpyDeviceToDevice, st);
+        return e;
+    }
+    const size_t n16 = bytes / 16;
+    const unsigned grid = (unsigned)std::min<size_t>((n16 + 255) / 256, (size_t)ctx->recon_sms * 8);
+    picture_copy_kernel<<<grid, 256, 0, st>>>(static_cast<uint4 *>(dst), static_cast<uint4 *>(dst2), static_cast<const uint4 *>(src), n16);
+    ctx->n_launches++;
+    return cudaGetLastError();
+}
+
 static int plan_launch(Eav1cuCtx *ctx, FramePlan &pl)
 {
     const Eav1FrameDesc *fd = &pl.fd;
@@ -1480,6 +1510,7 @@ static int plan_launch(Eav1cuCtx *ctx, FramePlan &pl)
         ctx->n_launches++;
     }
     }
+    bool cdef_mirrored = false;
     if (has_cdef) {
         StageTimer tm(ctx, 2);
         Picture &dst = (has_lr || superres) ? ctx->work[1] : cur;
@@ -1488,7 +1519,12 @@ static int plan_launch(Eav1cuCtx *ctx, FramePlan &pl)
         // Most 8x8 blocks of a typical frame are left alone by CDEF (skipped, strength 0, cdef_idx -1): the whole
         // picture is copied by the copy engine first (L2-resident, a few microseconds) and the kernel only writes
         // the blocks it filters; a warp copying its own 96 bytes spent its life waiting for them.
-        TCK(TC_D2D, cudaMemcpyAsync(dst.base, A.base, std::min(dst.bytes, A.bytes), cudaMemcpyDeviceToDevice, st));
+        // With loop restoration next (and no super-resolution in between) the final picture receives the same copy
+        // and the same filtered samples: LR's own whole-picture copy is not needed then.
+        cdef_mirrored = has_lr && !superres && &dst != &cur && cur.bytes == dst.bytes;
+        pp.cdef_mirror = cdef_mirrored;
+        if (cdef_mirrored) for (int i = 0; i < 3; i++) pp.p[i] = cur.pl[i];
+        TCK(TC_D2D, picture_copy(ctx, dst.base, A.base, std::min(dst.bytes, A.bytes), st, cdef_mirrored ? cur.base : nullptr));
         dim3 grid((fd->bw4 / 2 + 8) / 8, (fd->bh4 + 1) / 2);
         if (hbd) cdef_kernel<uint16_t><<<grid, 256, 0, st>>>(pp);
         else     cdef_kernel<uint8_t><<<grid, 256, 0, st>>>(pp);
@@ -1532,7 +1568,7 @@ static int plan_launch(Eav1cuCtx *ctx, FramePlan &pl)
         StageTimer tm(ctx, 3);
         Picture &src = *lr_src, &cur = *lr_out;
         for (int i = 0; i < 3; i++) { pp.b[i] = src.pl[i]; pp.p[i] = cur.pl[i]; }
-        TCK(TC_D2D, cudaMemcpyAsync(cur.base, src.base, std::min(cur.bytes, src.bytes), cudaMemcpyDeviceToDevice, st));
+        if (!cdef_mirrored) TCK(TC_D2D, picture_copy(ctx, cur.base, src.base, std::min(cur.bytes, src.bytes), st));
         dim3 grid(384 / LR_TW, (unsigned)pl.n_lr, 64 / LR_SUB_ROWS);
         if (hbd) lr_kernel<uint16_t><<<grid, 128, 0, st>>>(pp, pl.d_lr);
         else     lr_kernel<uint8_t><<<grid, 128, 0, st>>>(pp, pl.d_lr);

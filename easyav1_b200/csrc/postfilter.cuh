@@ -28,6 +28,8 @@ struct PfParams {
     int sb128w;
     int cdef_damping;
     uint8_t cdef_y[8], cdef_uv[8];
+    int cdef_mirror;         // CDEF stores every filtered sample in p[] as well: loop restoration follows, and its output
+                             // picture then starts as the copy of b[] it needs without a second whole-picture copy
     const Eav1Tables *tab;
 };
 
@@ -412,7 +414,8 @@ EAV1_DEV void cdef_load_group(const Plane *pl, int lx, int ly, int cx, int cy, i
 template <typename pixel>
 EAV1_DEV void cdef_filter(const Eav1Tables *tab, const Plane &out, int x0, int y0, int w, int h, const int16_t *tile,
                           int pri, int sec, int dir, int damping, int bitdepth_max, int tid, int nthr,
-                          const Plane *out2 = nullptr, const int16_t *tile2 = nullptr)
+                          const Plane *out2 = nullptr, const int16_t *tile2 = nullptr,
+                          const Plane *mirror = nullptr, const Plane *mirror2 = nullptr)
 {
     const int bd8 = (32 - clz32((unsigned)bitdepth_max)) - 8;
     const int pri_tap = 4 - ((pri >> bd8) & 1);
@@ -460,6 +463,7 @@ EAV1_DEV void cdef_filter(const Eav1Tables *tab, const Plane &out, int x0, int y
         int v = px + ((sum - (sum < 0) + 8) >> 4);
         if (pri && sec) v = iclip(v, mn, mx);
         *px_at<pixel>(second ? *out2 : out, x0 + x, y0 + y) = (pixel)v;
+        if (mirror) *px_at<pixel>(second ? *mirror2 : *mirror, x0 + x, y0 + y) = (pixel)v;
     }
 }
 
@@ -582,13 +586,14 @@ EAV1_DEV void cdef_block(const PfParams &pp, int bx, int by, bool valid, CdefSme
             do_y = pri || y_sec;
         } else do_y = y_sec != 0;
     }
-    if (do_y) cdef_filter<pixel>(pp.tab, pp.b[0], lx, ly, 8, 8, sm.tile[0], pri, y_sec, ydir, damping, pp.bitdepth_max, tid, nthr);
+    if (do_y) cdef_filter<pixel>(pp.tab, pp.b[0], lx, ly, 8, 8, sm.tile[0], pri, y_sec, ydir, damping, pp.bitdepth_max, tid, nthr,
+                                 nullptr, nullptr, pp.cdef_mirror ? &pp.p[0] : nullptr);
     if (has_chroma) {
         if (active && uv_lvl) {
             const uint8_t uvd422[8] = { 7, 0, 2, 4, 5, 6, 6, 6 };
             const int uvdir = uv_pri ? (pp.layout == 2 ? uvd422[dir] : dir) : 0;
             cdef_filter<pixel>(pp.tab, pp.b[1], cx, cy, cw, chh, sm.tile[1], uv_pri, uv_sec, uvdir, damping - 1, pp.bitdepth_max, tid, nthr,
-                               &pp.b[2], sm.tile[2]);
+                               &pp.b[2], sm.tile[2], pp.cdef_mirror ? &pp.p[1] : nullptr, &pp.p[2]);
         }
     }
 }

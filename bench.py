@@ -399,8 +399,11 @@ class Staged:
         if r:
             raise RuntimeError("replay failed: %d" % r)
 
-    def graph_build(self):
-        r = self.E.eav1cu_staged_graph_build(self.eng)
+    def graph_build(self, grain_pic=None, grain=None):
+        if grain is None:
+            r = self.E.eav1cu_staged_graph_build(self.eng)
+        else:       # film grain applied to every staged frame inside the same graph
+            r = self.E.eav1cu_staged_graph_build_grain(self.eng, grain_pic, C.byref(grain))
         if r:
             raise RuntimeError("graph capture failed: %d" % r)
 
@@ -409,14 +412,15 @@ class Staged:
         if r:
             raise RuntimeError("graph replay failed: %d" % r)
 
-    def last_frame_md5(self):
+    def last_frame_md5(self, pic=None):
+        """MD5 of the planes of the last staged frame's picture (or of picture id `pic` of the same geometry)"""
         si = self.infos[-1]
         w, hh, bps = si.w, si.h, 2 if si.bpc > 8 else 1
         cw, ch = (w + 1) // 2, (hh + 1) // 2
         y = C.create_string_buffer(w * hh * bps); u = C.create_string_buffer(cw * ch * bps); v = C.create_string_buffer(cw * ch * bps)
         data = (C.c_void_p * 3)(C.addressof(y), C.addressof(u), C.addressof(v))
         stride = (C.c_ssize_t * 2)(w * bps, cw * bps)
-        assert self.E.eav1cu_pic_download(self.eng, si.cur, data, stride) == 0
+        assert self.E.eav1cu_pic_download(self.eng, si.cur if pic is None else pic, data, stride) == 0
         return hashlib.md5(y.raw + u.raw + v.raw).hexdigest()
 
     def close(self):
@@ -453,11 +457,11 @@ def device_leg(E, host, man, obu, steps, warmup, torch, grain=None, prof=False):
     use_graph = [False]
 
     def replay_step():
+        if use_graph[0]:
+            st.graph_replay(1)     # all frames of the step (and their film grain) as one CUDA graph, built once outside the timed region
+            return
         if grain is None:
-            if use_graph[0]:
-                st.graph_replay(1)     # all frames of the step as one CUDA graph (built once, outside the timed region)
-            else:
-                st.replay(1)
+            st.replay(1)
             return
         for i in shown:
             r = E.eav1cu_staged_replay(st.eng, i)
@@ -490,13 +494,16 @@ def device_leg(E, host, man, obu, steps, warmup, torch, grain=None, prof=False):
         torch.cuda.synchronize()
         assert st.last_frame_md5() == man["frames"][-1]["md5"], "replayed frames differ from the golden MD5"
         E.eav1cu_set_stage_timing(st.eng, 0)
-        if grain is None and not os.environ.get("EAV1_BENCH_NO_GRAPH"):
-            st.graph_build()
+        if not os.environ.get("EAV1_BENCH_NO_GRAPH"):
+            grained = st.last_frame_md5(gp) if grain is not None else None      # the last frame with grain, direct launches
+            st.graph_build(gp, grain) if grain is not None else st.graph_build()
             use_graph[0] = True
             for _ in range(2):
                 replay_step()
             torch.cuda.synchronize()
             assert st.last_frame_md5() == man["frames"][-1]["md5"], "graph replay differs from the golden MD5"
+            if grain is not None:
+                assert st.last_frame_md5(gp) == grained, "film grain inside the graph differs from the direct launches"
         cnt0 = (C.c_longlong * 4)(); E.eav1cu_counters(st.eng, cnt0)
         dev_ms = timed(steps, prof)
         graph_used = use_graph[0]

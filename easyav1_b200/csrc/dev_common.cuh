@@ -23,7 +23,21 @@
 // group barrier: a work group is either one warp (nthr == 32) or the whole CTA; `nthr` must be in scope
 #define CTA_SYNC() do { if (nthr <= 32) __syncwarp(); else __syncthreads(); } while (0)
 #define EAV1_LDG(p) __ldg(p)
+// Programmatic dependent launch (sm_90+): a kernel launched with the attribute may be scheduled while its predecessor
+// in the stream drains. It may read what the host uploaded (work lists) but must not touch anything a kernel wrote
+// before pdl_wait() returns (a no-op for a kernel launched the ordinary way). Every kernel of the frame pipeline calls
+// it exactly once per thread. c_pdl_early != 0: the kernel then also releases its own successor, whose CTAs move into
+// slots as they fall free and have their prologue behind them when the last CTA of this kernel leaves. Wait before
+// release, always: a successor's prologue then implies that everything before this kernel has completed.
+__constant__ int c_pdl_early;
+static __device__ __forceinline__ void pdl_wait()
+{
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    if (c_pdl_early) asm volatile("griddepcontrol.launch_dependents;" :::);
+}
+#define EAV1_GRID_DEP_WAIT() pdl_wait()
 #else
+#define EAV1_GRID_DEP_WAIT() ((void)0)
 #define EAV1_DEV static inline
 #define EAV1_DEVN static
 #define EAV1_DEVH static inline

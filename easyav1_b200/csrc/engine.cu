@@ -6,6 +6,7 @@
 #include <stdio.h>
 #include <string.h>
 #include <stdlib.h>
+#include <algorithm>
 #include <atomic>
 #include <chrono>
 #include <mutex>
@@ -84,6 +85,41 @@ struct SubmitMutex {      // EAV1_NO_SUBMIT_LOCK=1 turns it off (A/B measurement
 };
 static SubmitMutex g_submit_mu;
 
+// Which launches carry the programmatic-dependency attribute. EAV1_PDL (A/B runs): bit 0 post-filter kernels, bit 1 the
+// dataflow kernel, bit 2 motion compensation, bit 3 early release. Default: all three, and early release while the
+// process has a single decoder (one 1080p stream 13.07 -> 12.16 ms per 120 frames). With several decoders on the GPU
+// early release is off: CTAs parked in pdl_wait() hold the slots the other streams' kernels would run in (8 streams
+// 24.1k -> 18.3k frames/s with it, 23.8k -> 24.1k with the attribute alone).
+static int pdl_mask()
+{
+    static const int m = [] { const char *e = getenv("EAV1_PDL"); return e ? atoi(e) : 7; }();
+    return m;
+}
+static void pdl_set_early(int device, int live, cudaStream_t st)
+{
+    static std::mutex mu;
+    static int cur[64];          // per device: 0 unknown, 1 off, 2 on
+    const char *e = getenv("EAV1_PDL");
+    const int want = e ? ((atoi(e) & 8) != 0) : live <= 1;
+    std::lock_guard<std::mutex> g(mu);
+    if (device < 0 || device >= 64 || cur[device] == want + 1) return;
+    if (cudaMemcpyToSymbolAsync(c_pdl_early, &want, sizeof(want), 0, cudaMemcpyHostToDevice, st) == cudaSuccess &&
+        cudaStreamSynchronize(st) == cudaSuccess)
+        cur[device] = want + 1;
+}
+template <typename... KArgs, typename... Args>
+static cudaError_t launch_k(void (*kernel)(KArgs...), dim3 grid, dim3 block, cudaStream_t st, bool pdl, Args &&...args)
+{
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = pdl ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
 // ------------------------------------------------------------------ kernels
 
 // One launch reconstructs a whole frame. CTAs draw chain tickets in decode order (which is a
@@ -149,6 +185,8 @@ __device__ __forceinline__ void recon_worker(const FrameCtx &fc, const ReconArgs
                                              int tid, int nthr)
 {
     uint32_t next = 0;
+    bool dep_waited = false;    // pdl_wait() once, before the first command touches pixels: tickets, unit records and
+                                // commands are this launch's own (or uploaded) state
     if (tid == 0) next = atomicAdd(counter, 1u);
     for (;;) {
         if (tid == 0) ws.ticket = next;
@@ -188,6 +226,7 @@ __device__ __forceinline__ void recon_worker(const FrameCtx &fc, const ReconArgs
             }
             ra.trace[EAV1_TRACE_WORDS * (size_t)id + 3] = who;
         }
+        if (!dep_waited) { pdl_wait(); dep_waited = true; }
         long long cyc_stage = 0, cyc_op[3] = { 0, 0, 0 }, n_op[3] = { 0, 0, 0 };
         for (uint32_t base = 0; base < count; base += EAV1_CMD_STAGE) {
             const uint32_t n = min(count - base, (uint32_t)EAV1_CMD_STAGE);
@@ -275,6 +314,7 @@ template <typename BD>
 __global__ void __launch_bounds__(128, EAV1_RECON_MIN_CTAS)
 flat_units_kernel(FrameCtx fc, const Eav1Cmd *__restrict__ cmds, const uint2 *__restrict__ units, uint32_t n_big, uint32_t n_small)
 {
+    pdl_wait();
     __shared__ alignas(16) unsigned char scratch[4 * EAV1_WARP_SCRATCH > sizeof(CtaScratch) ? 4 * EAV1_WARP_SCRATCH : sizeof(CtaScratch)];
     __shared__ Eav1Cmd cmd[4][2];
     int tid, nthr, w;
@@ -315,6 +355,7 @@ mc_kernel(FrameCtx fc, const Eav1Cmd *__restrict__ cmds, const uint32_t *__restr
     if (lane < (int)(sizeof(Eav1Cmd) / 4))
         reinterpret_cast<uint32_t *>(&cmd[w])[lane] = reinterpret_cast<const uint32_t *>(&cmds[ci])[lane];
     __syncwarp();
+    pdl_wait();     // the work lists above were uploaded by the host; pixels are touched from here on
     const Eav1Cmd &c = cmd[w];
     CtaScratch &sm = *reinterpret_cast<CtaScratch *>(scratch + w * EAV1_WARP_SCRATCH);
     if (c.op == EAV1_OP_MC) {
@@ -381,6 +422,7 @@ template <typename pixel>
 __global__ void __launch_bounds__(128)
 deblock_kernel(PfParams pp, const Eav1LfRec *__restrict__ recs, int n)
 {
+    pdl_wait();
     // one thread per line of a 4-sample edge unit: 128 threads = the 32 units of one recorded call
     const int ri = blockIdx.x;
     if (ri >= n) return;
@@ -394,6 +436,7 @@ deblock_kernel(PfParams pp, const Eav1LfRec *__restrict__ recs, int n)
 __global__ void __launch_bounds__(256)
 picture_copy_kernel(uint4 *__restrict__ dst, uint4 *__restrict__ dst2, const uint4 *__restrict__ src, size_t n16)
 {
+    pdl_wait();
     for (size_t i = (size_t)blockIdx.x * 256 + threadIdx.x; i < n16; i += (size_t)gridDim.x * 256) {
         const uint4 v = src[i];
         dst[i] = v;
@@ -420,6 +463,7 @@ lr_kernel(PfParams pp, const Eav1LrRec *__restrict__ recs)
     if (threadIdx.x < sizeof(Eav1LrRec) / 4)
         reinterpret_cast<uint32_t *>(&r)[threadIdx.x] = reinterpret_cast<const uint32_t *>(&recs[blockIdx.y])[threadIdx.x];
     __syncthreads();
+    pdl_wait();
     lr_tile<pixel>(pp, r, blockIdx.x, blockIdx.z, sm, threadIdx.x, blockDim.x);
 }
 
@@ -675,7 +719,9 @@ int eav1cu_ctx_create(Eav1cuCtx **out, int device)
                 *out = g_cache[i];
                 g_cache.erase(g_cache.begin() + i);
                 cudaSetDevice(device);
-                ctx_set_wait_mode(*out, want_spin(++g_live_ctx));
+                const int live = ++g_live_ctx;
+                ctx_set_wait_mode(*out, want_spin(live));
+                pdl_set_early(device, live, (*out)->stream);
                 return 0;
             }
     }
@@ -716,7 +762,9 @@ int eav1cu_ctx_create(Eav1cuCtx **out, int device)
     }
     if (const char *e = getenv("EAV1_DEBUG_CHECK")) ctx->debug_check = atoi(e) ? atoi(e) : 1;
     if (ctx->debug_check == 2) { cudaMalloc(&ctx->d_sums, 64 * 2 * 8); cudaMemset(ctx->d_sums, 0, 64 * 2 * 8); cudaDeviceSynchronize(); }
-    ctx_set_wait_mode(ctx, want_spin(++g_live_ctx));
+    const int live = ++g_live_ctx;
+    ctx_set_wait_mode(ctx, want_spin(live));
+    pdl_set_early(device, live, ctx->stream);
     *out = ctx;
     return 0;
 }
@@ -761,9 +809,10 @@ static void ctx_free(Eav1cuCtx *ctx)
 void eav1cu_ctx_destroy(Eav1cuCtx *ctx)
 {
     if (!ctx) return;
-    --g_live_ctx;
+    const int live = --g_live_ctx;
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
+    pdl_set_early(ctx->device, live, ctx->stream);
     bool keep = ctx->own_stream && !ctx->err && !getenv("EAV1_NO_CTX_CACHE");
     if (keep) {
         // back to a just-created state, keeping every allocation
@@ -1342,9 +1391,8 @@ static cudaError_t picture_copy(Eav1cuCtx *ctx, void *dst, const void *src, size
     }
     const size_t n16 = bytes / 16;
     const unsigned grid = (unsigned)std::min<size_t>((n16 + 255) / 256, (size_t)ctx->recon_sms * 8);
-    picture_copy_kernel<<<grid, 256, 0, st>>>(static_cast<uint4 *>(dst), static_cast<uint4 *>(dst2), static_cast<const uint4 *>(src), n16);
     ctx->n_launches++;
-    return cudaGetLastError();
+    return launch_k(picture_copy_kernel, dim3(grid), dim3(256), st, (pdl_mask() & 1) != 0, static_cast<uint4 *>(dst), static_cast<uint4 *>(dst2), static_cast<const uint4 *>(src), n16);
 }
 
 static int plan_launch(Eav1cuCtx *ctx, FramePlan &pl)
@@ -1397,8 +1445,9 @@ static int plan_launch(Eav1cuCtx *ctx, FramePlan &pl)
     if (pl.n_items) {
         StageTimer tm(ctx, 4);
         const unsigned grid = (pl.n_items + 3) / 4;
-        if (hbd) mc_kernel<BD16><<<grid, 128, 0, st>>>(fc, pl.d_cmds, pl.d_items, pl.n_items);
-        else     mc_kernel<BD8><<<grid, 128, 0, st>>>(fc, pl.d_cmds, pl.d_items, pl.n_items);
+        const bool pdl = (pdl_mask() & 4) != 0;
+        if (hbd) CK(launch_k(mc_kernel<BD16>, dim3(grid), dim3(128), st, pdl, fc, pl.d_cmds, pl.d_items, pl.n_items));
+        else     CK(launch_k(mc_kernel<BD8>, dim3(grid), dim3(128), st, pdl, fc, pl.d_cmds, pl.d_items, pl.n_items));
         ctx->n_launches++;
     }
     if (fork) TCK(TC_WAITEV, cudaStreamWaitEvent(st, ctx->ev_join, 0));
@@ -1474,8 +1523,9 @@ static int plan_launch(Eav1cuCtx *ctx, FramePlan &pl)
             CK(cudaMemset(ctx->d_ctrl + 4, 0, 4));
             CK(cudaDeviceSynchronize());
         }
-        if (hbd) recon_frame_kernel<BD16><<<grid, 128, 0, st>>>(fc, ra);
-        else     recon_frame_kernel<BD8><<<grid, 128, 0, st>>>(fc, ra);
+        const bool pdl = (pdl_mask() & 2) != 0;
+        if (hbd) CK(launch_k(recon_frame_kernel<BD16>, dim3(grid), dim3(128), st, pdl, fc, ra));
+        else     CK(launch_k(recon_frame_kernel<BD8>, dim3(grid), dim3(128), st, pdl, fc, ra));
         ctx->n_launches++;
         if (ctx->debug_check == 1) {
             uint32_t c[8];
@@ -1505,8 +1555,9 @@ static int plan_launch(Eav1cuCtx *ctx, FramePlan &pl)
         const size_t off = pass ? pl.n_lf0 : 0, cnt = pass ? pl.n_lf1 : pl.n_lf0;
         if (!cnt) continue;
         const unsigned grid = (unsigned)cnt;
-        if (hbd) deblock_kernel<uint16_t><<<grid, 128, 0, st>>>(pp, pl.d_lf + off, (int)cnt);
-        else     deblock_kernel<uint8_t><<<grid, 128, 0, st>>>(pp, pl.d_lf + off, (int)cnt);
+        const bool pdl = (pdl_mask() & 1) != 0;
+        if (hbd) CK(launch_k(deblock_kernel<uint16_t>, dim3(grid), dim3(128), st, pdl, pp, pl.d_lf + off, (int)cnt));
+        else     CK(launch_k(deblock_kernel<uint8_t>, dim3(grid), dim3(128), st, pdl, pp, pl.d_lf + off, (int)cnt));
         ctx->n_launches++;
     }
     }
@@ -1526,8 +1577,9 @@ static int plan_launch(Eav1cuCtx *ctx, FramePlan &pl)
         if (cdef_mirrored) for (int i = 0; i < 3; i++) pp.p[i] = cur.pl[i];
         TCK(TC_D2D, picture_copy(ctx, dst.base, A.base, std::min(dst.bytes, A.bytes), st, cdef_mirrored ? cur.base : nullptr));
         dim3 grid((fd->bw4 / 2 + 8) / 8, (fd->bh4 + 1) / 2);
-        if (hbd) cdef_kernel<uint16_t><<<grid, 256, 0, st>>>(pp);
-        else     cdef_kernel<uint8_t><<<grid, 256, 0, st>>>(pp);
+        const bool pdl = (pdl_mask() & 1) != 0;
+        if (hbd) CK(launch_k(cdef_kernel<uint16_t>, grid, dim3(256), st, pdl, pp));
+        else     CK(launch_k(cdef_kernel<uint8_t>, grid, dim3(256), st, pdl, pp));
         ctx->n_launches++;
     }
     Picture *lr_src = has_cdef ? &ctx->work[1] : &A, *lr_out = &cur;
@@ -1570,8 +1622,9 @@ static int plan_launch(Eav1cuCtx *ctx, FramePlan &pl)
         for (int i = 0; i < 3; i++) { pp.b[i] = src.pl[i]; pp.p[i] = cur.pl[i]; }
         if (!cdef_mirrored) TCK(TC_D2D, picture_copy(ctx, cur.base, src.base, std::min(cur.bytes, src.bytes), st));
         dim3 grid(384 / LR_TW, (unsigned)pl.n_lr, 64 / LR_SUB_ROWS);
-        if (hbd) lr_kernel<uint16_t><<<grid, 128, 0, st>>>(pp, pl.d_lr);
-        else     lr_kernel<uint8_t><<<grid, 128, 0, st>>>(pp, pl.d_lr);
+        const bool pdl = (pdl_mask() & 1) != 0;
+        if (hbd) CK(launch_k(lr_kernel<uint16_t>, grid, dim3(128), st, pdl, pp, pl.d_lr));
+        else     CK(launch_k(lr_kernel<uint8_t>, grid, dim3(128), st, pdl, pp, pl.d_lr));
         ctx->n_launches++;
     }
     CK(cudaGetLastError());
@@ -1780,11 +1833,26 @@ int eav1cu_staged_replay_all(Eav1cuCtx *ctx, int passes)
  * kernel's done flags carry launch epochs that are baked into the captured arguments, so the graph starts by clearing
  * this context's flags (an epoch can then never be met again from an earlier replay). Launch-bound replays (several
  * staged streams sharing the GPU) then run at the device's pace instead of the host's. */
-int eav1cu_staged_graph_build(Eav1cuCtx *ctx)
+struct FgLaunch;
+static int fg_fill(Eav1cuCtx *ctx, int src_pic, int dst_pic, const Eav1GrainParams *g, FgLaunch &L);
+static int fg_side_stream(Eav1cuCtx *ctx);
+static cudaError_t fg_launch_prepare(const FgLaunch &L, cudaStream_t st);
+static cudaError_t fg_launch_apply(const FgLaunch &L, cudaStream_t st);
+static FgLaunch *fg_launch_new();
+static void fg_launch_delete(FgLaunch *);
+
+int eav1cu_staged_graph_build_grain(Eav1cuCtx *ctx, int grain_dst_pic, const Eav1GrainParams *grain)
 {
     if (!ctx || ctx->staged.empty()) return EAV1CU_ERR_INVAL;
     if (ctx->err) return ctx->err;
     CK(cudaSetDevice(ctx->device));
+    if (grain) {        // everything the grain launches need must exist before the capture begins
+        FgLaunch *probe = fg_launch_new();
+        int r = fg_fill(ctx, ctx->staged[0]->fd.cur, grain_dst_pic, grain, *probe);
+        fg_launch_delete(probe);
+        if (!r) r = fg_side_stream(ctx);
+        if (r) return r;
+    }
     CK(cudaStreamSynchronize(ctx->stream));
     if (ctx->staged_exec) { cudaGraphExecDestroy(ctx->staged_exec); ctx->staged_exec = nullptr; }
     if (ctx->staged_graph) { cudaGraphDestroy(ctx->staged_graph); ctx->staged_graph = nullptr; }
@@ -1795,10 +1863,39 @@ int eav1cu_staged_graph_build(Eav1cuCtx *ctx)
     int r = 0;
     const long long n0 = ctx->n_launches;
     if (ctx->d_done && cudaMemsetAsync(ctx->d_done, 0, ctx->done_cap * 4, ctx->stream) != cudaSuccess) r = EAV1CU_ERR_CUDA;
+    FgLaunch *fg = grain ? fg_launch_new() : nullptr;
+    // Film grain of every frame runs on a stream of its own, template build and application both: the application
+    // only reads the finished frame, so the next frame's kernels need not queue behind it. The grain stream joins the
+    // capture here, waits for each frame's last kernel before that frame's application, and is joined at the end. The
+    // main stream waits for it only before a frame that reuses the picture of an application still outstanding.
+    std::vector<int> fg_reading;
+    if (grain && (cudaEventRecord(ctx->ev_fg_free, ctx->stream) != cudaSuccess ||
+                  cudaStreamWaitEvent(ctx->stream_fg, ctx->ev_fg_free, 0) != cudaSuccess)) r = EAV1CU_ERR_CUDA;
     for (FramePlan *pl : ctx->staged) {
         if (r) break;
+        if (grain) {
+            r = fg_fill(ctx, pl->fd.cur, grain_dst_pic, grain, *fg);
+            if (r) break;
+            if (std::find(fg_reading.begin(), fg_reading.end(), pl->fd.cur) != fg_reading.end() ||
+                (pl->fd.sr_pic >= 0 && std::find(fg_reading.begin(), fg_reading.end(), pl->fd.sr_pic) != fg_reading.end())) {
+                if (cudaEventRecord(ctx->ev_fg_ready, ctx->stream_fg) != cudaSuccess ||
+                    cudaStreamWaitEvent(ctx->stream, ctx->ev_fg_ready, 0) != cudaSuccess) { r = EAV1CU_ERR_CUDA; break; }
+                fg_reading.clear();
+            }
+            if (fg_launch_prepare(*fg, ctx->stream_fg) != cudaSuccess) { r = EAV1CU_ERR_CUDA; break; }
+        }
         r = plan_launch(ctx, *pl);
+        if (grain && !r) {
+            if (cudaEventRecord(ctx->ev_fg_free, ctx->stream) != cudaSuccess ||
+                cudaStreamWaitEvent(ctx->stream_fg, ctx->ev_fg_free, 0) != cudaSuccess ||
+                fg_launch_apply(*fg, ctx->stream_fg) != cudaSuccess) r = EAV1CU_ERR_CUDA;
+            fg_reading.push_back(pl->fd.cur);
+            ctx->n_launches += 2;
+        }
     }
+    if (grain && !r && (cudaEventRecord(ctx->ev_fg_ready, ctx->stream_fg) != cudaSuccess ||
+                        cudaStreamWaitEvent(ctx->stream, ctx->ev_fg_ready, 0) != cudaSuccess)) r = EAV1CU_ERR_CUDA;
+    if (fg) fg_launch_delete(fg);
     ctx->staged_graph_kernels = ctx->n_launches - n0;   // kernel nodes of the graph
     ctx->n_launches = n0;                               // capturing launched nothing
     cudaGraph_t graph = nullptr;
@@ -1813,6 +1910,8 @@ int eav1cu_staged_graph_build(Eav1cuCtx *ctx)
     CK(cudaGraphInstantiate(&ctx->staged_exec, graph, 0));
     return 0;
 }
+
+int eav1cu_staged_graph_build(Eav1cuCtx *ctx) { return eav1cu_staged_graph_build_grain(ctx, -1, nullptr); }
 
 int eav1cu_staged_graph_launch(Eav1cuCtx *ctx, int passes)
 {
@@ -1888,10 +1987,15 @@ int eav1cu_staged_info(Eav1cuCtx *ctx, int idx, Eav1StagedInfo *out)
 
 enum { FG_GRAIN_BYTES = 36864, FG_SCALE_BYTES = 3 * 4096, FG_OFFSET_BYTES = 65536 };
 
-int eav1cu_apply_grain(Eav1cuCtx *ctx, int src_pic, int dst_pic, const Eav1GrainParams *g)
+} // extern "C" (helpers)
+
+struct FgLaunch { FgParams P; int bpc; dim3 grid; };
+static FgLaunch *fg_launch_new() { return new FgLaunch(); }
+static void fg_launch_delete(FgLaunch *L) { delete L; }
+
+// validation + kernel parameters of one film-grain application (allocates the scratch on first use)
+static int fg_fill(Eav1cuCtx *ctx, int src_pic, int dst_pic, const Eav1GrainParams *g, FgLaunch &L)
 {
-    if (!ctx || !g) return EAV1CU_ERR_INVAL;
-    if (ctx->err) return ctx->err;
     const int np = (int)ctx->pics.size();
     if (src_pic < 0 || src_pic >= np || dst_pic < 0 || dst_pic >= np || src_pic == dst_pic ||
         !ctx->pics[src_pic].base || !ctx->pics[dst_pic].base)
@@ -1906,7 +2010,7 @@ int eav1cu_apply_grain(Eav1cuCtx *ctx, int src_pic, int dst_pic, const Eav1Grain
     coverage_count_grain(src.bpc, g);
     CK(cudaSetDevice(ctx->device));
     if (!ctx->d_fg) CK(cudaMalloc(&ctx->d_fg, FG_GRAIN_BYTES + FG_SCALE_BYTES + FG_OFFSET_BYTES));
-    FgParams P;
+    FgParams &P = L.P;
     memset(&P, 0, sizeof(P));
     P.g = *g;
     for (int i = 0; i < 3; i++) { P.src[i] = src.pl[i]; P.dst[i] = dst.pl[i]; }
@@ -1919,6 +2023,44 @@ int eav1cu_apply_grain(Eav1cuCtx *ctx, int src_pic, int dst_pic, const Eav1Grain
     P.grain = (int16_t *)ctx->d_fg;
     P.scaling = ctx->d_fg + FG_GRAIN_BYTES;
     P.offsets = ctx->d_fg + FG_GRAIN_BYTES + FG_SCALE_BYTES;
+    L.bpc = src.bpc;
+    L.grid = dim3((P.cols + FG_STRIP - 1) / FG_STRIP, P.rows);
+    return 0;
+}
+static int fg_side_stream(Eav1cuCtx *ctx)
+{
+    if (ctx->ev_fg_ready) return 0;
+    // Highest priority: the template build is one CTA of dependent steps beside kernels of thousands of CTAs. At
+    // equal priority its CTA queued behind every pending CTA of the kernels launched before it and the build ran
+    // after the frame instead of beside it.
+    int prio_lo = 0, prio_hi = 0;
+    cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi);
+    if (cudaStreamCreateWithPriority(&ctx->stream_fg, cudaStreamNonBlocking, prio_hi) != cudaSuccess ||
+        cudaEventCreateWithFlags(&ctx->ev_fg_ready, cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&ctx->ev_fg_free, cudaEventDisableTiming) != cudaSuccess)
+        return fail(ctx, EAV1CU_ERR_CUDA, "film grain stream / events");
+    return 0;
+}
+static cudaError_t fg_launch_prepare(const FgLaunch &L, cudaStream_t st)
+{
+    fg_prepare_kernel<<<1, 256, 0, st>>>(L.P);
+    return cudaGetLastError();
+}
+static cudaError_t fg_launch_apply(const FgLaunch &L, cudaStream_t st)
+{
+    if (L.bpc > 8) fg_apply_kernel<uint16_t><<<L.grid, 256, 0, st>>>(L.P);
+    else fg_apply_kernel<uint8_t><<<L.grid, 256, 0, st>>>(L.P);
+    return cudaGetLastError();
+}
+
+extern "C" {
+
+int eav1cu_apply_grain(Eav1cuCtx *ctx, int src_pic, int dst_pic, const Eav1GrainParams *g)
+{
+    if (!ctx || !g) return EAV1CU_ERR_INVAL;
+    if (ctx->err) return ctx->err;
+    FgLaunch L;
+    if (int r = fg_fill(ctx, src_pic, dst_pic, g, L)) return r;
     std::lock_guard<SubmitMutex> gs(g_submit_mu);
     StageTimer tm(ctx, 5);
     // The templates, LUTs and offsets depend on the parameters only (one CTA, ~0.1 ms of dependent steps): they are
@@ -1927,22 +2069,14 @@ int eav1cu_apply_grain(Eav1cuCtx *ctx, int src_pic, int dst_pic, const Eav1Grain
     // A stream of its own, not the one the residual kernels use: there the 0.2 ms template build of frame N sat in
     // front of the residuals of frame N+1 and, through them, in front of its reconstruction.
     const bool side = ctx->stream2 && !ctx->serial_phase1 && !ctx->stage_timing;
-    if (side && !ctx->ev_fg_ready) {
-        if (cudaStreamCreateWithFlags(&ctx->stream_fg, cudaStreamNonBlocking) != cudaSuccess ||
-            cudaEventCreateWithFlags(&ctx->ev_fg_ready, cudaEventDisableTiming) != cudaSuccess ||
-            cudaEventCreateWithFlags(&ctx->ev_fg_free, cudaEventDisableTiming) != cudaSuccess)
-            return fail(ctx, EAV1CU_ERR_CUDA, "film grain stream / events");
-    }
+    if (side) if (int r = fg_side_stream(ctx)) return r;
     cudaStream_t ps = side ? ctx->stream_fg : ctx->stream;
     if (side && ctx->fg_busy) CK(cudaStreamWaitEvent(ps, ctx->ev_fg_free, 0));
-    fg_prepare_kernel<<<1, 256, 0, ps>>>(P);
+    CK(fg_launch_prepare(L, ps));
     if (side) { CK(cudaEventRecord(ctx->ev_fg_ready, ps)); CK(cudaStreamWaitEvent(ctx->stream, ctx->ev_fg_ready, 0)); }
-    const dim3 grid((P.cols + FG_STRIP - 1) / FG_STRIP, P.rows);
-    if (src.bpc > 8) fg_apply_kernel<uint16_t><<<grid, 256, 0, ctx->stream>>>(P);
-    else fg_apply_kernel<uint8_t><<<grid, 256, 0, ctx->stream>>>(P);
+    CK(fg_launch_apply(L, ctx->stream));
     if (side) { CK(cudaEventRecord(ctx->ev_fg_free, ctx->stream)); ctx->fg_busy = true; }
     ctx->n_launches += 2;
-    CK(cudaGetLastError());
     return 0;
 }
 

@@ -99,6 +99,60 @@ EAV1_DEV void fg_draw(FgSmem &sm, const FgParams &P, int first_plane, int n_plan
     CTA_SYNC();
 }
 
+#ifdef __CUDACC__
+// The wavefront below with one thread per row (every row of every plane has a thread of its own), the lag a
+// compile-time constant: the 2*LAG*(LAG+1) coefficients of the thread's plane sit in registers, the tap loops are
+// unrolled, and the taps are summed on four accumulators. A step is then one round of independent shared-memory loads,
+// a short multiply-add tree, one store and the barrier; the generic loop spent ~1200 cycles per step on 24 dependent
+// iterations (constant-bank coefficient fetch, address arithmetic, loop control), 0.33 ms per frame in all.
+template <int LAG>
+EAV1_DEV void fg_ar_rows(FgSmem &sm, const FgParams &P, int first_plane, int n_planes, int W, int H,
+                         int subx, int suby, int tid)
+{
+    const Eav1GrainParams &g = P.g;
+    constexpr int skew = LAG + 1, NC = 2 * LAG * (LAG + 1);
+    const int bd8 = 32 - clz32((unsigned)P.bitdepth_max) - 8;
+    const int gmin = -(128 << bd8), gmax = (128 << bd8) - 1;
+    const int rows = H - 3, colsn = W - 6;
+    const int steps = colsn + (rows - 1) * skew;
+    const bool mine = tid < n_planes * rows;
+    const int p = mine ? tid / rows : 0, yy = mine ? tid - p * rows : 0;
+    const int pl = first_plane + p, y = yy + 3;
+    const int8_t *coeff = pl ? g.ar_coeffs_uv[pl - 1] : g.ar_coeffs_y;
+    int c[NC + 1];
+#pragma unroll
+    for (int k = 0; k < NC; k++) c[k] = coeff[k];
+    c[NC] = pl ? coeff[NC] : 0;      // the luma-coupling coefficient of a chroma plane
+    const bool coupled = pl && g.num_y_points;
+    for (int step = 0; step < steps; step++) {
+        const int xx = step - yy * skew;
+        if (mine && xx >= 0 && xx < colsn) {
+            const int x = xx + 3;
+            int acc[4] = { 0, 0, 0, 0 };
+            int k = 0;
+#pragma unroll
+            for (int dy = -LAG; dy <= 0; dy++)
+#pragma unroll
+                for (int dx = -LAG; dx <= LAG; dx++) {
+                    if (dy == 0 && dx >= 0) continue;
+                    acc[k & 3] += c[k] * sm.buf[pl][y + dy][x + dx];
+                    k++;
+                }
+            int sum = (acc[0] + acc[1]) + (acc[2] + acc[3]);
+            if (coupled) {
+                const int lx = ((x - 3) << subx) + 3, ly = ((y - 3) << suby) + 3;
+                int luma = 0;
+                for (int i = 0; i <= suby; i++)
+                    for (int j = 0; j <= subx; j++) luma += sm.buf[0][ly + i][lx + j];
+                sum += fg_round2(luma, subx + suby) * c[NC];
+            }
+            sm.buf[pl][y][x] = (int16_t)iclip(sm.buf[pl][y][x] + fg_round2(sum, g.ar_coeff_shift), gmin, gmax);
+        }
+        __syncthreads();
+    }
+}
+#endif
+
 // Auto-regressive filter as a wavefront: row y works on column x at step (x-3) + (y-3)*(lag+1),
 // one step after the row above finished column x+lag.
 EAV1_DEV void fg_ar(FgSmem &sm, const FgParams &P, int first_plane, int n_planes, int W, int H,
@@ -110,6 +164,16 @@ EAV1_DEV void fg_ar(FgSmem &sm, const FgParams &P, int first_plane, int n_planes
     const int gmin = -(128 << bd8), gmax = (128 << bd8) - 1;
     const int rows = H - 3, colsn = W - 6;
     const int steps = colsn + (rows - 1) * skew;
+#ifdef __CUDACC__
+    if (n_planes * rows <= nthr) {
+        switch (lag) {
+        case 0: fg_ar_rows<0>(sm, P, first_plane, n_planes, W, H, subx, suby, tid); return;
+        case 1: fg_ar_rows<1>(sm, P, first_plane, n_planes, W, H, subx, suby, tid); return;
+        case 2: fg_ar_rows<2>(sm, P, first_plane, n_planes, W, H, subx, suby, tid); return;
+        default: fg_ar_rows<3>(sm, P, first_plane, n_planes, W, H, subx, suby, tid); return;
+        }
+    }
+#endif
     for (int step = 0; step < steps; step++) {
         for (int r = tid; r < n_planes * rows; r += nthr) {
             const int p = r / rows, yy = r - p * rows;

@@ -543,6 +543,7 @@ EAV1_DEV void cdef_block(const PfParams &pp, int bx, int by, bool valid, CdefSme
     // The output picture starts as a copy of the input (made by the caller before this stage), so only filtered
     // blocks are written. A whole group (one warp, barriers are __syncwarp) with nothing to filter leaves at once.
     if (!active && nthr <= 32) return;
+    EAV1_GRID_DEP_WAIT();       // the decision above used uploaded side data only; pixels from here on
     if (active) {
         for (int i = tid; i < 8 * 16; i += nthr) (&sm.part[0][0])[i] = 0;
 #ifdef __CUDACC__

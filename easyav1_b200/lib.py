@@ -32,6 +32,8 @@ def load_engine():
         E.eav1cu_staged_replay.argtypes = [C.c_void_p, C.c_int]
         E.eav1cu_staged_replay_all.argtypes = [C.c_void_p, C.c_int]
         E.eav1cu_staged_graph_build.argtypes = [C.c_void_p]
+        E.eav1cu_staged_graph_build_grain.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
+        E.eav1cu_staged_graph_build_grain.restype = C.c_int
         E.eav1cu_staged_graph_launch.argtypes = [C.c_void_p, C.c_int]
         E.eav1cu_staged_info.argtypes = [C.c_void_p, C.c_int, C.POINTER(StagedInfo)]
         E.eav1cu_set_stream.argtypes = [C.c_void_p, C.c_void_p]

@@ -399,6 +399,10 @@ typedef struct Eav1GrainParams {
 /* dst = src + grain, both device pictures of the same geometry; stream-ordered after every frame
  * submitted so far. Three launches: grain templates + scaling LUTs + block offsets, then all planes. */
 int  eav1cu_apply_grain(Eav1cuCtx *ctx, int src_pic, int dst_pic, const Eav1GrainParams *g);
+/* eav1cu_staged_graph_build with film grain (parameters g) applied to every staged frame into picture dst_pic inside
+ * the same graph: the template build of a frame forks onto a stream of its own at the start of the frame and the
+ * apply joins after the frame's last kernel, as eav1cu_apply_grain arranges it for direct launches. */
+int  eav1cu_staged_graph_build_grain(Eav1cuCtx *ctx, int dst_pic, const Eav1GrainParams *g);
 
 /* eav1cu_apply_grain_noalloc has NO counterpart in the reference; it was added
  * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight

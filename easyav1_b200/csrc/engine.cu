@@ -211,7 +211,7 @@ __device__ __forceinline__ void recon_worker(const FrameCtx &fc, const ReconArgs
             const uint32_t *flag = &ra.done[ra.deps[d0 + d]];
             unsigned ns = 20;
 #ifndef EAV1_POLL_MAX_NS
-#define EAV1_POLL_MAX_NS 320
+#define EAV1_POLL_MAX_NS 80
 #endif
             while (ld_acquire(flag) != ra.epoch) { if (EAV1_POLL_MAX_NS) { __nanosleep(ns); if (ns < EAV1_POLL_MAX_NS) ns <<= 1; } }
         }

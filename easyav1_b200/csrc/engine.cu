@@ -603,6 +603,8 @@ struct Eav1cuCtx {
     cudaStream_t stream2 = nullptr;            // phase 1b (residuals) runs beside phase 1 (motion compensation)
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     cudaEvent_t ev_fg_ready = nullptr, ev_fg_free = nullptr;   // film grain: templates built on stream2, applied on the main stream
+    cudaEvent_t ev_fg_cap[2] = { nullptr, nullptr };          // the same two roles inside a stream capture: an event last
+                                                               // recorded in a capture cannot be waited for outside it
     cudaStream_t stream_fg = nullptr;   // film-grain template builds (eav1cu_apply_grain)
     unsigned event_flags = cudaEventDisableTiming | cudaEventBlockingSync;   // of the events host threads wait on
     bool fg_busy = false;
@@ -803,6 +805,7 @@ static void ctx_free(Eav1cuCtx *ctx)
     if (ctx->stream_fg) cudaStreamDestroy(ctx->stream_fg);
     if (ctx->ev_fg_ready) cudaEventDestroy(ctx->ev_fg_ready);
     if (ctx->ev_fg_free) cudaEventDestroy(ctx->ev_fg_free);
+    for (cudaEvent_t e : ctx->ev_fg_cap) if (e) cudaEventDestroy(e);
     delete ctx;
 }
 
@@ -1869,8 +1872,8 @@ int eav1cu_staged_graph_build_grain(Eav1cuCtx *ctx, int grain_dst_pic, const Eav
     // capture here, waits for each frame's last kernel before that frame's application, and is joined at the end. The
     // main stream waits for it only before a frame that reuses the picture of an application still outstanding.
     std::vector<int> fg_reading;
-    if (grain && (cudaEventRecord(ctx->ev_fg_free, ctx->stream) != cudaSuccess ||
-                  cudaStreamWaitEvent(ctx->stream_fg, ctx->ev_fg_free, 0) != cudaSuccess)) r = EAV1CU_ERR_CUDA;
+    if (grain && (cudaEventRecord(ctx->ev_fg_cap[0], ctx->stream) != cudaSuccess ||
+                  cudaStreamWaitEvent(ctx->stream_fg, ctx->ev_fg_cap[0], 0) != cudaSuccess)) r = EAV1CU_ERR_CUDA;
     for (FramePlan *pl : ctx->staged) {
         if (r) break;
         if (grain) {
@@ -1878,23 +1881,23 @@ int eav1cu_staged_graph_build_grain(Eav1cuCtx *ctx, int grain_dst_pic, const Eav
             if (r) break;
             if (std::find(fg_reading.begin(), fg_reading.end(), pl->fd.cur) != fg_reading.end() ||
                 (pl->fd.sr_pic >= 0 && std::find(fg_reading.begin(), fg_reading.end(), pl->fd.sr_pic) != fg_reading.end())) {
-                if (cudaEventRecord(ctx->ev_fg_ready, ctx->stream_fg) != cudaSuccess ||
-                    cudaStreamWaitEvent(ctx->stream, ctx->ev_fg_ready, 0) != cudaSuccess) { r = EAV1CU_ERR_CUDA; break; }
+                if (cudaEventRecord(ctx->ev_fg_cap[1], ctx->stream_fg) != cudaSuccess ||
+                    cudaStreamWaitEvent(ctx->stream, ctx->ev_fg_cap[1], 0) != cudaSuccess) { r = EAV1CU_ERR_CUDA; break; }
                 fg_reading.clear();
             }
             if (fg_launch_prepare(*fg, ctx->stream_fg) != cudaSuccess) { r = EAV1CU_ERR_CUDA; break; }
         }
         r = plan_launch(ctx, *pl);
         if (grain && !r) {
-            if (cudaEventRecord(ctx->ev_fg_free, ctx->stream) != cudaSuccess ||
-                cudaStreamWaitEvent(ctx->stream_fg, ctx->ev_fg_free, 0) != cudaSuccess ||
+            if (cudaEventRecord(ctx->ev_fg_cap[0], ctx->stream) != cudaSuccess ||
+                cudaStreamWaitEvent(ctx->stream_fg, ctx->ev_fg_cap[0], 0) != cudaSuccess ||
                 fg_launch_apply(*fg, ctx->stream_fg) != cudaSuccess) r = EAV1CU_ERR_CUDA;
             fg_reading.push_back(pl->fd.cur);
             ctx->n_launches += 2;
         }
     }
-    if (grain && !r && (cudaEventRecord(ctx->ev_fg_ready, ctx->stream_fg) != cudaSuccess ||
-                        cudaStreamWaitEvent(ctx->stream, ctx->ev_fg_ready, 0) != cudaSuccess)) r = EAV1CU_ERR_CUDA;
+    if (grain && !r && (cudaEventRecord(ctx->ev_fg_cap[1], ctx->stream_fg) != cudaSuccess ||
+                        cudaStreamWaitEvent(ctx->stream, ctx->ev_fg_cap[1], 0) != cudaSuccess)) r = EAV1CU_ERR_CUDA;
     if (fg) fg_launch_delete(fg);
     ctx->staged_graph_kernels = ctx->n_launches - n0;   // kernel nodes of the graph
     ctx->n_launches = n0;                               // capturing launched nothing
@@ -2037,7 +2040,9 @@ static int fg_side_stream(Eav1cuCtx *ctx)
     cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi);
     if (cudaStreamCreateWithPriority(&ctx->stream_fg, cudaStreamNonBlocking, prio_hi) != cudaSuccess ||
         cudaEventCreateWithFlags(&ctx->ev_fg_ready, cudaEventDisableTiming) != cudaSuccess ||
-        cudaEventCreateWithFlags(&ctx->ev_fg_free, cudaEventDisableTiming) != cudaSuccess)
+        cudaEventCreateWithFlags(&ctx->ev_fg_free, cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&ctx->ev_fg_cap[0], cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&ctx->ev_fg_cap[1], cudaEventDisableTiming) != cudaSuccess)
         return fail(ctx, EAV1CU_ERR_CUDA, "film grain stream / events");
     return 0;
 }

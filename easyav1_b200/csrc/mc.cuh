@@ -226,6 +226,127 @@ EAV1_DEVH void mc_block8_fast(const Eav1Tables *tab, const SrcView<uint8_t> &src
     CTA_SYNC();
 }
 
+// 16-bit put/prep for w >= 4 whose whole 8-tap footprint lies inside the reference picture (no edge replication: the
+// caller checks), four horizontally adjacent outputs per work item. Same arithmetic as the general path of mc_block
+// below (mc_tmpl.c:130-187, :247-306), but the taps sit in registers, the eleven samples four outputs share are read
+// once, rows come as plain loads without per-tap clamping, and items are split by shifts instead of divisions.
+EAV1_DEVH void mc_block16_fast(const Eav1Tables *tab, const SrcView<uint16_t> &src, int sx, int sy,
+                              int w, int h, int fw, int fh, int mx, int my, int filt_h, int filt_v,
+                              uint16_t *dst8, int16_t *dst16, int dstride, int bitdepth_max, int16_t *mid,
+                              int tid, int nthr)
+{
+    const int ib = intermediate_bits(bitdepth_max), bias = 8192;
+    const int lq = ulog2((unsigned)w) - 2, qmask = (1 << lq) - 1;
+    int fhc[8] = { 0, 0, 0, 0, 0, 0, 0, 0 }, fvc[8] = { 0, 0, 0, 0, 0, 0, 0, 0 };
+    if (mx) {
+        const int8_t *f = subpel_filter(tab, filt_h, mx, fw);
+#pragma unroll
+        for (int k = 0; k < 8; k++) fhc[k] = f[k];
+    }
+    if (my) {
+        const int8_t *f = subpel_filter(tab, filt_v, my, fh);
+#pragma unroll
+        for (int k = 0; k < 8; k++) fvc[k] = f[k];
+    }
+    auto row = [&](int y) { return reinterpret_cast<const uint16_t *>(src.p + (ptrdiff_t)y * src.stride); };
+    // four horizontally filtered outputs whose first tap is at column x0 of row y
+    auto hquad = [&](int x0, int y, int sum[4]) {
+        const uint16_t *r = row(y) + x0;
+        int v[11];
+#pragma unroll
+        for (int k = 0; k < 11; k++) v[k] = r[k];
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            int a = 0;
+#pragma unroll
+            for (int k = 0; k < 8; k++) a += fhc[k] * v[j + k];
+            sum[j] = a;
+        }
+    };
+    auto put4 = [&](int x, int y, const int o[4]) {          // final samples
+        uint16_t *d = dst8 + y * dstride + x;
+        if (((uintptr_t)d & 7) == 0) {
+            uint2 q; q.x = (uint32_t)o[0] | ((uint32_t)o[1] << 16); q.y = (uint32_t)o[2] | ((uint32_t)o[3] << 16);
+            *reinterpret_cast<uint2 *>(d) = q;
+        } else { d[0] = (uint16_t)o[0]; d[1] = (uint16_t)o[1]; d[2] = (uint16_t)o[2]; d[3] = (uint16_t)o[3]; }
+    };
+    const int n_items = h << lq;
+    if (mx && my) {
+        const int sh1 = 6 - ib, r1 = (1 << sh1) >> 1;
+        for (int y0 = 0; y0 < h; y0 += 32) {
+            const int th = imin(32, h - y0);
+            for (int it = tid; it < ((th + 7) << lq); it += nthr) {
+                const int r = it >> lq, x = (it & qmask) << 2;
+                int sum[4];
+                hquad(sx + x - 3, sy + y0 + r - 3, sum);
+#pragma unroll
+                for (int j = 0; j < 4; j++) sum[j] = (sum[j] + r1) >> sh1;
+                store4_i16(mid + r * w + x, sum);
+            }
+            CTA_SYNC();
+            for (int it = tid; it < (th << lq); it += nthr) {
+                const int r = it >> lq, x = (it & qmask) << 2;
+                int sum[4] = { 0, 0, 0, 0 };
+#pragma unroll
+                for (int k = 0; k < 8; k++) {
+                    const uint2 m = *reinterpret_cast<const uint2 *>(mid + (r + k) * w + x);
+                    sum[0] += fvc[k] * (int)(int16_t)(m.x & 0xffff);
+                    sum[1] += fvc[k] * (int)(int16_t)(m.x >> 16);
+                    sum[2] += fvc[k] * (int)(int16_t)(m.y & 0xffff);
+                    sum[3] += fvc[k] * (int)(int16_t)(m.y >> 16);
+                }
+                if (dst8) {
+#pragma unroll
+                    for (int j = 0; j < 4; j++) sum[j] = iclip((sum[j] + ((1 << (6 + ib)) >> 1)) >> (6 + ib), 0, bitdepth_max);
+                    put4(x, y0 + r, sum);
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 4; j++) sum[j] = ((sum[j] + 32) >> 6) - bias;
+                    store4_i16(dst16 + (y0 + r) * dstride + x, sum);
+                }
+            }
+            CTA_SYNC();
+        }
+        return;
+    }
+    for (int it = tid; it < n_items; it += nthr) {
+        const int y = it >> lq, x = (it & qmask) << 2;
+        int sum[4];
+        if (mx) {
+            hquad(sx + x - 3, sy + y, sum);
+            if (dst8) {
+#pragma unroll
+                for (int j = 0; j < 4; j++) sum[j] = iclip((sum[j] + 32 + ((1 << (6 - ib)) >> 1)) >> 6, 0, bitdepth_max);
+            } else {
+#pragma unroll
+                for (int j = 0; j < 4; j++) sum[j] = ((sum[j] + ((1 << (6 - ib)) >> 1)) >> (6 - ib)) - bias;
+            }
+        } else if (my) {
+            sum[0] = sum[1] = sum[2] = sum[3] = 0;
+#pragma unroll
+            for (int k = 0; k < 8; k++) {
+                const uint16_t *r = row(sy + y + k - 3) + sx + x;
+#pragma unroll
+                for (int j = 0; j < 4; j++) sum[j] += fvc[k] * (int)r[j];
+            }
+            if (dst8) {
+#pragma unroll
+                for (int j = 0; j < 4; j++) sum[j] = iclip((sum[j] + 32) >> 6, 0, bitdepth_max);
+            } else {
+#pragma unroll
+                for (int j = 0; j < 4; j++) sum[j] = ((sum[j] + ((1 << (6 - ib)) >> 1)) >> (6 - ib)) - bias;
+            }
+        } else {
+            const uint16_t *r = row(sy + y) + sx + x;
+#pragma unroll
+            for (int j = 0; j < 4; j++) sum[j] = dst8 ? (int)r[j] : ((int)r[j] << ib) - bias;
+        }
+        if (dst8) put4(x, y, sum);
+        else store4_i16(dst16 + y * dstride + x, sum);
+    }
+    CTA_SYNC();
+}
+
 // Unscaled put/prep. dst8 (pixels) xor dst16 (prep) receives a w x h block with the given
 // stride (elements). `mid` is CTA scratch of at least (32+7)*128 int16.
 // (w,h) is the rectangle produced; (fw,fh) the dimensions of the whole prediction block, which
@@ -243,6 +364,13 @@ EAV1_DEVH void mc_block(const Eav1Tables *tab, const SrcView<typename BD::pixel>
     if constexpr (!BD::hbd) {
         if (w >= 4 && !bilin && (!dst16 || (dstride & 3) == 0)) {
             mc_block8_fast(tab, src, sx, sy, w, h, fw, fh, mx, my, filt_h, filt_v, dst8, dst16, dstride, mid, tid, nthr);
+            return;
+        }
+    } else {
+        if (w >= 4 && !bilin && (!dst16 || (dstride & 3) == 0) &&
+            sx >= 3 && sy >= 3 && sx + w + 4 <= src.iw && sy + h + 4 <= src.ih) {
+            mc_block16_fast(tab, src, sx, sy, w, h, fw, fh, mx, my, filt_h, filt_v, dst8, dst16, dstride, bitdepth_max,
+                            mid, tid, nthr);
             return;
         }
     }
